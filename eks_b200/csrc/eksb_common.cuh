@@ -1,0 +1,34 @@
+// Shared host-side helpers for the libeksb translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include "../../include/eksb.h"
+#include "eksb_dims.h"
+#include "eksb_math.cuh"
+
+namespace eksb {
+
+void set_error(const char* fmt, ...);
+
+inline int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return EKSB_ECUDA;
+  }
+  return EKSB_OK;
+}
+
+inline long num_tiles(long B) { return (B + kLanes - 1) / kLanes; }
+
+// Device-side gather of one track's parameters into registers.
+template <typename T, int N, int P, int AM>
+__device__ __forceinline__ void load_track_params(Params<T, N, P, AM>& prm, const T* C, const T* A, const T* Q,
+                                                  int shared_mask, long b) {
+  const T* c = C + ((shared_mask & EKSB_SHARED_C) ? 0 : b * (P * N));
+  const T* a = A + ((shared_mask & EKSB_SHARED_A) ? 0 : b * (N * N));
+  const T* q = Q + ((shared_mask & EKSB_SHARED_Q) ? 0 : b * (N * N));
+  load_params<T, N, P, AM>(prm, c, a, q);
+}
+
+}  // namespace eksb

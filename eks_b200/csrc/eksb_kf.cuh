@@ -1,0 +1,143 @@
+// eksb_kf.cuh -- forward Kalman filter (A2/A3, A6) and RTS smoother (A4/A5) kernels.
+//
+// Mapping: one track per thread, one track-tile (32 tracks) per warp, one warp per CTA.
+// Every global access of a warp is one contiguous 128 B (f32) / 256 B (f64) line of the
+// track-tile layout (eksb_math.cuh), so the kernels stream HBM at full sector efficiency
+// with no shared-memory staging; latency is covered by a PF-frame register prefetch ring.
+// All matrices live in registers (see -Xptxas -v: no local memory).
+#pragma once
+#include "eksb_common.cuh"
+
+namespace eksb {
+
+// Frames in flight per thread: as many as fit in ~64 32-bit registers of prefetch ring.
+template <typename T, int ROWS> struct Prefetch {
+  static constexpr int kRegsPerFrame = ROWS * (int)(sizeof(T) / 4);
+  static constexpr int value = (64 / kRegsPerFrame) < 1 ? 1 : (64 / kRegsPerFrame);
+};
+
+// grid = (n_tiles, n_scale), block = 32
+template <typename T, int N, int P, int AM, bool NLL>
+__global__ void __launch_bounds__(kLanes)
+kf_forward_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
+                  const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
+                  long B, long Tn, int first, const T* __restrict__ q_scale, T* __restrict__ filt,
+                  double* __restrict__ nll, int* __restrict__ status) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
+  const long g = blockIdx.x;
+  const int lane = threadIdx.x;
+  const long b = g * kLanes + lane;
+  const long bp = b < B ? b : B - 1;   // padding lanes replay the last track's parameters
+  Params<T, N, P, AM> prm;
+  load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
+  if (q_scale) {
+    const T s = q_scale[blockIdx.y];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) prm.Q[i] *= s;
+  }
+  T m[N], V[NS];
+  {
+    const T* pm = m0 + ((shared_mask & EKSB_SHARED_M0) ? 0 : bp * N);
+    const T* ps = S0 + ((shared_mask & EKSB_SHARED_S0) ? 0 : bp * (N * N));
+#pragma unroll
+    for (int i = 0; i < N; ++i) m[i] = pm[i];
+    load_sym<T, N>(V, ps);
+  }
+  bool ok = true;
+  if (first == kPriorOnly) {   // eks/newton_eks.py:132 : P starts at inv(S0)
+    T Vi[NS];
+    sym_inv<T, N>(V, Vi, ok);
+#pragma unroll
+    for (int i = 0; i < NS; ++i) V[i] = Vi[i];
+  }
+  const T* o = obs + (g * Tn * (2 * P)) * kLanes + lane;
+  T* f = filt ? filt + (g * Tn * SG) * kLanes + lane : nullptr;
+  double acc = 0.0;
+  ok = kf_forward_range<T, N, P, AM, kLanes, Prefetch<T, 2 * P>::value, NLL>(prm, o, f, Tn, first, m, V, acc) && ok;
+  if (b < B) {
+    if (NLL) nll[(long)blockIdx.y * B + b] = 0.5 * (acc + (double)Tn * P * 1.8378770664093453 /* log 2pi */);
+    if (status && !ok) status[b] = 1;
+  }
+}
+
+// grid = n_tiles, block = 32
+template <typename T, int N, int P, int AM>
+__global__ void __launch_bounds__(kLanes)
+rts_backward_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
+                    int shared_mask, long B, long Tn, T* smth, T* __restrict__ ym, T* __restrict__ yv,
+                    T* __restrict__ cv, int* __restrict__ status) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
+  const long g = blockIdx.x;
+  const int lane = threadIdx.x;
+  const long b = g * kLanes + lane;
+  const long bp = b < B ? b : B - 1;
+  Params<T, N, P, AM> prm;
+  load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
+  const long base = g * Tn * kLanes;
+  T ms[N], Vs[NS];
+  bool ok = rts_backward_range<T, N, P, AM, kLanes, Prefetch<T, Dim<N>::SIGMA>::value>(
+      prm, filt + base * SG + lane, smth + base * SG + lane, ym ? ym + base * P + lane : nullptr,
+      yv ? yv + base * P + lane : nullptr, cv ? cv + base * (N * N) + lane : nullptr, Tn, true, ms, Vs);
+  if (b < B && status && !ok) status[b] = 1;
+}
+
+template <typename T, int N, int P>
+static int launch_forward(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
+                          long B, long Tn, int a_mode, int first, const T* q_scale, int n_scale, T* filt, double* nll,
+                          int* status, cudaStream_t st) {
+  dim3 grid((unsigned)num_tiles(B), (unsigned)(q_scale ? n_scale : 1));
+#define EKSB_GO(AM_, NLL_)                                                                                      \
+  kf_forward_kernel<T, N, P, AM_, NLL_><<<grid, kLanes, 0, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, \
+                                                                 q_scale, filt, nll, status)
+  if (a_mode == EKSB_A_DIAG) { if (nll) EKSB_GO(0, true); else EKSB_GO(0, false); }
+  else                       { if (nll) EKSB_GO(1, true); else EKSB_GO(1, false); }
+#undef EKSB_GO
+  return check_launch("kf_forward_kernel");
+}
+
+template <typename T, int N, int P>
+static int launch_backward(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
+                           int a_mode, T* smth, T* ym, T* yv, T* cv, int* status, cudaStream_t st) {
+  unsigned grid = (unsigned)num_tiles(B);
+  if (a_mode == EKSB_A_DIAG)
+    rts_backward_kernel<T, N, P, 0><<<grid, kLanes, 0, st>>>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, cv, status);
+  else
+    rts_backward_kernel<T, N, P, 1><<<grid, kLanes, 0, st>>>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, cv, status);
+  return check_launch("rts_backward_kernel");
+}
+
+template <typename T>
+static int kf_forward_api(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
+                          long B, long Tn, int n, int p, int a_mode, int first, const T* q_scale, int n_scale, T* filt,
+                          double* nll, int* status, void* stream) {
+  if (!obs || !m0 || !S0 || !C || !A || !Q || B <= 0 || Tn <= 0) { set_error("kf_forward: null pointer or empty batch"); return EKSB_EARG; }
+  if (first != kPriorUpdate && first != kPriorOnly) { set_error("kf_forward: bad first-frame mode %d", first); return EKSB_EARG; }
+  if (a_mode != EKSB_A_DIAG && a_mode != EKSB_A_DENSE) { set_error("kf_forward: bad a_mode %d", a_mode); return EKSB_EARG; }
+  if (q_scale && n_scale > 1 && filt) { set_error("kf_forward: filt must be NULL when sweeping n_scale > 1"); return EKSB_EARG; }
+  if (q_scale && n_scale < 1) { set_error("kf_forward: n_scale < 1"); return EKSB_EARG; }
+#define X(N_, P_)                                                                                                 \
+  if (n == N_ && p == P_)                                                                                         \
+    return launch_forward<T, N_, P_>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, a_mode, first, q_scale, n_scale,   \
+                                     filt, nll, status, (cudaStream_t)stream);
+  EKSB_FOR_EACH_DIM(X)
+#undef X
+  set_error("kf_forward: (n=%d,p=%d) not instantiated", n, p);
+  return EKSB_EDIM;
+}
+
+template <typename T>
+static int rts_backward_api(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, int n,
+                            int p, int a_mode, T* smth, T* ym, T* yv, T* cv, int* status, void* stream) {
+  if (!filt || !smth || !C || !A || !Q || B <= 0 || Tn <= 0) { set_error("rts_backward: null pointer or empty batch"); return EKSB_EARG; }
+  if (a_mode != EKSB_A_DIAG && a_mode != EKSB_A_DENSE) { set_error("rts_backward: bad a_mode %d", a_mode); return EKSB_EARG; }
+#define X(N_, P_)                                                                                           \
+  if (n == N_ && p == P_)                                                                                   \
+    return launch_backward<T, N_, P_>(filt, C, A, Q, shared_mask, B, Tn, a_mode, smth, ym, yv, cv, status, \
+                                      (cudaStream_t)stream);
+  EKSB_FOR_EACH_DIM(X)
+#undef X
+  set_error("rts_backward: (n=%d,p=%d) not instantiated", n, p);
+  return EKSB_EDIM;
+}
+
+}  // namespace eksb

@@ -1,0 +1,11 @@
+// one dtype x one pass per translation unit so `make -j` compiles them in parallel
+#define EKSB_ONLY_FWD 1
+#include "eksb_kf.cuh"
+using namespace eksb;
+
+extern "C" int eksb_kf_forward_f32(const float* obs, const float* m0, const float* S0, const float* C, const float* A,
+                                   const float* Q, int shared_mask, long B, long T, int n, int p, int a_mode, int first,
+                                   const float* q_scale, int n_scale, float* filt, double* nll, int* status,
+                                   void* stream) {
+  return kf_forward_api<float>(obs, m0, S0, C, A, Q, shared_mask, B, T, n, p, a_mode, first, q_scale, n_scale, filt, nll, status, stream);
+}

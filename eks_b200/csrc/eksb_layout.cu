@@ -1,0 +1,218 @@
+// eksb_layout.cu -- library housekeeping and the layout kernels: (B,T,R) <-> track-tile
+// transposes and the dense expansion of state records into the reference's return values.
+#include <stdarg.h>
+#include "eksb_common.cuh"
+
+namespace eksb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+constexpr int kFT = 16;   // frames per transpose tile
+
+// (B,T,R) row-major -> rows [row0,row0+R) of track-tile records.  One CTA moves a tile of
+// 32 tracks x kFT frames through shared memory: global reads are contiguous runs of kFT*R
+// scalars per track, global writes are full 32-lane lines.  grid = n_tiles * ceil(T/kFT).
+template <typename T>
+__global__ void __launch_bounds__(256) pack_rows_kernel(const T* __restrict__ src, long B, long Tn, int R,
+                                                        T* __restrict__ dst, int rows, int row0, T pad) {
+  extern __shared__ unsigned char smem_raw[];
+  T* s = reinterpret_cast<T*>(smem_raw);
+  const long nchunk = (Tn + kFT - 1) / kFT;      // 1-D grid: tile-major, frame-chunk minor
+  const long g = blockIdx.x / nchunk;
+  const long t0 = (blockIdx.x - g * nchunk) * kFT;
+  const int nf = (int)((Tn - t0) < kFT ? (Tn - t0) : kFT);
+  const int run = nf * R, pitch = kFT * R + 1;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = warp; i < kLanes; i += 8) {
+    const long b = g * kLanes + i;
+    for (int k = lane; k < run; k += 32) s[i * pitch + k] = (b < B) ? src[(b * Tn + t0) * R + k] : pad;
+  }
+  __syncthreads();
+  for (int fr = warp; fr < nf * R; fr += 8) {
+    const int f = fr / R, r = fr - f * R;
+    dst[((g * Tn + t0 + f) * rows + row0 + r) * kLanes + lane] = s[lane * pitch + fr];
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) unpack_rows_kernel(const T* __restrict__ src, int rows, int row0, long B, long Tn,
+                                                          int R, T* __restrict__ dst) {
+  extern __shared__ unsigned char smem_raw[];
+  T* s = reinterpret_cast<T*>(smem_raw);
+  const long nchunk = (Tn + kFT - 1) / kFT;      // 1-D grid: tile-major, frame-chunk minor
+  const long g = blockIdx.x / nchunk;
+  const long t0 = (blockIdx.x - g * nchunk) * kFT;
+  const int nf = (int)((Tn - t0) < kFT ? (Tn - t0) : kFT);
+  const int run = nf * R, pitch = kFT * R + 1;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int fr = warp; fr < run; fr += 8) {
+    const int f = fr / R, r = fr - f * R;
+    s[lane * pitch + fr] = src[((g * Tn + t0 + f) * rows + row0 + r) * kLanes + lane];
+  }
+  __syncthreads();
+  for (int i = warp; i < kLanes; i += 8) {
+    const long b = g * kLanes + i;
+    if (b < B)
+      for (int k = lane; k < run; k += 32) dst[(b * Tn + t0) * R + k] = s[i * pitch + k];
+  }
+}
+
+template <typename T>
+static int pack_rows_api(const T* src, long B, long Tn, int R, T* dst, int rows, int row0, T pad, void* stream, bool unpack) {
+  if (!src || !dst || B <= 0 || Tn <= 0 || R <= 0 || row0 < 0 || row0 + R > rows) { set_error("pack/unpack_rows: bad argument"); return EKSB_EARG; }
+  if (R > 64) { set_error("pack/unpack_rows: R > 64"); return EKSB_EARG; }
+  unsigned grid = (unsigned)(((Tn + kFT - 1) / kFT) * num_tiles(B));
+  size_t smem = sizeof(T) * kLanes * (kFT * R + 1);
+  if (smem > 48 * 1024) {
+    cudaFuncSetAttribute(pack_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(unpack_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  }
+  if (unpack) unpack_rows_kernel<T><<<grid, 256, smem, (cudaStream_t)stream>>>(src, rows, row0, B, Tn, R, dst);
+  else        pack_rows_kernel<T><<<grid, 256, smem, (cudaStream_t)stream>>>(src, B, Tn, R, dst, rows, row0, pad);
+  return check_launch(unpack ? "unpack_rows_kernel" : "pack_rows_kernel");
+}
+
+// One thread per (track, frame): state record -> dense mean / cov / predicted cov.
+// Output formatting for the numpy-facing API (small T); reads are lane-coalesced.
+template <typename T, int N>
+__global__ void expand_state_kernel(const T* __restrict__ state, long B, long Tn, const T* __restrict__ A,
+                                    const T* __restrict__ Q, const T* __restrict__ S0, int shared_mask,
+                                    T* __restrict__ mean, T* __restrict__ cov, T* __restrict__ pred) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
+  const int lane = threadIdx.x & 31;
+  const long nchunk = (Tn + 7) / 8;
+  const long g = blockIdx.x / nchunk;
+  const long t = (blockIdx.x - g * nchunk) * 8 + (threadIdx.x >> 5);
+  const long b = g * kLanes + lane;
+  if (t >= Tn || b >= B) return;
+  const T* rec = state + ((g * Tn + t) * SG) * kLanes + lane;
+  T m[N], V[NS];
+#pragma unroll
+  for (int i = 0; i < N; ++i) m[i] = rec[i * kLanes];
+#pragma unroll
+  for (int i = 0; i < NS; ++i) V[i] = rec[(N + i) * kLanes];
+  const long o = b * Tn + t;
+#pragma unroll
+  for (int i = 0; i < N; ++i) mean[o * N + i] = m[i];
+#pragma unroll
+  for (int i = 0; i < N; ++i)
+#pragma unroll
+    for (int j = 0; j < N; ++j) cov[(o * N + i) * N + j] = V[sym_idx<N>(i, j)];
+  if (pred) {
+    const T* a = A + ((shared_mask & EKSB_SHARED_A) ? 0 : b * (N * N));
+    const T* q = Q + ((shared_mask & EKSB_SHARED_Q) ? 0 : b * (N * N));
+    const T* s0 = S0 + ((shared_mask & EKSB_SHARED_S0) ? 0 : b * (N * N));
+#pragma unroll
+    for (int i = 0; i < N; ++i)
+#pragma unroll
+      for (int j = 0; j < N; ++j) {
+        T v = T(0);
+        if (Tn == 1) {
+          v = s0[i * N + j];                       // eks/ensemble_kalman.py:96 with T == 1
+        } else if (t < Tn - 1) {                   // :101 ; S[T-1] stays zero
+          v = q[i * N + j];
+          for (int k = 0; k < N; ++k)
+            for (int l = 0; l < N; ++l) v += a[i * N + k] * V[sym_idx<N>(k, l)] * a[j * N + l];
+        }
+        pred[(o * N + i) * N + j] = v;
+      }
+  }
+}
+
+template <typename T, int N>
+__global__ void pack_state_kernel(const T* __restrict__ mean, const T* __restrict__ cov, long B, long Tn,
+                                  T* __restrict__ state) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
+  const int lane = threadIdx.x & 31;
+  const long nchunk = (Tn + 7) / 8;
+  const long g = blockIdx.x / nchunk;
+  const long t = (blockIdx.x - g * nchunk) * 8 + (threadIdx.x >> 5);
+  const long b = g * kLanes + lane;
+  if (t >= Tn) return;
+  T* rec = state + ((g * Tn + t) * SG) * kLanes + lane;
+  const long o = (b < B ? b : B - 1) * Tn + t;   // padding lanes replicate the last track
+#pragma unroll
+  for (int i = 0; i < N; ++i) rec[i * kLanes] = mean[o * N + i];
+#pragma unroll
+  for (int i = 0; i < N; ++i)
+#pragma unroll
+    for (int j = i; j < N; ++j)
+      rec[(N + sym_idx<N>(i, j)) * kLanes] = T(0.5) * (cov[(o * N + i) * N + j] + cov[(o * N + j) * N + i]);
+}
+
+template <typename T>
+static int expand_state_api(const T* state, long B, long Tn, int n, const T* A, const T* Q, const T* S0, int shared_mask,
+                            T* mean, T* cov, T* pred, void* stream) {
+  if (!state || !mean || !cov || B <= 0 || Tn <= 0 || (pred && (!A || !Q || !S0))) { set_error("expand_state: bad argument"); return EKSB_EARG; }
+  unsigned grid = (unsigned)(((Tn + 7) / 8) * num_tiles(B));
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (n) {
+#define CASE(N_) case N_: expand_state_kernel<T, N_><<<grid, 256, 0, st>>>(state, B, Tn, A, Q, S0, shared_mask, mean, cov, pred); break;
+    CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
+#undef CASE
+    default: set_error("expand_state: n=%d not instantiated", n); return EKSB_EDIM;
+  }
+  return check_launch("expand_state_kernel");
+}
+
+template <typename T>
+static int pack_state_api(const T* mean, const T* cov, long B, long Tn, int n, T* state, void* stream) {
+  if (!state || !mean || !cov || B <= 0 || Tn <= 0) { set_error("pack_state: bad argument"); return EKSB_EARG; }
+  unsigned grid = (unsigned)(((Tn + 7) / 8) * num_tiles(B));
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (n) {
+#define CASE(N_) case N_: pack_state_kernel<T, N_><<<grid, 256, 0, st>>>(mean, cov, B, Tn, state); break;
+    CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
+#undef CASE
+    default: set_error("pack_state: n=%d not instantiated", n); return EKSB_EDIM;
+  }
+  return check_launch("pack_state_kernel");
+}
+
+}  // namespace eksb
+
+using namespace eksb;
+
+extern "C" int eksb_version(void) { return 100; }
+extern "C" const char* eksb_last_error_string(void) { return g_err; }
+extern "C" long eksb_num_tiles(long B) { return num_tiles(B); }
+extern "C" int eksb_supported_dims(int n, int p) {
+#define X(N_, P_) if (n == N_ && p == P_) return 1;
+  EKSB_FOR_EACH_DIM(X)
+#undef X
+  return 0;
+}
+
+extern "C" int eksb_pack_rows_f64(const double* src, long B, long T, int R, double* dst, int rows, int row0, double pad, void* stream) {
+  return pack_rows_api<double>(src, B, T, R, dst, rows, row0, pad, stream, false);
+}
+extern "C" int eksb_pack_rows_f32(const float* src, long B, long T, int R, float* dst, int rows, int row0, float pad, void* stream) {
+  return pack_rows_api<float>(src, B, T, R, dst, rows, row0, pad, stream, false);
+}
+extern "C" int eksb_unpack_rows_f64(const double* src, int rows, int row0, long B, long T, int R, double* dst, void* stream) {
+  return pack_rows_api<double>(src, B, T, R, dst, rows, row0, 0.0, stream, true);
+}
+extern "C" int eksb_unpack_rows_f32(const float* src, int rows, int row0, long B, long T, int R, float* dst, void* stream) {
+  return pack_rows_api<float>(src, B, T, R, dst, rows, row0, 0.f, stream, true);
+}
+extern "C" int eksb_expand_state_f64(const double* state, long B, long T, int n, const double* A, const double* Q, const double* S0,
+                                     int shared_mask, double* mean, double* cov, double* pred, void* stream) {
+  return expand_state_api<double>(state, B, T, n, A, Q, S0, shared_mask, mean, cov, pred, stream);
+}
+extern "C" int eksb_expand_state_f32(const float* state, long B, long T, int n, const float* A, const float* Q, const float* S0,
+                                     int shared_mask, float* mean, float* cov, float* pred, void* stream) {
+  return expand_state_api<float>(state, B, T, n, A, Q, S0, shared_mask, mean, cov, pred, stream);
+}
+extern "C" int eksb_pack_state_f64(const double* mean, const double* cov, long B, long T, int n, double* state, void* stream) {
+  return pack_state_api<double>(mean, cov, B, T, n, state, stream);
+}
+extern "C" int eksb_pack_state_f32(const float* mean, const float* cov, long B, long T, int n, float* state, void* stream) {
+  return pack_state_api<float>(mean, cov, B, T, n, state, stream);
+}

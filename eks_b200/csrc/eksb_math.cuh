@@ -1,0 +1,514 @@
+// eksb_math.cuh -- small-matrix arithmetic and the per-track EKS recursions.
+//
+// Everything here is a __host__ __device__ template so that the *same* per-thread
+// program the sm_100a kernels run can also be compiled by g++ and unit-tested on
+// the CPU-only build box (tests/hostsim -- test infrastructure; the product never
+// calls the host build).  State dimension N, observation dimension P and the
+// scalar type are template parameters; all loops have constant bounds and are
+// fully unrolled so every matrix lives in registers.
+//
+// Symmetric N x N matrices are stored packed, upper triangle row-major:
+//   sym_idx<N>(i,j), i<=j  ->  i*N - i*(i-1)/2 + (j-i)      (NS = N(N+1)/2 values)
+#pragma once
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define EKSB_HD __host__ __device__ __forceinline__
+#define EKSB_UNROLL _Pragma("unroll")
+#else
+#define EKSB_HD inline __attribute__((always_inline))
+#define EKSB_UNROLL
+#endif
+
+namespace eksb {
+
+constexpr int kLanes = 32;  // tracks per track-tile (one warp)
+
+template <int N> struct Dim { static constexpr int NS = N * (N + 1) / 2; static constexpr int SIGMA = N + NS; };
+
+template <int N> EKSB_HD constexpr int sym_idx(int i, int j) {
+  return (i <= j) ? (i * N - i * (i - 1) / 2 + (j - i)) : (j * N - j * (j - 1) / 2 + (i - j));
+}
+
+template <typename T> EKSB_HD T rcp(T x) { return T(1) / x; }
+
+// ---------------------------------------------------------------------------
+// SPD inverse of a packed symmetric matrix.  Returns det(a) (used by the NLL).
+// N<=3: closed-form adjugate (one reciprocal, short dependency chain);
+// N>3 : unrolled LDL^T, inverse = L^-T D^-1 L^-1.
+// ok is cleared when a pivot / determinant is not strictly positive (the
+// reference would raise numpy.linalg.LinAlgError or silently produce garbage).
+// ---------------------------------------------------------------------------
+template <typename T, int N> struct SymInv;
+
+template <typename T> struct SymInv<T, 1> {
+  static EKSB_HD T run(const T* a, T* inv, bool& ok) { ok = ok && (a[0] > T(0)); inv[0] = rcp(a[0]); return a[0]; }
+};
+
+template <typename T> struct SymInv<T, 2> {
+  static EKSB_HD T run(const T* a, T* inv, bool& ok) {
+    T det = a[0] * a[2] - a[1] * a[1];
+    ok = ok && (det > T(0)) && (a[0] > T(0));
+    T r = rcp(det);
+    inv[0] = a[2] * r; inv[1] = -a[1] * r; inv[2] = a[0] * r;
+    return det;
+  }
+};
+
+template <typename T> struct SymInv<T, 3> {
+  static EKSB_HD T run(const T* a, T* inv, bool& ok) {
+    // a = [a00 a01 a02 a11 a12 a22]
+    T c00 = a[3] * a[5] - a[4] * a[4];
+    T c01 = a[2] * a[4] - a[1] * a[5];
+    T c02 = a[1] * a[4] - a[2] * a[3];
+    T c11 = a[0] * a[5] - a[2] * a[2];
+    T c12 = a[1] * a[2] - a[0] * a[4];
+    T c22 = a[0] * a[3] - a[1] * a[1];
+    T det = a[0] * c00 + a[1] * c01 + a[2] * c02;
+    ok = ok && (det > T(0)) && (a[0] > T(0)) && (c22 > T(0));
+    T r = rcp(det);
+    inv[0] = c00 * r; inv[1] = c01 * r; inv[2] = c02 * r;
+    inv[3] = c11 * r; inv[4] = c12 * r; inv[5] = c22 * r;
+    return det;
+  }
+};
+
+template <typename T, int N> struct SymInv {
+  static EKSB_HD T run(const T* a, T* inv, bool& ok) {
+    T L[N][N];   // unit lower factor (strict lower part used)
+    T d[N], rd[N];
+    T det = T(1);
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T s = a[sym_idx<N>(j, j)];
+      EKSB_UNROLL
+      for (int k = 0; k < j; ++k) s -= L[j][k] * L[j][k] * d[k];
+      d[j] = s; ok = ok && (s > T(0)); rd[j] = rcp(s); det *= s;
+      EKSB_UNROLL
+      for (int i = j + 1; i < N; ++i) {
+        T v = a[sym_idx<N>(j, i)];
+        EKSB_UNROLL
+        for (int k = 0; k < j; ++k) v -= L[i][k] * L[j][k] * d[k];
+        L[i][j] = v * rd[j];
+      }
+    }
+    // Li = L^-1 (unit lower): Li[i][j] = -sum_{k=j}^{i-1} L[i][k] Li[k][j]
+    T Li[N][N];
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      Li[j][j] = T(1);
+      EKSB_UNROLL
+      for (int i = j + 1; i < N; ++i) {
+        T s = T(0);
+        EKSB_UNROLL
+        for (int k = j; k < i; ++k) s -= L[i][k] * Li[k][j];
+        Li[i][j] = s;
+      }
+    }
+    // inv = Li^T D^-1 Li
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = i; j < N; ++j) {
+        T s = T(0);
+        EKSB_UNROLL
+        for (int k = j; k < N; ++k) s += Li[k][i] * Li[k][j] * rd[k];
+        inv[sym_idx<N>(i, j)] = s;
+      }
+    }
+    return det;
+  }
+};
+
+template <typename T, int N> EKSB_HD T sym_inv(const T* a, T* inv, bool& ok) { return SymInv<T, N>::run(a, inv, ok); }
+
+// y = S x  (S packed symmetric)
+template <typename T, int N> EKSB_HD void sym_matvec(const T* S, const T* x, T* y) {
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    T s = T(0);
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) s += S[sym_idx<N>(i, j)] * x[j];
+    y[i] = s;
+  }
+}
+
+// out (packed sym) = J D J^T, D packed symmetric, J full row-major N x N
+template <typename T, int N> EKSB_HD void sandwich(const T J[N][N], const T* D, T* out) {
+  T W[N][N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += J[i][k] * D[sym_idx<N>(k, j)];
+      W[i][j] = s;
+    }
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = i; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += W[i][k] * J[j][k];
+      out[sym_idx<N>(i, j)] = s;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Per-track model parameters, held in registers for the whole pass.
+// AM = 0: diagonal state transition (covers A = I, every shipped config);
+// AM = 1: dense A.
+// ---------------------------------------------------------------------------
+template <typename T, int N, int P, int AM> struct Params {
+  static constexpr int NS = Dim<N>::NS;
+  T C[P][N];
+  T A[AM ? N * N : N];
+  T AA[AM ? 1 : NS];   // a_i * a_j (diagonal mode only)
+  T Q[NS];
+};
+
+// Load from dense row-major host-style arrays: C (P,N), A (N,N), Q (N,N).
+template <typename T, int N, int P, int AM>
+EKSB_HD void load_params(Params<T, N, P, AM>& prm, const T* C, const T* A, const T* Q) {
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) {
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) prm.C[j][i] = C[j * N + i];
+  }
+  if (AM) {
+    EKSB_UNROLL
+    for (int i = 0; i < N * N; ++i) prm.A[i] = A[i];
+  } else {
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) prm.A[i] = A[i * N + i];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = i; j < N; ++j) prm.AA[sym_idx<N>(i, j)] = A[i * N + i] * A[j * N + j];
+    }
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = i; j < N; ++j) prm.Q[sym_idx<N>(i, j)] = T(0.5) * (Q[i * N + j] + Q[j * N + i]);
+  }
+}
+
+// packed symmetric from a dense row-major (N,N) array
+template <typename T, int N> EKSB_HD void load_sym(T* S, const T* dense) {
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = i; j < N; ++j) S[sym_idx<N>(i, j)] = T(0.5) * (dense[i * N + j] + dense[j * N + i]);
+  }
+}
+
+// mp = A m ; S = A V A^T + Q        (eks/ensemble_kalman.py:101-102)
+template <typename T, int N, int P, int AM>
+EKSB_HD void predict(const Params<T, N, P, AM>& prm, const T* m, const T* V, T* mp, T* S) {
+  if (AM == 0) {
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) mp[i] = prm.A[i] * m[i];
+    EKSB_UNROLL
+    for (int k = 0; k < Dim<N>::NS; ++k) S[k] = prm.AA[k] * V[k] + prm.Q[k];
+  } else {
+    T G[N][N];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) s += prm.A[i * N + j] * m[j];
+      mp[i] = s;
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) {
+        T g = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) g += prm.A[i * N + k] * V[sym_idx<N>(k, j)];
+        G[i][j] = g;
+      }
+    }
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = i; j < N; ++j) {
+        T s = prm.Q[sym_idx<N>(i, j)];
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) s += G[i][k] * prm.A[j * N + k];
+        S[sym_idx<N>(i, j)] = s;
+      }
+    }
+  }
+}
+
+// Measurement update with R = diag(r), in information form (N x N inverses only,
+// independent of P):      Vf = (S^-1 + C^T R^-1 C)^-1 ,  mf = mp + Vf C^T R^-1 (y - C mp).
+// Algebraically identical to eks/ensemble_kalman.py:104-105,110-117 (Woodbury) and to
+// the update at eks/newton_eks.py:137-138.  When NLL is set, returns this frame's
+//   log det(R + C S C^T) + nu^T (R + C S C^T)^-1 nu      (determinant lemma).
+template <typename T, int N, int P, int AM, bool NLL>
+EKSB_HD double update(const Params<T, N, P, AM>& prm, const T* y, const T* r, const T* mp, const T* S,
+                      T* m, T* V, bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T w[P], nu[P];
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) {
+    w[j] = rcp(r[j]);
+    T s = y[j];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) s -= prm.C[j][i] * mp[i];
+    nu[j] = s;
+  }
+  T Sinv[NS], Lam[NS];
+  T detS = sym_inv<T, N>(S, Sinv, ok);
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) Lam[k] = Sinv[k];
+  T u[N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) u[i] = T(0);
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) {
+    T cw[N];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) cw[i] = prm.C[j][i] * w[j];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      u[i] += cw[i] * nu[j];
+      EKSB_UNROLL
+      for (int k = i; k < N; ++k) Lam[sym_idx<N>(i, k)] += cw[i] * prm.C[j][k];
+    }
+  }
+  T detL = sym_inv<T, N>(Lam, V, ok);
+  T Vu[N];
+  sym_matvec<T, N>(V, u, Vu);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) m[i] = mp[i] + Vu[i];
+  if (NLL) {
+    double quad = 0.0, detR = 1.0, uVu = 0.0;
+    EKSB_UNROLL
+    for (int j = 0; j < P; ++j) { quad += (double)nu[j] * (double)nu[j] * (double)w[j]; detR *= (double)r[j]; }
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) uVu += (double)u[i] * (double)Vu[i];
+    return log(detR * (double)detS * (double)detL) + (quad - uVu);
+  }
+  return 0.0;
+}
+
+// ---------------------------------------------------------------------------
+// Track-tile memory layout (DESIGN.md "HBM layout").  A tile is kLanes tracks;
+// a frame record is ROWS scalars per track stored as ROWS rows of kLanes lanes:
+//     addr(tile g, frame t, row r, lane l) = ((g*T + t)*ROWS + r)*kLanes + l
+// so a warp (lane = track) reads/writes one full 128 B (f32) / 256 B (f64) line per
+// row.  The range functions below take a pointer already offset to (g, t0, row 0,
+// lane) and a compile-time lane stride LS (kLanes on the device, 1 in host tests).
+//   obs record   : rows [0,P) = y, [P,2P) = ensemble variance          (2P rows)
+//   state record : rows [0,N) = mean, [N,N+NS) = packed covariance      (SIGMA rows)
+// ---------------------------------------------------------------------------
+enum FirstFrame { kContinue = 0, kPriorUpdate = 1, kPriorOnly = 2 };
+
+// Forward filter over `n` frames.  (m,V) carries the state in and out:
+//   first == kPriorUpdate : (m,V) = (m0,S0), frame 0 is an update with no predict
+//                           (eks/ensemble_kalman.py:94-96);
+//   first == kPriorOnly   : frame 0 just emits (m,V) (eks/newton_eks.py:128,132);
+//   first == kContinue    : (m,V) is the filtered state of the frame before this range.
+// filt may be null (NLL-only sweeps).  PF = software prefetch depth in frames.
+template <typename T, int N, int P, int AM, int LS, int PF, bool NLL>
+EKSB_HD bool kf_forward_range(const Params<T, N, P, AM>& prm, const T* __restrict__ obs, T* __restrict__ filt,
+                              long n, int first, T* m, T* V, double& nll) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
+  bool ok = true;
+  T buf[PF][R2];
+  EKSB_UNROLL
+  for (int k = 0; k < PF; ++k) {
+    long f = (k < n) ? k : (n - 1);
+    EKSB_UNROLL
+    for (int r = 0; r < R2; ++r) buf[k][r] = obs[(f * R2 + r) * LS];
+  }
+  for (long t = 0; t < n; t += PF) {
+    EKSB_UNROLL
+    for (int k = 0; k < PF; ++k) {
+      if (t + k < n) {
+        T cur[R2];
+        EKSB_UNROLL
+        for (int r = 0; r < R2; ++r) cur[r] = buf[k][r];
+        long f = t + k + PF;
+        if (f > n - 1) f = n - 1;
+        EKSB_UNROLL
+        for (int r = 0; r < R2; ++r) buf[k][r] = obs[(f * R2 + r) * LS];
+        const bool is_first = (t + k == 0);
+        if (!(is_first && first == kPriorOnly)) {
+          T mp[N], S[NS];
+          if (is_first && first == kPriorUpdate) {
+            EKSB_UNROLL
+            for (int i = 0; i < N; ++i) mp[i] = m[i];
+            EKSB_UNROLL
+            for (int i = 0; i < NS; ++i) S[i] = V[i];
+          } else {
+            predict<T, N, P, AM>(prm, m, V, mp, S);
+          }
+          double e = update<T, N, P, AM, NLL>(prm, cur, cur + P, mp, S, m, V, ok);
+          if (NLL) nll += e;
+        }
+        if (filt) {
+          T* o = filt + (t + k) * SG * LS;
+          EKSB_UNROLL
+          for (int i = 0; i < N; ++i) o[i * LS] = m[i];
+          EKSB_UNROLL
+          for (int i = 0; i < NS; ++i) o[(N + i) * LS] = V[i];
+        }
+      }
+    }
+  }
+  return ok;
+}
+
+// One RTS step (eks/ensemble_kalman.py:158-162): from filtered (m,V) at t and smoothed
+// (ms1,Vs1) at t+1 to smoothed (ms,Vs) at t.  S = A V A^T + Q is recomputed, not stored.
+// Jout (optional, full N x N) receives J so the caller can form CV = Vs1 J^T.
+template <typename T, int N, int P, int AM>
+EKSB_HD void rts_step(const Params<T, N, P, AM>& prm, const T* m, const T* V, const T* ms1, const T* Vs1,
+                      T* ms, T* Vs, T (*Jout)[N], bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T mp[N], S[NS], Sinv[NS];
+  predict<T, N, P, AM>(prm, m, V, mp, S);
+  sym_inv<T, N>(S, Sinv, ok);
+  T G[N][N], J[N][N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      if (AM == 0) {
+        G[i][j] = V[sym_idx<N>(i, j)] * prm.A[j];
+      } else {
+        T s = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) s += V[sym_idx<N>(i, k)] * prm.A[j * N + k];
+        G[i][j] = s;
+      }
+    }
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += G[i][k] * Sinv[sym_idx<N>(k, j)];
+      J[i][j] = s;
+    }
+  }
+  T d[N], D[NS], JDJ[NS];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) d[i] = ms1[i] - mp[i];
+  EKSB_UNROLL
+  for (int i = 0; i < NS; ++i) D[i] = Vs1[i] - S[i];
+  sandwich<T, N>(J, D, JDJ);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    T s = m[i];
+    EKSB_UNROLL
+    for (int k = 0; k < N; ++k) s += J[i][k] * d[k];
+    ms[i] = s;
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < NS; ++i) Vs[i] = V[i] + JDJ[i];
+  if (Jout) {
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) Jout[i][j] = J[i][j];
+    }
+  }
+}
+
+// Backward pass over `n` frames, last frame first.  (ms,Vs) carries the smoothed state
+// of the frame after this range in, and of the first frame of the range out; with
+// terminal set, the last frame of the range is the end of the track (ms=mf, Vs=Vf,
+// eks/ensemble_kalman.py:152-153).  smth may alias filt (in-place smoothing: a frame
+// is always read before it is overwritten).  Optional outputs, null to skip:
+//   ym (P rows)  = C ms                      (multiview_pca_smoother.py:745)
+//   yv (P rows)  = diag(C Vs C^T)            (:746, diagonal only)
+//   cv (N*N rows)= Vs[t+1] J^T  at frame t   (eks/ensemble_kalman.py:162; frame n-1 of a
+//                  terminal range is left untouched)
+template <typename T, int N, int P, int AM, int LS, int PF>
+EKSB_HD bool rts_backward_range(const Params<T, N, P, AM>& prm, const T* filt, T* smth, T* ym, T* yv, T* cv,
+                                long n, bool terminal, T* ms, T* Vs) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
+  bool ok = true;
+  T buf[PF][SG];
+  EKSB_UNROLL
+  for (int k = 0; k < PF; ++k) {
+    long f = n - 1 - k;
+    if (f < 0) f = 0;
+    EKSB_UNROLL
+    for (int r = 0; r < SG; ++r) buf[k][r] = filt[(f * SG + r) * LS];
+  }
+  for (long t = n - 1; t >= 0; t -= PF) {
+    EKSB_UNROLL
+    for (int k = 0; k < PF; ++k) {
+      if (t - k >= 0) {
+        T cur[SG];
+        EKSB_UNROLL
+        for (int r = 0; r < SG; ++r) cur[r] = buf[k][r];
+        long f = t - k - PF;
+        if (f < 0) f = 0;
+        EKSB_UNROLL
+        for (int r = 0; r < SG; ++r) buf[k][r] = filt[(f * SG + r) * LS];
+        const long tt = t - k;
+        if (terminal && tt == n - 1) {
+          EKSB_UNROLL
+          for (int i = 0; i < N; ++i) ms[i] = cur[i];
+          EKSB_UNROLL
+          for (int i = 0; i < NS; ++i) Vs[i] = cur[N + i];
+        } else {
+          T ms1[N], Vs1[NS], J[N][N];
+          EKSB_UNROLL
+          for (int i = 0; i < N; ++i) ms1[i] = ms[i];
+          EKSB_UNROLL
+          for (int i = 0; i < NS; ++i) Vs1[i] = Vs[i];
+          rts_step<T, N, P, AM>(prm, cur, cur + N, ms1, Vs1, ms, Vs, cv ? J : nullptr, ok);
+          if (cv) {
+            T* o = cv + tt * (N * N) * LS;
+            EKSB_UNROLL
+            for (int i = 0; i < N; ++i) {
+              EKSB_UNROLL
+              for (int j = 0; j < N; ++j) {
+                T s = T(0);
+                EKSB_UNROLL
+                for (int k2 = 0; k2 < N; ++k2) s += Vs1[sym_idx<N>(i, k2)] * J[j][k2];
+                o[(i * N + j) * LS] = s;
+              }
+            }
+          }
+        }
+        T* o = smth + tt * SG * LS;
+        EKSB_UNROLL
+        for (int i = 0; i < N; ++i) o[i * LS] = ms[i];
+        EKSB_UNROLL
+        for (int i = 0; i < NS; ++i) o[(N + i) * LS] = Vs[i];
+        if (ym || yv) {
+          EKSB_UNROLL
+          for (int j = 0; j < P; ++j) {
+            T s = T(0), q = T(0);
+            EKSB_UNROLL
+            for (int i = 0; i < N; ++i) {
+              s += prm.C[j][i] * ms[i];
+              T a = T(0);
+              EKSB_UNROLL
+              for (int k2 = 0; k2 < N; ++k2) a += Vs[sym_idx<N>(i, k2)] * prm.C[j][k2];
+              q += prm.C[j][i] * a;
+            }
+            if (ym) ym[(tt * P + j) * LS] = s;
+            if (yv) yv[(tt * P + j) * LS] = q;
+          }
+        }
+      }
+    }
+  }
+  return ok;
+}
+
+}  // namespace eksb

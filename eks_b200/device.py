@@ -1,0 +1,240 @@
+"""Device-resident (torch.Tensor) API over the libeksb C ABI.
+
+PyTorch is plumbing here: it owns device memory and streams; every computation is a
+hand-written sm_100a kernel in eks_b200/csrc reached through ctypes.  Tensors in the
+"track-tile" layout (include/eksb.h) are flat 1-D tensors of n_tiles*T*rows*32 scalars.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import LANES, check, lib
+
+
+def _sfx(dtype):
+    if dtype == torch.float64:
+        return "f64"
+    if dtype == torch.float32:
+        return "f32"
+    raise TypeError(f"eks_b200 computes in float32 or float64, got {dtype}")
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream(device):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _need_cuda(t, name):
+    if not t.is_cuda:
+        raise RuntimeError(f"eks_b200: '{name}' must be a CUDA tensor (there is no CPU path)")
+    if not t.is_contiguous():
+        raise RuntimeError(f"eks_b200: '{name}' must be contiguous")
+
+
+def num_tiles(B):
+    return (B + LANES - 1) // LANES
+
+
+def sigma(n):
+    return n + n * (n + 1) // 2
+
+
+def alloc_records(B, T, rows, dtype, device):
+    return torch.empty(num_tiles(B) * T * rows * LANES, dtype=dtype, device=device)
+
+
+@dataclass
+class TrackParams:
+    """Per-track (leading dim B) or shared (no leading dim) model matrices on the device.
+
+    Names follow eks/ensemble_kalman.py:59: m0 (n,), S0 (n,n), C (p,n), A (n,n), Q (n,n).
+    """
+    m0: torch.Tensor
+    S0: torch.Tensor
+    C: torch.Tensor
+    A: torch.Tensor
+    Q: torch.Tensor
+    a_mode: int = -1
+
+    def __post_init__(self):
+        self.p, self.n = int(self.C.shape[-2]), int(self.C.shape[-1])
+        mask = 0
+        for bit, t, nd in ((_lib.SHARED_M0, self.m0, 1), (_lib.SHARED_S0, self.S0, 2), (_lib.SHARED_C, self.C, 2),
+                           (_lib.SHARED_A, self.A, 2), (_lib.SHARED_Q, self.Q, 2)):
+            _need_cuda(t, "params")
+            if t.dim() == nd:
+                mask |= bit
+            elif t.dim() != nd + 1:
+                raise ValueError("parameter arrays must be (..) or (B, ..)")
+        self.shared_mask = mask
+        if self.a_mode < 0:
+            A = self.A
+            off = A - torch.diag_embed(torch.diagonal(A, dim1=-2, dim2=-1))
+            self.a_mode = _lib.A_DIAG if not bool((off != 0).any()) else _lib.A_DENSE
+
+    @property
+    def fast_path(self):
+        """True if (n,p) has a register-resident template instantiation."""
+        return bool(lib().eksb_supported_dims(self.n, self.p))
+
+    @property
+    def dtype(self):
+        return self.C.dtype
+
+    @classmethod
+    def from_numpy(cls, m0, S0, C, A, Q, dtype=torch.float64, device="cuda"):
+        f = lambda a: torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(device).contiguous()
+        A = np.asarray(A)
+        off = A - A * np.eye(A.shape[-1])
+        return cls(f(m0), f(S0), f(C), f(A), f(Q), a_mode=_lib.A_DIAG if not np.any(off != 0) else _lib.A_DENSE)
+
+
+# ------------------------------------------------------------------ layout
+def pack_rows(src, dst, rows, row0, pad=0.0):
+    """src (B,T,R) -> rows [row0,row0+R) of the track-tile buffer dst."""
+    _need_cuda(src, "src")
+    B, T, R = src.shape
+    fn = getattr(lib(), f"eksb_pack_rows_{_sfx(src.dtype)}")
+    check(fn(_ptr(src), B, T, R, _ptr(dst), rows, row0, pad, _stream(src.device)), "eksb_pack_rows")
+    return dst
+
+
+def unpack_rows(src, rows, row0, B, T, R):
+    """rows [row0,row0+R) of a track-tile buffer -> (B,T,R)."""
+    out = torch.empty((B, T, R), dtype=src.dtype, device=src.device)
+    fn = getattr(lib(), f"eksb_unpack_rows_{_sfx(src.dtype)}")
+    check(fn(_ptr(src), rows, row0, B, T, R, _ptr(out), _stream(src.device)), "eksb_unpack_rows")
+    return out
+
+
+def pack_obs(y, ev):
+    """y, ev (B,T,p) -> obs records (padding lanes: y=0, ev=1)."""
+    B, T, p = y.shape
+    obs = alloc_records(B, T, 2 * p, y.dtype, y.device)
+    pack_rows(y, obs, 2 * p, 0, 0.0)
+    pack_rows(ev, obs, 2 * p, p, 1.0)
+    return obs
+
+
+def expand_state(state, B, T, prm: TrackParams, want_pred=False):
+    """state records -> mean (B,T,n), cov (B,T,n,n) [, pred (B,T,n,n) = the reference's shifted S]."""
+    n = prm.n
+    mean = torch.empty((B, T, n), dtype=state.dtype, device=state.device)
+    cov = torch.empty((B, T, n, n), dtype=state.dtype, device=state.device)
+    pred = torch.empty((B, T, n, n), dtype=state.dtype, device=state.device) if want_pred else None
+    fn = getattr(lib(), f"eksb_expand_state_{_sfx(state.dtype)}")
+    check(fn(_ptr(state), B, T, n, _ptr(prm.A), _ptr(prm.Q), _ptr(prm.S0), prm.shared_mask, _ptr(mean), _ptr(cov),
+             _ptr(pred), _stream(state.device)), "eksb_expand_state")
+    return (mean, cov, pred) if want_pred else (mean, cov)
+
+
+def pack_state(mean, cov):
+    """dense mean (B,T,n), cov (B,T,n,n) -> state records."""
+    _need_cuda(mean, "mean"); _need_cuda(cov, "cov")
+    B, T, n = mean.shape
+    state = alloc_records(B, T, sigma(n), mean.dtype, mean.device)
+    fn = getattr(lib(), f"eksb_pack_state_{_sfx(mean.dtype)}")
+    check(fn(_ptr(mean), _ptr(cov), B, T, n, _ptr(state), _stream(mean.device)), "eksb_pack_state")
+    return state
+
+
+# ------------------------------------------------------------------ A1 ensemble
+def _mode(mode):
+    if mode == "median":
+        return _lib.MODE_MEDIAN
+    if mode == "mean":
+        return _lib.MODE_MEAN
+    raise ValueError(f"{mode} averaging not supported")      # eks/ensemble_kalman.py:39
+
+
+def ensemble(preds, mode="median"):
+    """preds (M,T,K) -> (avg (T,K), var (T,K)); eks/ensemble_kalman.py:45-46."""
+    md = _mode(mode)
+    _need_cuda(preds, "preds")
+    M, T, K = preds.shape
+    avg = torch.empty((T, K), dtype=preds.dtype, device=preds.device)
+    var = torch.empty_like(avg)
+    fn = getattr(lib(), f"eksb_ensemble_{_sfx(preds.dtype)}")
+    check(fn(_ptr(preds), M, T, K, md, _ptr(avg), _ptr(var), _stream(preds.device)), "eksb_ensemble")
+    return avg, var
+
+
+def ensemble_tiled(preds, B, p, mode="median", offset=None, out=None):
+    """preds (M,T,B*p) -> obs records, y = avg - offset (offset (B,p) or None)."""
+    md = _mode(mode)
+    _need_cuda(preds, "preds")
+    M, T, K = preds.shape
+    if K != B * p:
+        raise ValueError("preds last dim must be B*p")
+    obs = out if out is not None else alloc_records(B, T, 2 * p, preds.dtype, preds.device)
+    fn = getattr(lib(), f"eksb_ensemble_tiled_{_sfx(preds.dtype)}")
+    check(fn(_ptr(preds), M, T, B, p, md, _ptr(offset), _ptr(obs), _stream(preds.device)), "eksb_ensemble_tiled")
+    return obs
+
+
+# ------------------------------------------------------------------ A2 / A6 forward
+def kf_forward(obs, prm: TrackParams, B, T, first=_lib.FIRST_PRIOR_UPDATE, q_scale=None, want_filt=True,
+               want_nll=False, filt=None, status=None):
+    """Forward filter.  Returns (filt or None, nll (n_scale,B) float64 or None, status (B,) int32)."""
+    _need_cuda(obs, "obs")
+    dev, dt = obs.device, obs.dtype
+    if prm.dtype != dt:
+        raise TypeError("obs and params dtypes differ")
+    n_scale = 0 if q_scale is None else int(q_scale.numel())
+    if want_filt and filt is None:
+        filt = alloc_records(B, T, sigma(prm.n), dt, dev)
+    if not want_filt:
+        filt = None
+    nll = torch.empty((max(n_scale, 1), B), dtype=torch.float64, device=dev) if want_nll else None
+    if status is None:
+        status = torch.zeros(B, dtype=torch.int32, device=dev)
+    fn = getattr(lib(), f"eksb_kf_forward_{_sfx(dt)}")
+    check(fn(_ptr(obs), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), prm.shared_mask, B, T,
+             prm.n, prm.p, prm.a_mode, first, _ptr(q_scale), n_scale, _ptr(filt), _ptr(nll), _ptr(status),
+             _stream(dev)), "eksb_kf_forward")
+    return filt, nll, status
+
+
+def kf_forward_generic(obs, prm: TrackParams, B, T, R=None, first=_lib.FIRST_PRIOR_UPDATE, status=None):
+    """Literal-arithmetic forward filter (dense R (p,p)/(B,p,p), any n<=8, p<=16).  Returns (filt, status)."""
+    _need_cuda(obs, "obs")
+    dev, dt = obs.device, obs.dtype
+    filt = alloc_records(B, T, sigma(prm.n), dt, dev)
+    if status is None:
+        status = torch.zeros(B, dtype=torch.int32, device=dev)
+    r_shared = 1 if (R is None or R.dim() == 2) else 0
+    fn = getattr(lib(), f"eksb_kf_forward_generic_{_sfx(dt)}")
+    check(fn(_ptr(obs), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), _ptr(R), r_shared,
+             prm.shared_mask, B, T, prm.n, prm.p, first, _ptr(filt), _ptr(status), _stream(dev)),
+          "eksb_kf_forward_generic")
+    return filt, status
+
+
+# ------------------------------------------------------------------ A4 / A5 backward
+def rts_backward(filt, prm: TrackParams, B, T, inplace=False, want_ym=True, want_yv=False, want_cv=False,
+                 smth=None, ym=None, status=None):
+    """RTS pass.  Returns dict(smth, ym, yv, cv, status); smth is filt itself when inplace."""
+    _need_cuda(filt, "filt")
+    dev, dt = filt.device, filt.dtype
+    n, p = prm.n, prm.p
+    if smth is None:
+        smth = filt if inplace else torch.empty_like(filt)
+    if want_ym and ym is None:
+        ym = alloc_records(B, T, p, dt, dev)
+    if not want_ym:
+        ym = None
+    yv = alloc_records(B, T, p, dt, dev) if want_yv else None
+    cv = alloc_records(B, T, n * n, dt, dev).zero_() if want_cv else None
+    if status is None:
+        status = torch.zeros(B, dtype=torch.int32, device=dev)
+    fn = getattr(lib(), f"eksb_rts_backward_{_sfx(dt)}")
+    check(fn(_ptr(filt), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), prm.shared_mask, B, T, n, p, prm.a_mode, _ptr(smth),
+             _ptr(ym), _ptr(yv), _ptr(cv), _ptr(status), _stream(dev)), "eksb_rts_backward")
+    return dict(smth=smth, ym=ym, yv=yv, cv=cv, status=status)

@@ -1,0 +1,173 @@
+/* eksb.h -- C ABI of libeksb.so, the sm_100a (B200) implementation of the EKS hot path.
+ *
+ * The reference (erialc-cal/eks) is pure Python/numpy and has no FFI; its boundary for
+ * this path is four module-level functions plus the Newton variants.  Each entry point
+ * below names the reference function (file:line, relative to the reference checkout)
+ * whose arithmetic it replaces.  The Python package eks_b200 binds these with ctypes
+ * (eks_b200/_lib.py) and re-exports the reference's own names and signatures;
+ * INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *  - Every pointer is a DEVICE pointer unless the name ends in _host.  The caller owns all
+ *    buffers; the library never allocates.  `stream` is a cudaStream_t passed as void*.
+ *  - All calls are asynchronous on `stream` and return 0, or a negative EKSB_E* code
+ *    (message via eksb_last_error_string()).  Numerical trouble inside a track (a
+ *    non-positive pivot: the reference would raise numpy.linalg.LinAlgError) is reported
+ *    per track through the optional `status` array (0 ok, 1 = non-positive pivot seen).
+ *  - _f32 / _f64 suffix = arithmetic and storage type of every non-integer buffer.
+ *  - "Track-tile" layout (all per-frame device arrays): tracks are grouped in tiles of
+ *    EKSB_LANES = 32; a frame record has ROWS scalars per track;
+ *        index(tile g, frame t, row r, lane l) = ((g*T + t)*ROWS + r)*32 + l ,  track b = 32 g + l
+ *    so warp lane == track and every warp access is one full contiguous line.
+ *    n_tiles = eksb_num_tiles(B) = ceil(B/32); buffers hold n_tiles*T*ROWS*32 scalars.
+ *      obs   record: ROWS = 2p : rows [0,p) = y (ensemble mean/median, centred), [p,2p) = ensemble variance
+ *      state record: ROWS = n + n(n+1)/2 : rows [0,n) = mean, then the covariance packed
+ *                    upper-triangular row-major ((0,0),(0,1),..,(0,n-1),(1,1),..)
+ *  - Per-track parameters are dense row-major arrays with a leading track dimension,
+ *    m0 (B,n)  S0 (B,n,n)  C (B,p,n)  A (B,n,n)  Q (B,n,n); a bit set in `shared_mask`
+ *    (EKSB_SHARED_*) means that array has no track dimension and is shared by all tracks.
+ *  - Supported (n,p): (2,4) (3,4) (3,6) (3,8) (4,6) (6,8); anything else -> EKSB_EDIM.
+ *  - a_mode: EKSB_A_DIAG if every A is diagonal (identity included; every shipped config),
+ *    else EKSB_A_DENSE.  R is diag(ensemble variance): the reference overwrites diag(R) each
+ *    frame (eks/ensemble_kalman.py:88-89,99-100) and every caller passes R = I, so
+ *    off-diagonals are zero.
+ */
+#ifndef EKSB_H_
+#define EKSB_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define EKSB_API __attribute__((visibility("default")))
+#else
+#define EKSB_API
+#endif
+
+#define EKSB_LANES 32
+
+#define EKSB_OK 0
+#define EKSB_EDIM (-1)    /* unsupported (n,p) or M */
+#define EKSB_EARG (-2)    /* bad argument (null pointer, non-positive size, bad mode) */
+#define EKSB_ECUDA (-3)   /* CUDA runtime error; see eksb_last_error_string() */
+
+#define EKSB_SHARED_M0 1
+#define EKSB_SHARED_S0 2
+#define EKSB_SHARED_C 4
+#define EKSB_SHARED_A 8
+#define EKSB_SHARED_Q 16
+#define EKSB_SHARED_ALL 31
+
+#define EKSB_A_DIAG 0
+#define EKSB_A_DENSE 1
+
+#define EKSB_MODE_MEDIAN 0
+#define EKSB_MODE_MEAN 1
+
+/* first-frame behaviour of the forward recursion */
+#define EKSB_FIRST_PRIOR_UPDATE 1 /* filtering_pass: frame 0 = update from (m0,S0), no predict (eks/ensemble_kalman.py:94-96) */
+#define EKSB_FIRST_PRIOR_ONLY 2   /* kalman_newton_recursive: q[0]=mu0, P=inv(S0), y[0] unused (eks/newton_eks.py:128,132) */
+
+EKSB_API int eksb_version(void);
+EKSB_API const char* eksb_last_error_string(void);
+EKSB_API long eksb_num_tiles(long B);
+EKSB_API int eksb_supported_dims(int n, int p); /* 1 if (n,p) is instantiated */
+
+/* ---- A1: ensemble()  eks/ensemble_kalman.py:4-57 -------------------------------------
+ * preds is the raw prediction tensor [M][T][K] (models x frames x keypoint columns, K fastest).
+ * avg = median or mean over models (:45), var = population variance / M (:46).  Medians and
+ * means are bit-exact w.r.t. numpy (same summation order, no FMA contraction); NaN propagates.
+ * 1 <= M <= 16. */
+EKSB_API int eksb_ensemble_f64(const double* preds, int M, long T, long K, int mode, double* avg, double* var, void* stream);
+EKSB_API int eksb_ensemble_f32(const float* preds, int M, long T, long K, int mode, float* avg, float* var, void* stream);
+
+/* Same reduction, fused with the multi-view restack (multiview_pca_smoother.py:645-682):
+ * column k = b*p + j of preds is observation j of track b; writes the obs record (track-tile
+ * layout) directly: y = avg - offset[b][j] (offset (B,p), may be null), ev = var.
+ * Padding lanes of the last tile get y = 0, ev = 1. */
+EKSB_API int eksb_ensemble_tiled_f64(const double* preds, int M, long T, long B, int p, int mode, const double* offset,
+                            double* obs, void* stream);
+EKSB_API int eksb_ensemble_tiled_f32(const float* preds, int M, long T, long B, int p, int mode, const float* offset,
+                            float* obs, void* stream);
+
+/* ---- layout conversion ------------------------------------------------------------------
+ * pack:   src (B,T,R) row-major -> rows [row0,row0+R) of a track-tile buffer with `rows` rows
+ *         per record; padding lanes are filled with `pad`.
+ * unpack: the inverse (padding lanes dropped). */
+EKSB_API int eksb_pack_rows_f64(const double* src, long B, long T, int R, double* dst, int rows, int row0, double pad, void* stream);
+EKSB_API int eksb_pack_rows_f32(const float* src, long B, long T, int R, float* dst, int rows, int row0, float pad, void* stream);
+EKSB_API int eksb_unpack_rows_f64(const double* src, int rows, int row0, long B, long T, int R, double* dst, void* stream);
+EKSB_API int eksb_unpack_rows_f32(const float* src, int rows, int row0, long B, long T, int R, float* dst, void* stream);
+
+/* Expand a state record buffer into the reference's dense return values
+ * (eks/ensemble_kalman.py:91-93,107): mean (B,T,n), cov (B,T,n,n) and, if pred != NULL,
+ * pred (B,T,n,n) with pred[t] = A cov[t] A^T + Q for t < T-1 and pred[T-1] = 0 (the
+ * reference's shifted `S`; for T == 1 pred[0] = S0).  A/Q/S0 follow shared_mask. */
+EKSB_API int eksb_expand_state_f64(const double* state, long B, long T, int n, const double* A, const double* Q, const double* S0,
+                          int shared_mask, double* mean, double* cov, double* pred, void* stream);
+EKSB_API int eksb_expand_state_f32(const float* state, long B, long T, int n, const float* A, const float* Q, const float* S0,
+                          int shared_mask, float* mean, float* cov, float* pred, void* stream);
+/* The inverse for callers that hold dense mf (B,T,n) / Vf (B,T,n,n) (smooth_backward's inputs). */
+EKSB_API int eksb_pack_state_f64(const double* mean, const double* cov, long B, long T, int n, double* state, void* stream);
+EKSB_API int eksb_pack_state_f32(const float* mean, const float* cov, long B, long T, int n, float* state, void* stream);
+
+/* ---- A2/A3: filtering_pass() + kalman_dot()  eks/ensemble_kalman.py:59-117 -------------
+ * Forward Kalman filter over all B tracks, one track per thread, whole state in registers.
+ * The measurement update is done in information form (n x n inverses; algebraically the
+ * update of :104-105).  Outputs, each optional (NULL to skip):
+ *   filt   state records (mf, Vf)                               [n_tiles][T][n+n(n+1)/2][32]
+ *   nll    (n_scale, B) doubles: 0.5*sum_t[log det Sig_t + nu^T Sig_t^-1 nu + p log 2pi],
+ *          Sig_t = R_t + C S_pred C^T (:112), nu_t the innovation of :102
+ *   status (B) ints
+ * q_scale (device, n_scale values) evaluates the pass once per smoothing-parameter candidate
+ * with Q replaced by q_scale[g]*Q (grid search over `s`, multiview_pca_smoother.py:728);
+ * pass NULL / 0 for a single evaluation with Q as given.  filt must be NULL if n_scale > 1.
+ * first = EKSB_FIRST_PRIOR_UPDATE for filtering_pass; EKSB_FIRST_PRIOR_ONLY turns the same
+ * recursion into kalman_newton_recursive (A6, eks/newton_eks.py:115-148: B=C, E=Q, q = mean rows). */
+EKSB_API int eksb_kf_forward_f64(const double* obs, const double* m0, const double* S0, const double* C, const double* A,
+                        const double* Q, int shared_mask, long B, long T, int n, int p, int a_mode, int first,
+                        const double* q_scale, int n_scale, double* filt, double* nll, int* status, void* stream);
+EKSB_API int eksb_kf_forward_f32(const float* obs, const float* m0, const float* S0, const float* C, const float* A,
+                        const float* Q, int shared_mask, long B, long T, int n, int p, int a_mode, int first,
+                        const float* q_scale, int n_scale, float* filt, double* nll, int* status, void* stream);
+
+/* ---- A4/A5: smooth_backward() + back-projection  eks/ensemble_kalman.py:120-164 --------
+ * RTS pass over state records written by eksb_kf_forward.  S = A Vf A^T + Q is recomputed
+ * per frame instead of being read back (:101,:158).  smth may equal filt (in-place).
+ * Optional outputs (NULL to skip), all track-tile layout:
+ *   ym (p rows)   C ms                       (multiview_pca_smoother.py:745, pupil_smoother.py:190)
+ *   yv (p rows)   diag(C Vs C^T)             (:746)
+ *   cv (n*n rows) CV[t] = Vs[t+1] J^T, frames 0..T-2 (:162); frame T-1 is not written */
+EKSB_API int eksb_rts_backward_f64(const double* filt, const double* C, const double* A, const double* Q, int shared_mask,
+                          long B, long T, int n, int p, int a_mode, double* smth, double* ym, double* yv, double* cv,
+                          int* status, void* stream);
+EKSB_API int eksb_rts_backward_f32(const float* filt, const float* C, const float* A, const float* Q, int shared_mask,
+                          long B, long T, int n, int p, int a_mode, float* smth, float* ym, float* yv, float* cv,
+                          int* status, void* stream);
+
+/* ---- generic (runtime-dimension) kernels: literal reference arithmetic ------------------
+ * kalman_dot: out (n,k) = V C^T (R + C V C^T)^-1 array, array (p,k), via a p x p LU solve with
+ * partial pivoting (eks/ensemble_kalman.py:110-117; numpy.linalg.solve -> LAPACK gesv).
+ * n <= 8, p <= 16, k <= 8.  *status = 1 on an exactly singular matrix (LinAlgError). */
+EKSB_API int eksb_kalman_dot_f64(const double* array, int k, const double* V, const double* C, const double* R, int n, int p,
+                        double* out, int* status, void* stream);
+EKSB_API int eksb_kalman_dot_f32(const float* array, int k, const float* V, const float* C, const float* R, int n, int p,
+                        float* out, int* status, void* stream);
+/* filtering_pass with a dense R (B,p,p) or shared (p,p) [r_shared=1] whose off-diagonals take
+ * part unchanged (eks/ensemble_kalman.py:112) and/or an (n,p) pair that is not instantiated
+ * (n <= 8, p <= 16).  R == NULL means identity off-diagonals.  Same obs / state records. */
+EKSB_API int eksb_kf_forward_generic_f64(const double* obs, const double* m0, const double* S0, const double* C, const double* A,
+                                const double* Q, const double* R, int r_shared, int shared_mask, long B, long T, int n,
+                                int p, int first, double* filt, int* status, void* stream);
+EKSB_API int eksb_kf_forward_generic_f32(const float* obs, const float* m0, const float* S0, const float* C, const float* A,
+                                const float* Q, const float* R, int r_shared, int shared_mask, long B, long T, int n,
+                                int p, int first, float* filt, int* status, void* stream);
+
+/* EKSB_DECLS_END (new declarations go above this line) */
+#ifdef __cplusplus
+}
+#endif
+#endif /* EKSB_H_ */

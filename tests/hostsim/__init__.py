@@ -1,0 +1,74 @@
+"""ctypes access to the host build of the kernel math (test infrastructure only)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(HERE, "libhostsim.so")
+
+
+def build(force=False):
+    srcs = [os.path.join(HERE, "hostsim.cpp"),
+            os.path.join(HERE, "../../eks_b200/csrc/eksb_math.cuh"),
+            os.path.join(HERE, "../../eks_b200/csrc/eksb_dims.h")]
+    if force or not os.path.exists(LIB) or any(os.path.getmtime(s) > os.path.getmtime(LIB) for s in srcs):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-ffp-contract=off",
+                               "-x", "c++", srcs[0], "-o", LIB])
+    return ctypes.CDLL(LIB)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = build()
+    return _lib
+
+
+def sym_unpack(packed, n):
+    """(T, n(n+1)/2) packed upper-triangular rows -> (T,n,n)."""
+    T = packed.shape[0]
+    out = np.zeros((T, n, n), dtype=packed.dtype)
+    k = 0
+    for i in range(n):
+        for j in range(i, n):
+            out[:, i, j] = packed[:, k]
+            out[:, j, i] = packed[:, k]
+            k += 1
+    return out
+
+
+def a_mode(A):
+    return 0 if np.count_nonzero(A - np.diag(np.diagonal(A))) == 0 else 1
+
+
+def kf_rts(y, ev, m0, S0, C, A, Q, dtype=np.float64, first=1, smooth=True, want_cv=True):
+    """Run the host build of kf_forward_range + rts_backward_range on one track."""
+    T, p = y.shape
+    n = m0.shape[0]
+    c = lambda a: np.ascontiguousarray(a, dtype=dtype)
+    am = a_mode(A)
+    y, ev, m0, S0, C, A, Q = map(c, (y, ev, m0, S0, C, A, Q))
+    sg = n + n * (n + 1) // 2
+    filt = np.zeros((T, sg), dtype=dtype)
+    smth = np.zeros((T, sg), dtype=dtype)
+    ym = np.zeros((T, p), dtype=dtype)
+    yv = np.zeros((T, p), dtype=dtype)
+    cv = np.zeros((T, n * n), dtype=dtype)
+    nll = ctypes.c_double(0.0)
+    fn = lib().hs_kf_rts_f64 if dtype == np.float64 else lib().hs_kf_rts_f32
+    P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    null = ctypes.c_void_p(0)
+    rc = fn(ctypes.c_int(n), ctypes.c_int(p), ctypes.c_int(am), ctypes.c_long(T), P(y), P(ev), P(m0), P(S0), P(C),
+            P(A), P(Q), ctypes.c_int(first), P(filt), P(smth) if smooth else null, P(ym), P(yv),
+            P(cv) if want_cv else null, ctypes.byref(nll))
+    if rc < 0:
+        raise ValueError(f"unsupported dims n={n} p={p}")
+    out = dict(rc=rc, mf=filt[:, :n], Vf=sym_unpack(filt[:, n:], n), nll_terms=nll.value)
+    if smooth:
+        out.update(ms=smth[:, :n], Vs=sym_unpack(smth[:, n:], n), ym=ym, yv=yv, CV=cv.reshape(T, n, n)[:T - 1])
+    return out
