@@ -19,7 +19,20 @@ inline int check_launch(const char* what) {
   return EKSB_OK;
 }
 
-inline long num_tiles(long B) { return (B + kLanes - 1) / kLanes; }
+__host__ __device__ inline long num_tiles(long B) { return (B + kLanes - 1) / kLanes; }
+__device__ __forceinline__ long num_tiles_dev(long B) { return (B + kLanes - 1) / kLanes; }
+
+// Warp-specialised (pipelined) variants, defined in eksb_pipe_*.cu.  Return EKSB_EDIM when the
+// (n,p) pair has no pipelined instantiation (the caller then uses the plain kernel).
+template <typename T>
+int kf_forward_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B,
+                    long Tn, int n, int p, int a_mode, int first, T* filt, int* status, cudaStream_t st);
+template <typename T>
+int rts_backward_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, int n, int p,
+                      int a_mode, T* smth, T* ym, T* yv, int* status, cudaStream_t st);
+// Policy: use the pipelined kernels when the batch is too small to hide instruction latency
+// with plain thread-per-track occupancy.  EKSB_PIPE=0 disables, EKSB_PIPE_MAX_TILES overrides.
+bool use_pipe(long B);
 
 // Device-side gather of one track's parameters into registers.
 template <typename T, int N, int P, int AM>

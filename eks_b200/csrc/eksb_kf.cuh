@@ -85,6 +85,10 @@ template <typename T, int N, int P>
 static int launch_forward(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                           long B, long Tn, int a_mode, int first, const T* q_scale, int n_scale, T* filt, double* nll,
                           int* status, cudaStream_t st) {
+  if (filt && !nll && !q_scale && use_pipe(B)) {           // latency-bound regime: warp-specialised kernel
+    int rc = kf_forward_pipe<T>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, N, P, a_mode, first, filt, status, st);
+    if (rc != EKSB_EDIM) return rc;
+  }
   dim3 grid((unsigned)num_tiles(B), (unsigned)(q_scale ? n_scale : 1));
 #define EKSB_GO(AM_, NLL_)                                                                                      \
   kf_forward_kernel<T, N, P, AM_, NLL_><<<grid, kLanes, 0, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, \
@@ -98,6 +102,10 @@ static int launch_forward(const T* obs, const T* m0, const T* S0, const T* C, co
 template <typename T, int N, int P>
 static int launch_backward(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
                            int a_mode, T* smth, T* ym, T* yv, T* cv, int* status, cudaStream_t st) {
+  if (!cv && use_pipe(B)) {
+    int rc = rts_backward_pipe<T>(filt, C, A, Q, shared_mask, B, Tn, N, P, a_mode, smth, ym, yv, status, st);
+    if (rc != EKSB_EDIM) return rc;
+  }
   unsigned grid = (unsigned)num_tiles(B);
   if (a_mode == EKSB_A_DIAG)
     rts_backward_kernel<T, N, P, 0><<<grid, kLanes, 0, st>>>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, cv, status);

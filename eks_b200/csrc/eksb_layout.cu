@@ -1,6 +1,7 @@
 // eksb_layout.cu -- library housekeeping and the layout kernels: (B,T,R) <-> track-tile
 // transposes and the dense expansion of state records into the reference's return values.
 #include <stdarg.h>
+#include <stdlib.h>
 #include "eksb_common.cuh"
 
 namespace eksb {
@@ -12,6 +13,18 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+
+bool use_pipe(long B) {
+  static int enabled = -1;
+  static long max_tiles = 0;
+  if (enabled < 0) {
+    const char* e = getenv("EKSB_PIPE");
+    const char* m = getenv("EKSB_PIPE_MAX_TILES");
+    max_tiles = m ? atol(m) : 1536;      // ~10 tiles per SM; beyond that plain occupancy hides latency
+    enabled = (e && e[0] == '0') ? 0 : 1;
+  }
+  return enabled && num_tiles(B) <= max_tiles;
 }
 
 constexpr int kFT = 16;   // frames per transpose tile

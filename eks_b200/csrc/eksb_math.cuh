@@ -30,7 +30,32 @@ template <int N> EKSB_HD constexpr int sym_idx(int i, int j) {
   return (i <= j) ? (i * N - i * (i - 1) / 2 + (j - i)) : (j * N - j * (j - 1) / 2 + (i - j));
 }
 
-template <typename T> EKSB_HD T rcp(T x) { return T(1) / x; }
+// Reciprocal.  Device: MUFU approximation + Newton steps (no IEEE-division slow path, which
+// costs a CALL and ~50 serialised cycles on the recursion's critical path); relative error
+// <= ~1 ulp for normal inputs, 0/inf/NaN propagate like 1/x.  Host (tests): plain 1/x.
+EKSB_HD float rcp(float x) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  float e = fmaf(-x, r, 1.0f);
+  return (e == e) ? fmaf(r, e, r) : r;       // skip the refinement when x*r is NaN (x = 0 or inf)
+#else
+  return 1.0f / x;
+#endif
+}
+EKSB_HD double rcp(double x) {
+#if defined(__CUDA_ARCH__)
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  double r2 = fma(r, e, r);
+  return (e == e) ? r2 : r;
+#else
+  return 1.0 / x;
+#endif
+}
 
 // ---------------------------------------------------------------------------
 // SPD inverse of a packed symmetric matrix.  Returns det(a) (used by the NLL).
@@ -265,7 +290,7 @@ EKSB_HD double update(const Params<T, N, P, AM>& prm, const T* y, const T* r, co
   T Sinv[NS], Lam[NS];
   T detS = sym_inv<T, N>(S, Sinv, ok);
   EKSB_UNROLL
-  for (int k = 0; k < NS; ++k) Lam[k] = Sinv[k];
+  for (int k = 0; k < NS; ++k) Lam[k] = T(0);   // C^T R^-1 C is accumulated apart from S^-1 (state-independent)
   T u[N];
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) u[i] = T(0);
@@ -281,6 +306,8 @@ EKSB_HD double update(const Params<T, N, P, AM>& prm, const T* y, const T* r, co
       for (int k = i; k < N; ++k) Lam[sym_idx<N>(i, k)] += cw[i] * prm.C[j][k];
     }
   }
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) Lam[k] += Sinv[k];
   T detL = sym_inv<T, N>(Lam, V, ok);
   T Vu[N];
   sym_matvec<T, N>(V, u, Vu);
@@ -509,6 +536,139 @@ EKSB_HD bool rts_backward_range(const Params<T, N, P, AM>& prm, const T* filt, T
     }
   }
   return ok;
+}
+
+// ---------------------------------------------------------------------------
+// Producer / consumer split of the two recursions (used by the warp-specialised kernels,
+// eksb_pipe.cuh).  Everything that does not depend on the running state is done by helper
+// warps ("prep"), so the single warp that carries the sequential dependency ("chain") only
+// executes the short critical path.
+//   forward  prep : obs frame (y, r) -> info record  [ I = C^T R^-1 C (NS) | iv = C^T R^-1 y (N) ]
+//   forward  chain: S = A V A^T + Q; V = (S^-1 + I)^-1; m = mp + V (iv - I mp)
+//   backward prep : filtered (m, V)  -> smoothing element [ J (N*N) | L = V - J A V (NS) | g = m - J A m (N) ]
+//                   with J = V A^T (A V A^T + Q)^-1   (eks/ensemble_kalman.py:158; the (E,g,L)
+//                   element of Sarkka & Garcia-Fernandez 2021)
+//   backward chain: ms = g + J ms1 ; Vs = L + J Vs1 J^T      (== :160-161)
+// ---------------------------------------------------------------------------
+template <int N> struct Rec {
+  static constexpr int FWD = Dim<N>::NS + N;
+  static constexpr int BWD = N * N + Dim<N>::NS + N;
+};
+
+template <typename T, int N, int P, int AM>
+EKSB_HD void fwd_prep(const Params<T, N, P, AM>& prm, const T* y, const T* r, T* rec) {
+  constexpr int NS = Dim<N>::NS;
+  EKSB_UNROLL
+  for (int k = 0; k < NS + N; ++k) rec[k] = T(0);
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) {
+    const T w = rcp(r[j]);
+    T cw[N];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) cw[i] = prm.C[j][i] * w;
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      rec[NS + i] += cw[i] * y[j];
+      EKSB_UNROLL
+      for (int k = i; k < N; ++k) rec[sym_idx<N>(i, k)] += cw[i] * prm.C[j][k];
+    }
+  }
+}
+
+template <typename T, int N, int P, int AM>
+EKSB_HD void fwd_chain(const Params<T, N, P, AM>& prm, const T* rec, bool do_predict, T* m, T* V, bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T mp[N], S[NS], Sinv[NS], Lam[NS], u[N], Vu[N];
+  if (do_predict) {
+    predict<T, N, P, AM>(prm, m, V, mp, S);
+  } else {
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) mp[i] = m[i];
+    EKSB_UNROLL
+    for (int i = 0; i < NS; ++i) S[i] = V[i];
+  }
+  sym_matvec<T, N>(rec, mp, u);                   // I mp  (off the covariance chain)
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
+  sym_inv<T, N>(S, Sinv, ok);
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) Lam[k] = Sinv[k] + rec[k];
+  sym_inv<T, N>(Lam, V, ok);
+  sym_matvec<T, N>(V, u, Vu);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) m[i] = mp[i] + Vu[i];
+}
+
+template <typename T, int N, int P, int AM>
+EKSB_HD void bwd_prep(const Params<T, N, P, AM>& prm, const T* m, const T* V, T* rec, bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T mp[N], S[NS], Sinv[NS];
+  predict<T, N, P, AM>(prm, m, V, mp, S);
+  sym_inv<T, N>(S, Sinv, ok);
+  T G[N][N], J[N][N];                             // G = V A^T
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      if (AM == 0) {
+        G[i][j] = V[sym_idx<N>(i, j)] * prm.A[j];
+      } else {
+        T s = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) s += V[sym_idx<N>(i, k)] * prm.A[j * N + k];
+        G[i][j] = s;
+      }
+    }
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += G[i][k] * Sinv[sym_idx<N>(k, j)];
+      J[i][j] = s;
+      rec[i * N + j] = s;
+    }
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = i; j < N; ++j) {                 // L = V - J (A V),  (A V)_{kj} = G[j][k]
+      T s = V[sym_idx<N>(i, j)];
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s -= J[i][k] * G[j][k];
+      rec[N * N + sym_idx<N>(i, j)] = s;
+    }
+    T gi = m[i];
+    EKSB_UNROLL
+    for (int k = 0; k < N; ++k) gi -= J[i][k] * mp[k];
+    rec[N * N + NS + i] = gi;
+  }
+}
+
+template <typename T, int N>
+EKSB_HD void bwd_chain(const T* rec, T* ms, T* Vs) {
+  constexpr int NS = Dim<N>::NS;
+  T J[N][N], ms1[N], Vs1[NS], JVJ[NS];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    ms1[i] = ms[i];
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) J[i][j] = rec[i * N + j];
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < NS; ++i) Vs1[i] = Vs[i];
+  sandwich<T, N>(J, Vs1, JVJ);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    T s = rec[N * N + NS + i];
+    EKSB_UNROLL
+    for (int k = 0; k < N; ++k) s += J[i][k] * ms1[k];
+    ms[i] = s;
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < NS; ++i) Vs[i] = rec[N * N + i] + JVJ[i];
 }
 
 }  // namespace eksb

@@ -1,0 +1,96 @@
+// eksb_pipe_impl.cuh -- launch configuration + dispatch for the warp-specialised kernels.
+#pragma once
+#include "eksb_pipe.cuh"
+
+namespace eksb {
+
+constexpr int kSmemBudget = 110 * 1024;   // per CTA, so that at least two CTAs fit the 227 KB of an SM
+
+template <typename T, int ROWS> struct HelperRing {      // helper prefetch ring: ~64 32-bit registers
+  static constexpr int kRegs = ROWS * (int)(sizeof(T) / 4);
+  static constexpr int raw = 64 / kRegs;
+  static constexpr int value = raw < 1 ? 1 : (raw > 8 ? 8 : raw);
+};
+
+#ifndef EKSB_PIPE_TPC
+#define EKSB_PIPE_TPC 4
+#endif
+
+template <typename T, int N, int P, int H, int ROWS_IN, int REC> struct AutoCfg {
+  static constexpr int PFH0 = HelperRing<T, ROWS_IN>::value;
+  // frames per hand-off batch: 8, or 4 when 8 would need more than ~40 KB of ring per tile
+  static constexpr int FT = ((size_t)2 * 8 * REC * kLanes * sizeof(T) <= 40 * 1024) ? 8 : 4;
+  static constexpr int PFH = (H * PFH0 > FT) ? (FT / H) : PFH0;
+  static constexpr int ROUNDS = (FT + H * PFH - 1) / (H * PFH);
+  static constexpr int F = H * PFH * ROUNDS;
+  static constexpr size_t kTileSmem = (size_t)2 * F * REC * kLanes * sizeof(T);
+  static constexpr int TPC0 = (int)(kSmemBudget / kTileSmem);
+  static constexpr int TPC = TPC0 > EKSB_PIPE_TPC ? EKSB_PIPE_TPC : TPC0;
+  static constexpr bool ok = TPC >= 1 && PFH >= 1;
+  using type = PipeCfg<N, P, H, (PFH >= 1 ? PFH : 1), ROUNDS, (TPC >= 1 ? TPC : 1)>;
+};
+
+constexpr int kFwdHelpers = 1, kBwdHelpers = 2;
+
+template <typename T, int N, int P, int AM>
+static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
+                           long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
+  using Auto = AutoCfg<T, N, P, kFwdHelpers, 2 * P, Rec<N>::FWD>;
+  if (!Auto::ok) return EKSB_EDIM;
+  using Cfg = typename Auto::type;
+  auto kern = kf_forward_pipe_kernel<T, N, P, AM, Cfg>;
+  const size_t smem = Auto::kTileSmem * Cfg::TPC;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const unsigned grid = (unsigned)((num_tiles(B) + Cfg::TPC - 1) / Cfg::TPC);
+  kern<<<grid, Cfg::THREADS, smem, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status);
+  return check_launch("kf_forward_pipe_kernel");
+}
+
+template <typename T, int N, int P, int AM>
+static int launch_bwd_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, T* smth,
+                           T* ym, T* yv, int* status, cudaStream_t st) {
+  using Auto = AutoCfg<T, N, P, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD>;
+  if (!Auto::ok) return EKSB_EDIM;
+  using Cfg = typename Auto::type;
+  auto kern = rts_backward_pipe_kernel<T, N, P, AM, Cfg>;
+  const size_t smem = Auto::kTileSmem * Cfg::TPC;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const unsigned grid = (unsigned)((num_tiles(B) + Cfg::TPC - 1) / Cfg::TPC);
+  kern<<<grid, Cfg::THREADS, smem, st>>>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status);
+  return check_launch("rts_backward_pipe_kernel");
+}
+
+// pipelined instantiations: state dim <= 4 (larger records do not fit the shared-memory ring)
+#define EKSB_FOR_EACH_PIPE_DIM(X) X(2, 4) X(3, 4) X(3, 6) X(3, 8) X(4, 6)
+
+#ifdef EKSB_PIPE_FWD
+template <typename T>
+int kf_forward_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B,
+                    long Tn, int n, int p, int a_mode, int first, T* filt, int* status, cudaStream_t st) {
+#define X(N_, P_)                                                                                                      \
+  if (n == N_ && p == P_)                                                                                              \
+    return a_mode == EKSB_A_DIAG                                                                                       \
+               ? launch_fwd_pipe<T, N_, P_, 0>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, st)      \
+               : launch_fwd_pipe<T, N_, P_, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, st);
+  EKSB_FOR_EACH_PIPE_DIM(X)
+#undef X
+  return EKSB_EDIM;
+}
+#endif
+
+#ifdef EKSB_PIPE_BWD
+template <typename T>
+int rts_backward_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, int n, int p,
+                      int a_mode, T* smth, T* ym, T* yv, int* status, cudaStream_t st) {
+#define X(N_, P_)                                                                                                 \
+  if (n == N_ && p == P_)                                                                                         \
+    return a_mode == EKSB_A_DIAG                                                                                  \
+               ? launch_bwd_pipe<T, N_, P_, 0>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st)       \
+               : launch_bwd_pipe<T, N_, P_, 1>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+  EKSB_FOR_EACH_PIPE_DIM(X)
+#undef X
+  return EKSB_EDIM;
+}
+#endif
+
+}  // namespace eksb

@@ -72,3 +72,22 @@ def kf_rts(y, ev, m0, S0, C, A, Q, dtype=np.float64, first=1, smooth=True, want_
     if smooth:
         out.update(ms=smth[:, :n], Vs=sym_unpack(smth[:, n:], n), ym=ym, yv=yv, CV=cv.reshape(T, n, n)[:T - 1])
     return out
+
+
+def kf_rts_split(y, ev, m0, S0, C, A, Q, dtype=np.float64, first=1):
+    """Host build of the prep/chain split (fwd_prep+fwd_chain, bwd_prep+bwd_chain) on one track."""
+    T, p = y.shape
+    n = m0.shape[0]
+    c = lambda a: np.ascontiguousarray(a, dtype=dtype)
+    am = a_mode(A)
+    y, ev, m0, S0, C, A, Q = map(c, (y, ev, m0, S0, C, A, Q))
+    sg = n + n * (n + 1) // 2
+    filt = np.zeros((T, sg), dtype=dtype)
+    smth = np.zeros((T, sg), dtype=dtype)
+    fn = lib().hs_split_f64 if dtype == np.float64 else lib().hs_split_f32
+    P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    rc = fn(ctypes.c_int(n), ctypes.c_int(p), ctypes.c_int(am), ctypes.c_long(T), P(y), P(ev), P(m0), P(S0), P(C),
+            P(A), P(Q), ctypes.c_int(first), P(filt), P(smth))
+    if rc < 0:
+        raise ValueError(f"unsupported dims n={n} p={p}")
+    return dict(rc=rc, mf=filt[:, :n], Vf=sym_unpack(filt[:, n:], n), ms=smth[:, :n], Vs=sym_unpack(smth[:, n:], n))

@@ -53,3 +53,60 @@ extern "C" int hs_kf_rts_f32(int n, int p, int am, long Tn, const float* y, cons
                              float* filt, float* smth, float* ym, float* yv, float* cv, double* nll) {
   return dispatch<float>(n, p, am, Tn, y, ev, m0, S0, C, A, Q, first, filt, smth, ym, yv, cv, nll);
 }
+
+// ---- producer/consumer split form (what the warp-specialised kernels run) ----
+template <typename T, int N, int P, int AM>
+static int run_split(long Tn, const T* y, const T* ev, const T* m0, const T* S0, const T* C, const T* A, const T* Q,
+                     int first, T* filt, T* smth) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
+  Params<T, N, P, AM> prm;
+  load_params<T, N, P, AM>(prm, C, A, Q);
+  T m[N], V[NS];
+  for (int i = 0; i < N; ++i) m[i] = m0[i];
+  load_sym<T, N>(V, S0);
+  bool ok = true;
+  for (long t = 0; t < Tn; ++t) {
+    T rec[Rec<N>::FWD];
+    fwd_prep<T, N, P, AM>(prm, y + t * P, ev + t * P, rec);
+    if (!(t == 0 && first == kPriorOnly)) fwd_chain<T, N, P, AM>(prm, rec, !(t == 0 && first == kPriorUpdate), m, V, ok);
+    for (int i = 0; i < N; ++i) filt[t * SG + i] = m[i];
+    for (int i = 0; i < NS; ++i) filt[t * SG + N + i] = V[i];
+  }
+  T ms[N], Vs[NS];
+  for (long t = Tn - 1; t >= 0; --t) {
+    if (t == Tn - 1) {
+      for (int i = 0; i < N; ++i) ms[i] = filt[t * SG + i];
+      for (int i = 0; i < NS; ++i) Vs[i] = filt[t * SG + N + i];
+    } else {
+      T rec[Rec<N>::BWD];
+      bwd_prep<T, N, P, AM>(prm, filt + t * SG, filt + t * SG + N, rec, ok);
+      bwd_chain<T, N>(rec, ms, Vs);
+    }
+    for (int i = 0; i < N; ++i) smth[t * SG + i] = ms[i];
+    for (int i = 0; i < NS; ++i) smth[t * SG + N + i] = Vs[i];
+  }
+  return ok ? 0 : 1;
+}
+
+template <typename T>
+static int dispatch_split(int n, int p, int am, long Tn, const T* y, const T* ev, const T* m0, const T* S0, const T* C,
+                          const T* A, const T* Q, int first, T* filt, T* smth) {
+#define X(N_, P_)                                                                       \
+  if (n == N_ && p == P_)                                                               \
+    return am ? run_split<T, N_, P_, 1>(Tn, y, ev, m0, S0, C, A, Q, first, filt, smth)  \
+              : run_split<T, N_, P_, 0>(Tn, y, ev, m0, S0, C, A, Q, first, filt, smth);
+  EKSB_FOR_EACH_DIM(X)
+#undef X
+  return -1;
+}
+
+extern "C" int hs_split_f64(int n, int p, int am, long Tn, const double* y, const double* ev, const double* m0,
+                            const double* S0, const double* C, const double* A, const double* Q, int first,
+                            double* filt, double* smth) {
+  return dispatch_split<double>(n, p, am, Tn, y, ev, m0, S0, C, A, Q, first, filt, smth);
+}
+extern "C" int hs_split_f32(int n, int p, int am, long Tn, const float* y, const float* ev, const float* m0,
+                            const float* S0, const float* C, const float* A, const float* Q, int first, float* filt,
+                            float* smth) {
+  return dispatch_split<float>(n, p, am, Tn, y, ev, m0, S0, C, A, Q, first, filt, smth);
+}

@@ -83,3 +83,69 @@ def test_ensemble_bad_mode():
     from eks_b200.ensemble_kalman import ensemble
     with pytest.raises(ValueError, match="averaging not supported"):
         ensemble([pd.DataFrame({"a": [1.0]})], ["a"], "mode")
+
+
+def _random_batch(B, T, p, n, dt, seed=0, a_diag=True):
+    import torch
+    from eks_b200 import device as dev
+    rng = np.random.default_rng(seed)
+    C = np.stack([np.linalg.qr(rng.normal(size=(p, n)))[0] for _ in range(B)])
+    A = np.diag(rng.uniform(0.95, 1.0, n)) if a_diag else np.eye(n) * 0.97 + 0.01 * rng.normal(size=(n, n))
+    Q = 0.01 * np.eye(n) + 0.001
+    S0 = np.diag(rng.uniform(0.5, 2, n)); m0 = rng.normal(size=n)
+    x = np.cumsum(rng.normal(size=(B, T, n)) * 0.1, axis=1)
+    sd = np.exp(rng.normal(np.log(0.5), 0.8, size=(B, T, p)))
+    y = np.einsum("bpn,btn->btp", C, x) + sd * rng.normal(size=(B, T, p))
+    ev = sd ** 2 / 5
+    d = torch.device("cuda", 0)
+    prm = dev.TrackParams.from_numpy(m0, S0, C, A, Q, dtype=dt, device=d)
+    obs = dev.pack_obs(torch.as_tensor(y, dtype=dt).to(d), torch.as_tensor(ev, dtype=dt).to(d))
+    return dict(y=y, ev=ev, C=C, A=A, Q=Q, S0=S0, m0=m0, prm=prm, obs=obs)
+
+
+@pytest.mark.parametrize("n,p", [(3, 4), (3, 6), (3, 8), (2, 4), (4, 6), (6, 8)])
+@pytest.mark.parametrize("dtname,tol", [("float64", 1e-9), ("float32", 1e-3)])
+@pytest.mark.parametrize("a_diag", [True, False])
+def test_batched_pipe_and_plain_kernels_vs_oracle(n, p, dtname, tol, a_diag, monkeypatch):
+    """Ragged batch (B not a multiple of 32, T not a multiple of the hand-off batch): both the
+    warp-specialised and the plain kernels against the oracle, per track."""
+    import torch
+    from eks_b200 import device as dev
+    dt = getattr(torch, dtname)
+    B, T = 70, 203
+    c = _random_batch(B, T, p, n, dt, seed=n * 10 + p, a_diag=a_diag)
+    res = {}
+    for label, want_nll in (("pipe", False), ("plain", True)):     # an NLL request routes to the plain kernel
+        filt, nll, st = dev.kf_forward(c["obs"], c["prm"], B, T, want_nll=want_nll)
+        out = dev.rts_backward(filt, c["prm"], B, T, want_ym=True, want_yv=True, want_cv=want_nll)
+        assert int(st.sum()) == 0 and int(out["status"].sum()) == 0
+        sg = dev.sigma(n)
+        res[label] = dict(
+            mf=dev.unpack_rows(filt, sg, 0, B, T, n).cpu().numpy().astype(np.float64),
+            ms=dev.unpack_rows(out["smth"], sg, 0, B, T, n).cpu().numpy().astype(np.float64),
+            Vsp=dev.unpack_rows(out["smth"], sg, n, B, T, sg - n).cpu().numpy().astype(np.float64),
+            ym=dev.unpack_rows(out["ym"], p, 0, B, T, p).cpu().numpy().astype(np.float64),
+            yv=dev.unpack_rows(out["yv"], p, 0, B, T, p).cpu().numpy().astype(np.float64))
+    iu = np.triu_indices(n)
+    for b in (0, 31, 32, B - 1):
+        yq = c["y"].astype(np.float32).astype(np.float64) if dtname == "float32" else c["y"]
+        evq = c["ev"].astype(np.float32).astype(np.float64) if dtname == "float32" else c["ev"]
+        mf, Vf, S = o.filtering_pass(yq[b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], evq[b])
+        ms, Vs, _ = o.smooth_backward(yq[b], mf, Vf, S, c["A"], c["Q"], c["C"][b])
+        for label in ("pipe", "plain"):
+            r = res[label]
+            assert rel(r["mf"][b], mf) < tol, (label, b)
+            assert rel(r["ms"][b], ms) < tol, (label, b)
+            assert rel(r["Vsp"][b], Vs[:, iu[0], iu[1]]) < tol, (label, b)
+            assert rel(r["ym"][b], ms @ c["C"][b].T) < tol, (label, b)
+            assert rel(r["yv"][b], np.einsum("jk,tkl,jl->tj", c["C"][b], Vs, c["C"][b])) < tol, (label, b)
+
+
+def test_inplace_smoothing_equals_out_of_place():
+    import torch
+    from eks_b200 import device as dev
+    c = _random_batch(40, 150, 4, 3, torch.float64, seed=3)
+    filt, _, _ = dev.kf_forward(c["obs"], c["prm"], 40, 150)
+    a = dev.rts_backward(filt, c["prm"], 40, 150)
+    b = dev.rts_backward(filt.clone(), c["prm"], 40, 150, inplace=True)
+    assert torch.equal(a["smth"], b["smth"]) and torch.equal(a["ym"], b["ym"])

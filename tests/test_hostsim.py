@@ -56,3 +56,26 @@ def test_real_data_dynamic_range(dtype, tol):
         r = hostsim.kf_rts(st["y"], st["ev"], st["m0"], st["S0"], st["C"], st["A"], st["Q"], dtype=dtype, want_cv=False)
         assert r["rc"] == 0
         assert rel(r["ms"], ms) < tol and rel(r["Vs"], Vs) < tol and rel(r["ym"], ms @ st["C"].T) < tol
+
+
+@pytest.mark.parametrize("name", [k for k in KF_CASES if "ms" in CORE[k]])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-11), (np.float32, 1e-3)])
+def test_split_form_vs_reference(name, dtype, tol):
+    """prep/chain split used by the warp-specialised kernels == reference."""
+    c = CORE[name]
+    r = hostsim.kf_rts_split(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], dtype=dtype)
+    assert r["rc"] == 0
+    for k in ("mf", "Vf", "ms", "Vs"):
+        assert rel(r[k], c[k]) < tol, k
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 1e-3)])
+def test_split_form_real_data(dtype, tol):
+    from oracle import restated_smoothers as osm
+    z = cases_of(load_golden("mirror_mouse.npz"))
+    for kp, c in z.items():
+        st = osm.multicam_setup(c["stack"], 0.01, 25)
+        mf, Vf, S = o.filtering_pass(st["y"], st["m0"], st["S0"], st["C"], np.eye(4), st["A"], st["Q"], st["ev"])
+        ms, Vs, _ = o.smooth_backward(st["y"], mf, Vf, S, st["A"], st["Q"], st["C"])
+        r = hostsim.kf_rts_split(st["y"], st["ev"], st["m0"], st["S0"], st["C"], st["A"], st["Q"], dtype=dtype)
+        assert rel(r["ms"], ms) < tol and rel(r["Vs"], Vs) < tol and rel(r["mf"], mf) < tol
