@@ -1,17 +1,24 @@
-// eksb_pipe.cuh -- warp-specialised forward-filter / RTS kernels for the latency-bound regime
-// (few thousand tracks x very long T, e.g. 16 384 x 100 000: only ~3.5 track tiles per SM).
+// eksb_pipe.cuh -- warp-specialised, TMA-fed forward-filter / RTS kernels for the latency-bound
+// regime (few thousand tracks x very long T, e.g. 16 384 x 100 000: ~3.5 track tiles per SM).
 //
-// A sequential recursion exposes one warp per 32 tracks; a single warp issues ~1 dependent
-// instruction every 4 cycles, so the plain kernels (eksb_kf.cuh) run at the *instruction
-// latency* of the whole frame program.  Here each track tile gets 1 "chain" warp + H "helper"
-// warps.  Helpers stream the frame records from HBM (coalesced, register prefetch ring), do
-// every state-independent part of the frame (eksb_math.cuh: fwd_prep / bwd_prep) and hand a
-// compact record to the chain warp through a double-buffered shared-memory ring; the chain warp
-// executes only the true dependency chain (fwd_chain / bwd_chain) and writes the results.
+// A sequential recursion exposes one warp per 32 tracks.  Two things then dominate a plain
+// thread-per-track kernel (eksb_kf.cuh): (1) a lone warp issues ~1 dependent instruction every
+// 4 cycles, so the frame time is the instruction latency of the WHOLE frame program; (2) a
+// register prefetch ring cannot hide HBM latency because a warp has only 6 scoreboard slots:
+// the wait on frame t's loads also waits on the younger prefetches sharing the slot (measured:
+// ~600 ns per frame regardless of ring depth).  This kernel removes both:
+//   * raw frame records are brought HBM -> shared memory by 1-D bulk async copies
+//     (cp.async.bulk + mbarrier complete_tx; the track-tile layout makes F consecutive frames of
+//     a tile one contiguous run), NST batches in flight per tile, no registers, no scoreboards;
+//   * each tile gets 1 "chain" warp + H "helper" warps.  Helpers turn raw frames into compact
+//     state-independent records (eksb_math.cuh fwd_prep / bwd_prep) in a double-buffered
+//     shared-memory ring; the chain warp runs only the true dependency chain (fwd_chain /
+//     bwd_chain) and stores the results with full-line writes.
 // Hand-off is one named barrier (bar.sync id, (H+1)*32) per batch of F frames, per tile, so
-// tiles sharing a CTA do not couple.  TPC tiles per CTA puts one chain warp on each of the
-// SM's 4 warp schedulers.
+// tiles sharing a CTA do not couple.  TPC tiles per CTA spreads chain warps over the SM's 4
+// warp schedulers.
 #pragma once
+#include <stdint.h>
 #include "eksb_common.cuh"
 
 namespace eksb {
@@ -19,11 +26,53 @@ namespace eksb {
 __device__ __forceinline__ void tile_barrier(int id, int count) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+// global -> shared bulk async copy (TMA engine, 1-D); bytes % 16 == 0, both addresses 16 B aligned
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
 
-template <int N_, int P_, int H_, int PFH_, int ROUNDS_, int TPC_> struct PipeCfg {
-  static constexpr int H = H_, PFH = PFH_, ROUNDS = ROUNDS_, TPC = TPC_;
-  static constexpr int F = H * PFH * ROUNDS;              // frames per hand-off batch
+// H helper warps per tile, F frames per batch, NST raw batches in flight, TPC tiles per CTA
+template <int H_, int F_, int NST_, int TPC_> struct PipeCfg {
+  static constexpr int H = H_, F = F_, NST = NST_, TPC = TPC_;
   static constexpr int THREADS = TPC * (H + 1) * kLanes;
+  static_assert(F % H == 0, "helpers split a batch evenly");
+};
+
+template <typename T, int ROWS_IN, int REC, typename Cfg> struct PipeSmem {
+  static constexpr size_t kRaw = (size_t)Cfg::NST * Cfg::F * ROWS_IN * kLanes * sizeof(T);
+  static constexpr size_t kRec = (size_t)2 * Cfg::F * REC * kLanes * sizeof(T);
+  static constexpr size_t kBar = 128;                      // NST mbarriers (8 B each), padded
+  static constexpr size_t kTile = kRaw + kRec + kBar;
+  static_assert(Cfg::NST * 8 <= 128, "too many stages");
 };
 
 // ------------------------------------------------------------------------------------------
@@ -35,59 +84,71 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
                        const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
                        long B, long Tn, int first, T* __restrict__ filt, int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, REC = Rec<N>::FWD;
-  constexpr int H = Cfg::H, PFH = Cfg::PFH, ROUNDS = Cfg::ROUNDS, TPC = Cfg::TPC, F = Cfg::F;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int H = Cfg::H, TPC = Cfg::TPC, F = Cfg::F, NST = Cfg::NST;
+  using SM = PipeSmem<T, R2, REC, Cfg>;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool is_chain = warp < TPC;
   const int tile_in_cta = is_chain ? warp : (warp - TPC) % TPC;
   const int h = is_chain ? 0 : (warp - TPC) / TPC;
   const long g = (long)blockIdx.x * TPC + tile_in_cta;
   if (g >= num_tiles_dev(B)) return;                       // chain + helpers of a tile leave together
-  T* buf = reinterpret_cast<T*>(smem_raw) + (size_t)tile_in_cta * (2 * F * REC * kLanes) + lane;
+  unsigned char* tile_smem = smem_raw + (size_t)tile_in_cta * SM::kTile;
+  T* raw = reinterpret_cast<T*>(tile_smem);
+  T* recb = reinterpret_cast<T*>(tile_smem + SM::kRaw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(tile_smem + SM::kRaw + SM::kRec);
   const int bar_id = tile_in_cta + 1, bar_cnt = (H + 1) * kLanes;
   const long b = g * kLanes + lane;
   const long bp = b < B ? b : B - 1;
   Params<T, N, P, AM> prm;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
   const long nb = (Tn + F - 1) / F;
+  const T* gsrc = obs + (g * Tn * R2) * kLanes;            // tile base (lane 0)
+  constexpr uint32_t kFrameBytes = R2 * kLanes * sizeof(T);
 
   if (!is_chain) {
-    // ---------------- helper: HBM -> registers -> info records in shared memory
-    const T* o = obs + (g * Tn * R2) * kLanes + lane;
-    T ring[PFH][R2];
-#pragma unroll
-    for (int i = 0; i < PFH; ++i) {
-      long t = h + (long)i * H;
-      if (t > Tn - 1) t = Tn - 1;
-#pragma unroll
-      for (int r = 0; r < R2; ++r) ring[i][r] = o[(t * R2 + r) * kLanes];
+    const bool issuer = (h == 0 && lane == 0);
+    if (issuer) {
+      for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
+      mbar_fence_init();
+    }
+    tile_barrier(bar_id, bar_cnt);                         // barriers initialised
+    if (issuer) {
+      for (int s = 0; s < NST; ++s) {
+        if (s < nb) {
+          const long t0 = (long)s * F;
+          const uint32_t bytes = (uint32_t)((Tn - t0 < F ? Tn - t0 : F)) * kFrameBytes;
+          mbar_expect_tx(&full[s], bytes);
+          bulk_g2s(raw + (size_t)s * F * R2 * kLanes, gsrc + t0 * R2 * kLanes, bytes, &full[s]);
+        }
+      }
     }
     for (long k = 0; k <= nb; ++k) {
+      const int st = (int)(k % NST);
       if (k < nb) {
-        T* dst = buf + (k & 1) * (F * REC * kLanes);
+        mbar_wait(&full[st], (uint32_t)((k / NST) & 1));
+        const T* src = raw + (size_t)st * F * R2 * kLanes + lane;
+        T* dst = recb + (k & 1) * (F * REC * kLanes) + lane;
 #pragma unroll
-        for (int rd = 0; rd < ROUNDS; ++rd) {
+        for (int jj = 0; jj < F / H; ++jj) {
+          const int j = jj * H + h;
+          if (k * F + j < Tn) {
+            T cur[R2], rec[REC];
 #pragma unroll
-          for (int i = 0; i < PFH; ++i) {
-            const int j = (rd * PFH + i) * H + h;
-            const long t = k * F + j;
-            if (t < Tn) {
-              T cur[R2];
+            for (int r = 0; r < R2; ++r) cur[r] = src[(j * R2 + r) * kLanes];
+            fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
 #pragma unroll
-              for (int r = 0; r < R2; ++r) cur[r] = ring[i][r];
-              long tn = t + (long)PFH * H;
-              if (tn > Tn - 1) tn = Tn - 1;
-#pragma unroll
-              for (int r = 0; r < R2; ++r) ring[i][r] = o[(tn * R2 + r) * kLanes];
-              T rec[REC];
-              fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
-#pragma unroll
-              for (int r = 0; r < REC; ++r) dst[(j * REC + r) * kLanes] = rec[r];
-            }
+            for (int r = 0; r < REC; ++r) dst[(j * REC + r) * kLanes] = rec[r];
           }
         }
       }
-      tile_barrier(bar_id, bar_cnt);                       // batch k published / batch k-1 released
+      tile_barrier(bar_id, bar_cnt);                       // batch k published; raw stage st is free
+      if (issuer && k + NST < nb) {
+        const long t0 = (k + NST) * F;
+        const uint32_t bytes = (uint32_t)((Tn - t0 < F ? Tn - t0 : F)) * kFrameBytes;
+        mbar_expect_tx(&full[st], bytes);
+        bulk_g2s(raw + (size_t)st * F * R2 * kLanes, gsrc + t0 * R2 * kLanes, bytes, &full[st]);
+      }
     }
     return;
   }
@@ -109,9 +170,10 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
     for (int i = 0; i < NS; ++i) V[i] = Vi[i];
   }
   T* f = filt + (g * Tn * SG) * kLanes + lane;
+  tile_barrier(bar_id, bar_cnt);                           // (barrier init)
   tile_barrier(bar_id, bar_cnt);                           // batch 0 ready
   for (long k = 0; k < nb; ++k) {
-    const T* src = buf + (k & 1) * (F * REC * kLanes);
+    const T* src = recb + (k & 1) * (F * REC * kLanes) + lane;
 #pragma unroll
     for (int j = 0; j < F; ++j) {
       const long t = k * F + j;
@@ -134,7 +196,9 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
 }
 
 // ------------------------------------------------------------------------------------------
-// backward:  filt records -> smth records (+ ym, yv); walks u = T-1-t upward
+// backward:  filt records -> smth records (+ ym, yv); walks u = T-1-t upward.
+// Batch k holds frames t_hi = T-1-kF down to t_lo = max(0, T-(k+1)F): one contiguous run in
+// HBM; local frame j (u = kF+j) sits at run offset nfr-1-j.
 // ------------------------------------------------------------------------------------------
 template <typename T, int N, int P, int AM, typename Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS)
@@ -142,70 +206,86 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
                          int shared_mask, long B, long Tn, T* smth, T* __restrict__ ym, T* __restrict__ yv,
                          int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, REC = Rec<N>::BWD;
-  constexpr int H = Cfg::H, PFH = Cfg::PFH, ROUNDS = Cfg::ROUNDS, TPC = Cfg::TPC, F = Cfg::F;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int H = Cfg::H, TPC = Cfg::TPC, F = Cfg::F, NST = Cfg::NST;
+  using SM = PipeSmem<T, SG, REC, Cfg>;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool is_chain = warp < TPC;
   const int tile_in_cta = is_chain ? warp : (warp - TPC) % TPC;
   const int h = is_chain ? 0 : (warp - TPC) / TPC;
   const long g = (long)blockIdx.x * TPC + tile_in_cta;
   if (g >= num_tiles_dev(B)) return;
-  T* buf = reinterpret_cast<T*>(smem_raw) + (size_t)tile_in_cta * (2 * F * REC * kLanes) + lane;
+  unsigned char* tile_smem = smem_raw + (size_t)tile_in_cta * SM::kTile;
+  T* raw = reinterpret_cast<T*>(tile_smem);
+  T* recb = reinterpret_cast<T*>(tile_smem + SM::kRaw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(tile_smem + SM::kRaw + SM::kRec);
   const int bar_id = tile_in_cta + 1, bar_cnt = (H + 1) * kLanes;
   const long b = g * kLanes + lane;
   const long bp = b < B ? b : B - 1;
   Params<T, N, P, AM> prm;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
   const long nb = (Tn + F - 1) / F;
+  const T* gsrc = filt + (g * Tn * SG) * kLanes;
+  constexpr uint32_t kFrameBytes = SG * kLanes * sizeof(T);
   bool ok = true;
 
   if (!is_chain) {
-    const T* fi = filt + (g * Tn * SG) * kLanes + lane;
-    T ring[PFH][SG];
-#pragma unroll
-    for (int i = 0; i < PFH; ++i) {
-      long u = h + (long)i * H;
-      if (u > Tn - 1) u = Tn - 1;
-      const long t = Tn - 1 - u;
-#pragma unroll
-      for (int r = 0; r < SG; ++r) ring[i][r] = fi[(t * SG + r) * kLanes];
+    const bool issuer = (h == 0 && lane == 0);
+    if (issuer) {
+      for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
+      mbar_fence_init();
+    }
+    tile_barrier(bar_id, bar_cnt);
+    if (issuer) {
+      for (int s = 0; s < NST; ++s) {
+        if (s < nb) {
+          const long rem = Tn - (long)s * F;
+          const long nfr = rem < F ? rem : F;
+          const long t_lo = rem - nfr;
+          mbar_expect_tx(&full[s], (uint32_t)nfr * kFrameBytes);
+          bulk_g2s(raw + (size_t)s * F * SG * kLanes, gsrc + t_lo * SG * kLanes, (uint32_t)nfr * kFrameBytes, &full[s]);
+        }
+      }
     }
     for (long k = 0; k <= nb; ++k) {
+      const int st = (int)(k % NST);
       if (k < nb) {
-        T* dst = buf + (k & 1) * (F * REC * kLanes);
+        mbar_wait(&full[st], (uint32_t)((k / NST) & 1));
+        const long rem = Tn - k * F;
+        const int nfr = (int)(rem < F ? rem : F);
+        const T* src = raw + (size_t)st * F * SG * kLanes + lane;
+        T* dst = recb + (k & 1) * (F * REC * kLanes) + lane;
 #pragma unroll
-        for (int rd = 0; rd < ROUNDS; ++rd) {
+        for (int jj = 0; jj < F / H; ++jj) {
+          const int j = jj * H + h;
+          if (j < nfr) {
+            const int off = nfr - 1 - j;
+            T cur[SG], rec[REC];
 #pragma unroll
-          for (int i = 0; i < PFH; ++i) {
-            const int j = (rd * PFH + i) * H + h;
-            const long u = k * F + j;
-            if (u < Tn) {
-              T cur[SG];
+            for (int r = 0; r < SG; ++r) cur[r] = src[(off * SG + r) * kLanes];
+            if (k == 0 && j == 0) {                        // last frame: ms = mf, Vs = Vf  (:152-153)
 #pragma unroll
-              for (int r = 0; r < SG; ++r) cur[r] = ring[i][r];
-              long un = u + (long)PFH * H;
-              if (un > Tn - 1) un = Tn - 1;
-              const long tn = Tn - 1 - un;
+              for (int r = 0; r < N * N; ++r) rec[r] = T(0);
 #pragma unroll
-              for (int r = 0; r < SG; ++r) ring[i][r] = fi[(tn * SG + r) * kLanes];
-              T rec[REC];
-              if (u == 0) {                                // last frame: ms = mf, Vs = Vf  (:152-153)
+              for (int r = 0; r < NS; ++r) rec[N * N + r] = cur[N + r];
 #pragma unroll
-                for (int r = 0; r < N * N; ++r) rec[r] = T(0);
-#pragma unroll
-                for (int r = 0; r < NS; ++r) rec[N * N + r] = cur[N + r];
-#pragma unroll
-                for (int r = 0; r < N; ++r) rec[N * N + NS + r] = cur[r];
-              } else {
-                bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
-              }
-#pragma unroll
-              for (int r = 0; r < REC; ++r) dst[(j * REC + r) * kLanes] = rec[r];
+              for (int r = 0; r < N; ++r) rec[N * N + NS + r] = cur[r];
+            } else {
+              bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
             }
+#pragma unroll
+            for (int r = 0; r < REC; ++r) dst[(j * REC + r) * kLanes] = rec[r];
           }
         }
       }
       tile_barrier(bar_id, bar_cnt);
+      if (issuer && k + NST < nb) {
+        const long rem = Tn - (k + NST) * F;
+        const long nfr = rem < F ? rem : F;
+        const long t_lo = rem - nfr;
+        mbar_expect_tx(&full[st], (uint32_t)nfr * kFrameBytes);
+        bulk_g2s(raw + (size_t)st * F * SG * kLanes, gsrc + t_lo * SG * kLanes, (uint32_t)nfr * kFrameBytes, &full[st]);
+      }
     }
     if (b < B && status && !ok) status[b] = 1;
     return;
@@ -219,9 +299,10 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
   T* so = smth + (g * Tn * SG) * kLanes + lane;
   T* ymo = ym ? ym + (g * Tn * P) * kLanes + lane : nullptr;
   T* yvo = yv ? yv + (g * Tn * P) * kLanes + lane : nullptr;
-  tile_barrier(bar_id, bar_cnt);
+  tile_barrier(bar_id, bar_cnt);                           // (barrier init)
+  tile_barrier(bar_id, bar_cnt);                           // batch 0 ready
   for (long k = 0; k < nb; ++k) {
-    const T* src = buf + (k & 1) * (F * REC * kLanes);
+    const T* src = recb + (k & 1) * (F * REC * kLanes) + lane;
 #pragma unroll
     for (int j = 0; j < F; ++j) {
       const long u = k * F + j;

@@ -4,30 +4,31 @@
 
 namespace eksb {
 
-constexpr int kSmemBudget = 110 * 1024;   // per CTA, so that at least two CTAs fit the 227 KB of an SM
-
-template <typename T, int ROWS> struct HelperRing {      // helper prefetch ring: ~64 32-bit registers
-  static constexpr int kRegs = ROWS * (int)(sizeof(T) / 4);
-  static constexpr int raw = 64 / kRegs;
-  static constexpr int value = raw < 1 ? 1 : (raw > 8 ? 8 : raw);
-};
+constexpr size_t kCtaSmemBudget = 113 * 1024;   // two CTAs per SM (227 KB usable)
+constexpr size_t kTileSmemBudget = 56 * 1024;   // four tiles per SM
 
 #ifndef EKSB_PIPE_TPC
 #define EKSB_PIPE_TPC 4
 #endif
 
-template <typename T, int N, int P, int H, int ROWS_IN, int REC> struct AutoCfg {
-  static constexpr int PFH0 = HelperRing<T, ROWS_IN>::value;
-  // frames per hand-off batch: 8, or 4 when 8 would need more than ~40 KB of ring per tile
-  static constexpr int FT = ((size_t)2 * 8 * REC * kLanes * sizeof(T) <= 40 * 1024) ? 8 : 4;
-  static constexpr int PFH = (H * PFH0 > FT) ? (FT / H) : PFH0;
-  static constexpr int ROUNDS = (FT + H * PFH - 1) / (H * PFH);
-  static constexpr int F = H * PFH * ROUNDS;
-  static constexpr size_t kTileSmem = (size_t)2 * F * REC * kLanes * sizeof(T);
-  static constexpr int TPC0 = (int)(kSmemBudget / kTileSmem);
+template <typename T, int ROWS_IN, int REC, int H, int F, int NST> struct TileBytes {
+  static constexpr size_t value = PipeSmem<T, ROWS_IN, REC, PipeCfg<H, F, NST, 1>>::kTile;
+};
+
+// Largest (F, NST) whose per-tile ring fits the budget: F frames per hand-off batch (fewer
+// barriers when larger), NST raw batches in flight (deeper HBM prefetch when larger).
+template <typename T, int H, int ROWS_IN, int REC> struct AutoCfg {
+  static constexpr bool f8n3 = TileBytes<T, ROWS_IN, REC, H, 8, 3>::value <= kTileSmemBudget;
+  static constexpr bool f4n3 = TileBytes<T, ROWS_IN, REC, H, 4, 3>::value <= kTileSmemBudget;
+  static constexpr bool f4n2 = TileBytes<T, ROWS_IN, REC, H, 4, 2>::value <= kTileSmemBudget;
+  static constexpr bool f2n3 = TileBytes<T, ROWS_IN, REC, H, 2, 3>::value <= kTileSmemBudget;
+  static constexpr int F = f8n3 ? 8 : (f4n3 || f4n2) ? 4 : 2;
+  static constexpr int NST = f8n3 ? 3 : f4n3 ? 3 : f4n2 ? 2 : 3;
+  static constexpr size_t kTileSmem = TileBytes<T, ROWS_IN, REC, H, F, NST>::value;
+  static constexpr int TPC0 = (int)(kCtaSmemBudget / kTileSmem);
   static constexpr int TPC = TPC0 > EKSB_PIPE_TPC ? EKSB_PIPE_TPC : TPC0;
-  static constexpr bool ok = TPC >= 1 && PFH >= 1;
-  using type = PipeCfg<N, P, H, (PFH >= 1 ? PFH : 1), ROUNDS, (TPC >= 1 ? TPC : 1)>;
+  static constexpr bool ok = TPC >= 1 && (f8n3 || f4n3 || f4n2 || f2n3);
+  using type = PipeCfg<H, F, NST, (TPC >= 1 ? TPC : 1)>;
 };
 
 constexpr int kFwdHelpers = 1, kBwdHelpers = 2;
@@ -35,7 +36,7 @@ constexpr int kFwdHelpers = 1, kBwdHelpers = 2;
 template <typename T, int N, int P, int AM>
 static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                            long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
-  using Auto = AutoCfg<T, N, P, kFwdHelpers, 2 * P, Rec<N>::FWD>;
+  using Auto = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD>;
   if (!Auto::ok) return EKSB_EDIM;
   using Cfg = typename Auto::type;
   auto kern = kf_forward_pipe_kernel<T, N, P, AM, Cfg>;
@@ -49,7 +50,7 @@ static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, c
 template <typename T, int N, int P, int AM>
 static int launch_bwd_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, T* smth,
                            T* ym, T* yv, int* status, cudaStream_t st) {
-  using Auto = AutoCfg<T, N, P, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD>;
+  using Auto = AutoCfg<T, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD>;
   if (!Auto::ok) return EKSB_EDIM;
   using Cfg = typename Auto::type;
   auto kern = rts_backward_pipe_kernel<T, N, P, AM, Cfg>;
