@@ -189,6 +189,36 @@ static int pack_state_api(const T* mean, const T* cov, long B, long Tn, int n, T
   return check_launch("pack_state_kernel");
 }
 
+// ym = C * mean: rows [0,n) of a state record buffer -> p-row records (y_m = C ms, multiview_pca_smoother.py:745;
+// y_m = B q for the Newton variant, :905).  One warp per (tile, frame); runtime n <= 8, p <= 16.
+template <typename T>
+__global__ void project_kernel(const T* __restrict__ state, int rows, const T* __restrict__ C, int shared_mask, long B,
+                               long Tn, int n, int p, T* __restrict__ ym) {
+  const int lane = threadIdx.x & 31;
+  const long nchunk = (Tn + 7) / 8;
+  const long g = blockIdx.x / nchunk;
+  const long t = (blockIdx.x - g * nchunk) * 8 + (threadIdx.x >> 5);
+  if (t >= Tn) return;
+  const long b = g * kLanes + lane;
+  const long bp = b < B ? b : B - 1;
+  const T* c = C + ((shared_mask & EKSB_SHARED_C) ? 0 : bp * p * n);
+  T m[8];
+  for (int i = 0; i < n; ++i) m[i] = state[((g * Tn + t) * rows + i) * kLanes + lane];
+  for (int j = 0; j < p; ++j) {
+    T s = T(0);
+    for (int i = 0; i < n; ++i) s += c[j * n + i] * m[i];
+    ym[((g * Tn + t) * p + j) * kLanes + lane] = s;
+  }
+}
+
+template <typename T>
+static int project_api(const T* state, int rows, const T* C, int shared_mask, long B, long Tn, int n, int p, T* ym, void* stream) {
+  if (!state || !C || !ym || B <= 0 || Tn <= 0 || n < 1 || n > 8 || p < 1 || p > 16 || rows < n) { set_error("project: bad argument"); return EKSB_EARG; }
+  unsigned grid = (unsigned)(((Tn + 7) / 8) * num_tiles(B));
+  project_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(state, rows, C, shared_mask, B, Tn, n, p, ym);
+  return check_launch("project_kernel");
+}
+
 }  // namespace eksb
 
 using namespace eksb;
@@ -228,4 +258,10 @@ extern "C" int eksb_pack_state_f64(const double* mean, const double* cov, long B
 }
 extern "C" int eksb_pack_state_f32(const float* mean, const float* cov, long B, long T, int n, float* state, void* stream) {
   return pack_state_api<float>(mean, cov, B, T, n, state, stream);
+}
+extern "C" int eksb_project_f64(const double* state, int rows, const double* C, int shared_mask, long B, long T, int n, int p, double* ym, void* stream) {
+  return project_api<double>(state, rows, C, shared_mask, B, T, n, p, ym, stream);
+}
+extern "C" int eksb_project_f32(const float* state, int rows, const float* C, int shared_mask, long B, long T, int n, int p, float* ym, void* stream) {
+  return project_api<float>(state, rows, C, shared_mask, B, T, n, p, ym, stream);
 }

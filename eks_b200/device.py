@@ -145,6 +145,16 @@ def pack_state(mean, cov):
     return state
 
 
+def project(state, prm: "TrackParams", B, T, rows=None):
+    """ym records = C * (mean rows of a state record buffer)."""
+    rows = sigma(prm.n) if rows is None else rows
+    ym = alloc_records(B, T, prm.p, state.dtype, state.device)
+    fn = getattr(lib(), f"eksb_project_{_sfx(state.dtype)}")
+    check(fn(_ptr(state), rows, _ptr(prm.C), prm.shared_mask, B, T, prm.n, prm.p, _ptr(ym), _stream(state.device)),
+          "eksb_project")
+    return ym
+
+
 # ------------------------------------------------------------------ A1 ensemble
 def _mode(mode):
     if mode == "median":

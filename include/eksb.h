@@ -166,6 +166,14 @@ EKSB_API int eksb_kf_forward_generic_f32(const float* obs, const float* m0, cons
                                 const float* Q, const float* R, int r_shared, int shared_mask, long B, long T, int n,
                                 int p, int first, float* filt, int* status, void* stream);
 
+/* ym = C * mean over a state record buffer with `rows` rows per record (mean = rows [0,n)):
+ * y_m_smooth = C ms (multiview_pca_smoother.py:745) or B q for the Newton variant (:905).
+ * ym: p-row track-tile records.  n <= 8, p <= 16. */
+EKSB_API int eksb_project_f64(const double* state, int rows, const double* C, int shared_mask, long B, long T, int n, int p,
+                     double* ym, void* stream);
+EKSB_API int eksb_project_f32(const float* state, int rows, const float* C, int shared_mask, long B, long T, int n, int p,
+                     float* ym, void* stream);
+
 /* EKSB_DECLS_END (new declarations go above this line) */
 #ifdef __cplusplus
 }

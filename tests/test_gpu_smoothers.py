@@ -1,0 +1,75 @@
+"""GPU: the reference-named smoothers against the reference's own shipped outputs (golden CSV values
+frozen in tests/golden by make_golden.py) -- mirror-mouse, ibl-pupil, ibl-paw, mirror-fish clips."""
+import numpy as np
+import pandas as pd
+import pytest
+
+from conftest import load_golden, cases_of
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-7     # absolute, pixels; observed ~1e-10.  north_star bar: 1e-5 relative in fp64
+
+
+def _cams(stack, names):
+    M = stack.shape[0]
+    return [[pd.DataFrame(stack[m][:, 2 * c:2 * c + 2], columns=["kp_x", "kp_y"]) for m in range(M)]
+            for c in range(len(names))]
+
+
+def test_mirror_mouse_standard_and_opti():
+    from eks_b200.multiview_pca_smoother import ensemble_kalman_smoother_multi_cam, eks_opti_smoother_multi_cam
+    cams = ["top", "bot"]
+    for kp, c in cases_of(load_golden("mirror_mouse.npz")).items():
+        out = ensemble_kalman_smoother_multi_cam(_cams(c["stack"], cams), kp, 0.01, 25, cams)
+        got = np.column_stack([out[f"{n}_df"].to_numpy()[:, :2] for n in cams])
+        np.testing.assert_allclose(got, c["shipped_std"], rtol=0, atol=TOL)
+        np.testing.assert_allclose(got, c["ref_std"], rtol=0, atol=TOL)
+        df = out["top_df"]
+        assert list(df.columns) == [("ensemble-kalman_tracker", kp, k) for k in ("x", "y", "likelihood")]
+        assert df.columns.names == ["scorer", "bodyparts", "coords"] and np.isnan(df.to_numpy()[:, 2]).all()
+        opt = eks_opti_smoother_multi_cam(_cams(c["stack"], cams), kp, 0.01, 25, cams, plot=False)
+        got = np.column_stack([opt[f"{n}_df"].to_numpy()[:, :2] for n in cams])
+        np.testing.assert_allclose(got, c["shipped_opti"], rtol=0, atol=TOL)
+
+
+def test_fish_clips():
+    from eks_b200.multiview_pca_smoother import ensemble_kalman_smoother_multi_cam
+    cams = ["main", "top", "right"]
+    z = cases_of(load_golden("fish.npz"))
+    assert len(z) >= 100
+    for kp, c in z.items():
+        out = ensemble_kalman_smoother_multi_cam(_cams(c["stack"], cams), "kp", 0.01, 50, cams)
+        got = np.column_stack([out[f"{n}_df"].to_numpy()[:, :2] for n in cams])
+        np.testing.assert_allclose(got, c["shipped"], rtol=0, atol=1e-6)
+
+
+def test_pupil_standard_and_opti():
+    from eks_b200.pupil_smoother import ensemble_kalman_smoother_pupil, eks_opti_smoother_pupil, KEYS
+    z = load_golden("pupil.npz")
+    dfs = [pd.DataFrame(z["stack"][m], columns=KEYS) for m in range(z["stack"].shape[0])]
+    kp = [str(s) for s in z["keypoint_names"]]
+    out = ensemble_kalman_smoother_pupil(dfs, kp, "ensemble-kalman_tracker", np.diag([.99, .99, .99]))
+    np.testing.assert_allclose(out["latents_df"].to_numpy(), z["shipped/latents"], rtol=0, atol=TOL)
+    np.testing.assert_allclose(out["markers_df"].to_numpy(), z["shipped/markers"], rtol=0, atol=TOL, equal_nan=True)
+    assert out["markers_df"].shape == (2000, 12) and out["latents_df"].columns.names == ["scorer", "latent"]
+    assert [c[1] for c in out["latents_df"].columns] == ["diameter", "com_x", "com_y"]
+    out = ensemble_kalman_smoother_pupil(dfs, kp, "ensemble-kalman_tracker", np.diag([.9999, .999, .999]))
+    np.testing.assert_allclose(out["latents_df"].to_numpy(), z["adef/latents"], rtol=0, atol=TOL)
+    opt = eks_opti_smoother_pupil(dfs, kp, "ensemble-kalman_tracker", np.eye(3), plot=False)
+    np.testing.assert_allclose(opt["latents_df"].to_numpy(), z["shipped/opti_latents"], rtol=0, atol=TOL)
+
+
+def test_paw_asynchronous():
+    from eks_b200.multiview_pca_smoother import ensemble_kalman_smoother_paw_asynchronous, eks_opti_smoother_paw_asynchronous
+    from oracle import restated as o
+    z = load_golden("paw.npz")
+    cols = ["paw_l_x", "paw_l_y", "paw_l_likelihood", "paw_r_x", "paw_r_y", "paw_r_likelihood"]
+    left = [pd.DataFrame(a, columns=cols) for a in z["left"]]
+    right = [pd.DataFrame(a, columns=cols) for a in z["right"]]
+    kp = [str(s) for s in z["keypoint_names"]]
+    out = ensemble_kalman_smoother_paw_asynchronous(left, right, z["ts_left"], z["ts_right"], kp, 0.01, 25)
+    assert out["left_df"].shape == (997, 6)
+    np.testing.assert_allclose(out["left_df"].to_numpy(), z["left_df"], rtol=0, atol=TOL, equal_nan=True)
+    np.testing.assert_allclose(out["right_df"].to_numpy(), z["right_df"], rtol=0, atol=TOL, equal_nan=True)
+    opt = eks_opti_smoother_paw_asynchronous(left, right, z["ts_left"], z["ts_right"], kp, 0.01, 25)
+    assert opt["left_df"].shape == (997, 6) and np.isfinite(opt["left_df"].to_numpy()[:, [0, 1, 3, 4]]).all()
