@@ -219,9 +219,82 @@ static int project_api(const T* state, int rows, const T* C, int shared_mask, lo
   return check_launch("project_kernel");
 }
 
+// z[t,j] = (y[t,j] - (C ms[t])_j) / sqrt((C Vs[t] C^T)_jj + add_ev * ev[t,j])   (build-side
+// definition, the reference has no z-score).  One warp per (tile, frame); runtime n <= 8, p <= 16.
+template <typename T>
+__global__ void zscore_kernel(const T* __restrict__ obs, const T* __restrict__ smth, const T* __restrict__ C,
+                              int shared_mask, long B, long Tn, int n, int p, int add_ev, T* __restrict__ z) {
+  const int lane = threadIdx.x & 31;
+  const long nchunk = (Tn + 7) / 8;
+  const long g = blockIdx.x / nchunk;
+  const long t = (blockIdx.x - g * nchunk) * 8 + (threadIdx.x >> 5);
+  if (t >= Tn) return;
+  const long b = g * kLanes + lane;
+  const long bp = b < B ? b : B - 1;
+  const T* c = C + ((shared_mask & EKSB_SHARED_C) ? 0 : bp * p * n);
+  const int sg = n + n * (n + 1) / 2;
+  T m[8], V[8][8];
+  const T* rec = smth + ((g * Tn + t) * sg) * kLanes + lane;
+  for (int i = 0; i < n; ++i) m[i] = rec[i * kLanes];
+  int k = n;
+  for (int i = 0; i < n; ++i)
+    for (int j = i; j < n; ++j) { V[i][j] = rec[k * kLanes]; V[j][i] = V[i][j]; ++k; }
+  const T* o = obs + ((g * Tn + t) * 2 * p) * kLanes + lane;
+  for (int j = 0; j < p; ++j) {
+    T mu = T(0), var = T(0);
+    for (int i = 0; i < n; ++i) {
+      mu += c[j * n + i] * m[i];
+      T a = T(0);
+      for (int l = 0; l < n; ++l) a += V[i][l] * c[j * n + l];
+      var += c[j * n + i] * a;
+    }
+    if (add_ev) var += o[(p + j) * kLanes];
+    z[((g * Tn + t) * p + j) * kLanes + lane] = (o[j * kLanes] - mu) / sqrt(var);
+  }
+}
+
+template <typename T>
+static int zscore_api(const T* obs, const T* smth, const T* C, int shared_mask, long B, long Tn, int n, int p, int add_ev,
+                      T* z, void* stream) {
+  if (!obs || !smth || !C || !z || B <= 0 || Tn <= 0 || n < 1 || n > 8 || p < 1 || p > 16) { set_error("zscore: bad argument"); return EKSB_EARG; }
+  unsigned grid = (unsigned)(((Tn + 7) / 8) * num_tiles(B));
+  zscore_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(obs, smth, C, shared_mask, B, Tn, n, p, add_ev, z);
+  return check_launch("zscore_kernel");
+}
+
+// out[g] = sum_b in[g][b]: one CTA per row, fixed-order tree so the result does not depend on timing.
+// Feeds the NCCL all-reduce of the smoothing-parameter grid search.
+__global__ void __launch_bounds__(256) reduce_rows_kernel(const double* __restrict__ in, long B, double* __restrict__ out) {
+  __shared__ double part[256];
+  const double* row = in + (long)blockIdx.x * B;
+  double s = 0.0;
+  for (long i = threadIdx.x; i < B; i += 256) s += row[i];
+  part[threadIdx.x] = s;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (threadIdx.x < w) part[threadIdx.x] += part[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[blockIdx.x] = part[0];
+}
+
 }  // namespace eksb
 
 using namespace eksb;
+
+extern "C" int eksb_reduce_rows_f64(const double* in, int rows, long B, double* out, void* stream) {
+  if (!in || !out || rows <= 0 || B <= 0) { set_error("reduce_rows: bad argument"); return EKSB_EARG; }
+  reduce_rows_kernel<<<rows, 256, 0, (cudaStream_t)stream>>>(in, B, out);
+  return check_launch("reduce_rows_kernel");
+}
+extern "C" int eksb_zscore_f64(const double* obs, const double* smth, const double* C, int shared_mask, long B, long T, int n,
+                               int p, int add_ev, double* z, void* stream) {
+  return zscore_api<double>(obs, smth, C, shared_mask, B, T, n, p, add_ev, z, stream);
+}
+extern "C" int eksb_zscore_f32(const float* obs, const float* smth, const float* C, int shared_mask, long B, long T, int n,
+                               int p, int add_ev, float* z, void* stream) {
+  return zscore_api<float>(obs, smth, C, shared_mask, B, T, n, p, add_ev, z, stream);
+}
 
 extern "C" int eksb_version(void) { return 100; }
 extern "C" const char* eksb_last_error_string(void) { return g_err; }

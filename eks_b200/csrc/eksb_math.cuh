@@ -671,4 +671,121 @@ EKSB_HD void bwd_chain(const T* rec, T* ms, T* Vs) {
   for (int i = 0; i < NS; ++i) Vs[i] = rec[N * N + i] + JVJ[i];
 }
 
+// ---------------------------------------------------------------------------
+// A7: block-tridiagonal Newton system  H x = g  of the EKS posterior (spec:
+// ref/Kalman_smoother.pdf p.1, Simulations.ipynb[16-20], eks/block_tridiag.py:15-24):
+//   H_tt = B^T D_t^-1 B + [S0^-1 | E^-1] + [A^T E^-1 A | 0 at t=T-1],  H_{t,t+1} = U = -A^T E^-1,
+//   g_t  = B^T D_t^-1 y_t (+ S0^-1 m0 at t=0).
+// Block-Thomas:  M_t = H_tt - U^T M_{t-1}^-1 U,  z_t = g_t - U^T M_{t-1}^-1 z_{t-1}   (forward chain)
+//                x_t = M_t^-1 (z_t - U x_{t+1})                                       (back-substitution)
+// and the diagonal blocks of H^-1:  Sig_t = M_t^-1 + G_t Sig_{t+1} G_t^T,  G_t = -M_t^-1 U.
+// B^T D^-1 B and B^T D^-1 y are exactly the info record fwd_prep() builds, and the backward
+// recursion has the shape of bwd_chain() with (J,L,g) = (G_t, M_t^-1, M_t^-1 z_t), so the solver
+// reuses both pipelines.  x equals the RTS mean and Sig the RTS covariance.
+// ---------------------------------------------------------------------------
+template <typename T, int N> struct BtdConst {
+  T iE[Dim<N>::NS];     // E^-1
+  T K[Dim<N>::NS];      // A^T E^-1 A
+  T Ut[N][N];           // U^T = -E^-1 A
+};
+
+template <typename T, int N, int P, int AM>
+EKSB_HD void btd_make_const(const Params<T, N, P, AM>& prm, BtdConst<T, N>& c, bool& ok) {
+  sym_inv<T, N>(prm.Q, c.iE, ok);
+  T EA[N][N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      if (AM == 0) {
+        EA[i][j] = c.iE[sym_idx<N>(i, j)] * prm.A[j];
+      } else {
+        T s = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) s += c.iE[sym_idx<N>(i, k)] * prm.A[k * N + j];
+        EA[i][j] = s;
+      }
+      c.Ut[i][j] = -EA[i][j];
+    }
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = i; j < N; ++j) {
+      T s = T(0);
+      if (AM == 0) {
+        s = prm.A[i] * EA[i][j];
+      } else {
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) s += prm.A[k * N + i] * EA[k][j];
+      }
+      c.K[sym_idx<N>(i, j)] = s;
+    }
+  }
+}
+
+// one forward-elimination step; (z, iM) carry z_{t-1}, M_{t-1}^-1 in and z_t, M_t^-1 out
+template <typename T, int N>
+EKSB_HD void btd_fwd_chain(const BtdConst<T, N>& c, const T* rec, bool first, bool last, const T* iS0,
+                           const T* iS0m0, T* z, T* iM, bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T M[NS], g[N];
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) M[k] = rec[k] + (first ? iS0[k] : c.iE[k]) + (last ? T(0) : c.K[k]);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) g[i] = rec[NS + i] + (first ? iS0m0[i] : T(0));
+  if (!first) {
+    T W[N][N];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) {
+        T s = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) s += c.Ut[i][k] * iM[sym_idx<N>(k, j)];
+        W[i][j] = s;
+      }
+    }
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = i; j < N; ++j) {
+        T s = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) s += W[i][k] * c.Ut[j][k];
+        M[sym_idx<N>(i, j)] -= s;
+      }
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += W[i][k] * z[k];
+      g[i] -= s;
+    }
+  }
+  sym_inv<T, N>(M, iM, ok);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) z[i] = g[i];
+}
+
+// (z_t, M_t^-1) -> backward record [ J = G_t | L = M_t^-1 | g = M_t^-1 z_t ]  (J = 0 at the last frame)
+template <typename T, int N>
+EKSB_HD void btd_bwd_prep(const BtdConst<T, N>& c, const T* z, const T* iM, bool terminal, T* rec) {
+  constexpr int NS = Dim<N>::NS;
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s -= iM[sym_idx<N>(i, k)] * c.Ut[j][k];
+      rec[i * N + j] = terminal ? T(0) : s;
+    }
+    T gi = T(0);
+    EKSB_UNROLL
+    for (int k = 0; k < N; ++k) gi += iM[sym_idx<N>(i, k)] * z[k];
+    rec[N * N + NS + i] = gi;
+  }
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) rec[N * N + k] = iM[k];
+}
+
 }  // namespace eksb

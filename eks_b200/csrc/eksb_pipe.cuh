@@ -78,7 +78,9 @@ template <typename T, int ROWS_IN, int REC, typename Cfg> struct PipeSmem {
 // ------------------------------------------------------------------------------------------
 // forward:  obs records -> filt records
 // ------------------------------------------------------------------------------------------
-template <typename T, int N, int P, int AM, typename Cfg>
+// OP = 0: Kalman filter (A2/A6).  OP = 1: forward elimination of the block-tridiagonal Newton
+// system (A7, eksb_math.cuh btd_fwd_chain); the record written is (z_t, M_t^-1).
+template <typename T, int N, int P, int AM, int OP, typename Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS)
 kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                        const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
@@ -163,7 +165,17 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
     load_sym<T, N>(V, ps);
   }
   bool ok = true;
-  if (first == kPriorOnly) {
+  BtdConst<T, N> bc;
+  T iS0[NS], iS0m0[N];
+  if (OP == 1) {
+    btd_make_const<T, N, P, AM>(prm, bc, ok);
+    sym_inv<T, N>(V, iS0, ok);
+    sym_matvec<T, N>(iS0, m, iS0m0);
+#pragma unroll
+    for (int i = 0; i < N; ++i) m[i] = T(0);
+#pragma unroll
+    for (int i = 0; i < NS; ++i) V[i] = T(0);
+  } else if (first == kPriorOnly) {
     T Vi[NS];
     sym_inv<T, N>(V, Vi, ok);
 #pragma unroll
@@ -181,7 +193,9 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
         T rec[REC];
 #pragma unroll
         for (int r = 0; r < REC; ++r) rec[r] = src[(j * REC + r) * kLanes];
-        if (!(t == 0 && first == kPriorOnly))
+        if (OP == 1)
+          btd_fwd_chain<T, N>(bc, rec, t == 0, t == Tn - 1, iS0, iS0m0, m, V, ok);
+        else if (!(t == 0 && first == kPriorOnly))
           fwd_chain<T, N, P, AM>(prm, rec, !(t == 0 && first == kPriorUpdate), m, V, ok);
         T* o = f + t * SG * kLanes;
 #pragma unroll
@@ -200,7 +214,9 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
 // Batch k holds frames t_hi = T-1-kF down to t_lo = max(0, T-(k+1)F): one contiguous run in
 // HBM; local frame j (u = kF+j) sits at run offset nfr-1-j.
 // ------------------------------------------------------------------------------------------
-template <typename T, int N, int P, int AM, typename Cfg>
+// OP = 0: RTS smoother (A4/A5).  OP = 1: back-substitution + selected inverse of the
+// block-tridiagonal system from the (z_t, M_t^-1) records (btd_bwd_prep); same chain.
+template <typename T, int N, int P, int AM, int OP, typename Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS)
 rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
                          int shared_mask, long B, long Tn, T* smth, T* __restrict__ ym, T* __restrict__ yv,
@@ -231,6 +247,8 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
 
   if (!is_chain) {
     const bool issuer = (h == 0 && lane == 0);
+    BtdConst<T, N> bc;
+    if (OP == 1) btd_make_const<T, N, P, AM>(prm, bc, ok);
     if (issuer) {
       for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
       mbar_fence_init();
@@ -263,7 +281,9 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
             T cur[SG], rec[REC];
 #pragma unroll
             for (int r = 0; r < SG; ++r) cur[r] = src[(off * SG + r) * kLanes];
-            if (k == 0 && j == 0) {                        // last frame: ms = mf, Vs = Vf  (:152-153)
+            if (OP == 1) {
+              btd_bwd_prep<T, N>(bc, cur, cur + N, k == 0 && j == 0, rec);
+            } else if (k == 0 && j == 0) {                 // last frame: ms = mf, Vs = Vf  (:152-153)
 #pragma unroll
               for (int r = 0; r < N * N; ++r) rec[r] = T(0);
 #pragma unroll

@@ -33,13 +33,13 @@ template <typename T, int H, int ROWS_IN, int REC> struct AutoCfg {
 
 constexpr int kFwdHelpers = 1, kBwdHelpers = 2;
 
-template <typename T, int N, int P, int AM>
+template <typename T, int N, int P, int AM, int OP = 0>
 static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                            long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
   using Auto = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD>;
   if (!Auto::ok) return EKSB_EDIM;
   using Cfg = typename Auto::type;
-  auto kern = kf_forward_pipe_kernel<T, N, P, AM, Cfg>;
+  auto kern = kf_forward_pipe_kernel<T, N, P, AM, OP, Cfg>;
   const size_t smem = Auto::kTileSmem * Cfg::TPC;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const unsigned grid = (unsigned)((num_tiles(B) + Cfg::TPC - 1) / Cfg::TPC);
@@ -47,13 +47,13 @@ static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, c
   return check_launch("kf_forward_pipe_kernel");
 }
 
-template <typename T, int N, int P, int AM>
+template <typename T, int N, int P, int AM, int OP = 0>
 static int launch_bwd_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, T* smth,
                            T* ym, T* yv, int* status, cudaStream_t st) {
   using Auto = AutoCfg<T, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD>;
   if (!Auto::ok) return EKSB_EDIM;
   using Cfg = typename Auto::type;
-  auto kern = rts_backward_pipe_kernel<T, N, P, AM, Cfg>;
+  auto kern = rts_backward_pipe_kernel<T, N, P, AM, OP, Cfg>;
   const size_t smem = Auto::kTileSmem * Cfg::TPC;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const unsigned grid = (unsigned)((num_tiles(B) + Cfg::TPC - 1) / Cfg::TPC);
@@ -90,6 +90,28 @@ int rts_backward_pipe(const T* filt, const T* C, const T* A, const T* Q, int sha
                : launch_bwd_pipe<T, N_, P_, 1>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
   EKSB_FOR_EACH_PIPE_DIM(X)
 #undef X
+  return EKSB_EDIM;
+}
+#endif
+
+#ifdef EKSB_PIPE_BTD
+// A7: forward elimination then back-substitution; `work` receives (z_t, M_t^-1), `sol` (x_t, Sig_t)
+template <typename T>
+int btd_solve_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B,
+                   long Tn, int n, int p, int a_mode, T* work, T* sol, T* ym, int* status, cudaStream_t st) {
+#define X(N_, P_)                                                                                                       \
+  if (n == N_ && p == P_) {                                                                                             \
+    int rc = a_mode == EKSB_A_DIAG                                                                                      \
+                 ? launch_fwd_pipe<T, N_, P_, 0, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, kPriorUpdate, work, status, st) \
+                 : launch_fwd_pipe<T, N_, P_, 1, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, kPriorUpdate, work, status, st); \
+    if (rc != EKSB_OK) return rc;                                                                                       \
+    return a_mode == EKSB_A_DIAG                                                                                        \
+               ? launch_bwd_pipe<T, N_, P_, 0, 1>(work, C, A, Q, shared_mask, B, Tn, sol, ym, nullptr, status, st)      \
+               : launch_bwd_pipe<T, N_, P_, 1, 1>(work, C, A, Q, shared_mask, B, Tn, sol, ym, nullptr, status, st);     \
+  }
+  EKSB_FOR_EACH_PIPE_DIM(X)
+#undef X
+  set_error("btd_solve: (n=%d,p=%d) not instantiated (state dim <= 4)", n, p);
   return EKSB_EDIM;
 }
 #endif

@@ -248,3 +248,20 @@ def rts_backward(filt, prm: TrackParams, B, T, inplace=False, want_ym=True, want
     check(fn(_ptr(filt), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), prm.shared_mask, B, T, n, p, prm.a_mode, _ptr(smth),
              _ptr(ym), _ptr(yv), _ptr(cv), _ptr(status), _stream(dev)), "eksb_rts_backward")
     return dict(smth=smth, ym=ym, yv=yv, cv=cv, status=status)
+
+
+# ------------------------------------------------------------------ A7 block-tridiagonal solve
+def btd_solve(obs, prm: TrackParams, B, T, want_ym=False, inplace=True, status=None):
+    """Block-tridiagonal Newton step.  prm.C is the observation matrix B, prm.Q the process noise E.
+    Returns dict(sol [x | diag blocks of H^-1, state-record layout], ym, status)."""
+    _need_cuda(obs, "obs")
+    dev, dt = obs.device, obs.dtype
+    work = alloc_records(B, T, sigma(prm.n), dt, dev)
+    sol = work if inplace else torch.empty_like(work)
+    ym = alloc_records(B, T, prm.p, dt, dev) if want_ym else None
+    if status is None:
+        status = torch.zeros(B, dtype=torch.int32, device=dev)
+    fn = getattr(lib(), f"eksb_btd_solve_{_sfx(dt)}")
+    check(fn(_ptr(obs), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.A), _ptr(prm.C), _ptr(prm.Q), prm.shared_mask, B, T,
+             prm.n, prm.p, prm.a_mode, _ptr(work), _ptr(sol), _ptr(ym), _ptr(status), _stream(dev)), "eksb_btd_solve")
+    return dict(sol=sol, ym=ym, status=status)

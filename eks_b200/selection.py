@@ -1,0 +1,67 @@
+"""Smoothing-parameter selection by negative log-likelihood, z-scores, and the multi-GPU plumbing
+for them.  The reference has none of this (its smoothing parameter is a CLI
+flag, scripts/multicam_example.py:38-43); definitions are the build's own:
+
+    NLL(s) = 1/2 sum_t [ log det Sig_t + nu_t^T Sig_t^-1 nu_t + p log 2 pi ],  Sig_t = R_t + C S_pred C^T
+    (the matrix of eks/ensemble_kalman.py:112 and the innovation of :102), with Q = s * Q0.
+
+Tracks shard independently across GPUs (one process per GPU); the ONLY collective is one
+all-reduce(SUM) of the (n_grid,) float64 vector of per-GPU NLL sums, after which every rank takes
+the same argmin.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib, device as dev
+from ._lib import check, lib
+
+
+def shard_bounds(n_tracks, rank, world):
+    """Contiguous block of tracks owned by `rank` (sizes differ by at most one)."""
+    base, extra = divmod(n_tracks, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def allreduce_sum_(vec):
+    """In-place SUM over all ranks when torch.distributed is initialised (NCCL on GPUs, gloo in CPU tests)."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(vec, op=dist.ReduceOp.SUM)
+    return vec
+
+
+def nll_grid(obs, prm, B, T, s_grid):
+    """(n_grid,B) float64 NLL of every local track for Q = s*prm.Q, one launch (grid.y = n_grid)."""
+    q = torch.as_tensor(np.asarray(s_grid, dtype=np.float64), dtype=obs.dtype).to(obs.device)
+    _, nll, status = dev.kf_forward(obs, prm, B, T, q_scale=q, want_filt=False, want_nll=True)
+    return nll, status
+
+
+def nll_sums(nll):
+    """(n_grid,B) -> (n_grid,) on the device with the library's deterministic row reduction."""
+    G, B = nll.shape
+    out = torch.empty(G, dtype=torch.float64, device=nll.device)
+    check(lib().eksb_reduce_rows_f64(nll.data_ptr(), G, B, out.data_ptr(),
+                                     torch.cuda.current_stream(nll.device).cuda_stream), "eksb_reduce_rows")
+    return out
+
+
+def select_smooth_param(obs, prm, B, T, s_grid):
+    """Grid search: local NLL sums -> all-reduce over track shards -> argmin.
+    Returns (best_s, total_nll (n_grid,) host array)."""
+    nll, _ = nll_grid(obs, prm, B, T, s_grid)
+    tot = allreduce_sum_(nll_sums(nll))
+    tot_h = tot.cpu().numpy()
+    return float(np.asarray(s_grid)[int(np.argmin(tot_h))]), tot_h
+
+
+def zscore(obs, smth, prm, B, T, add_ev=True):
+    """p-row records of z = (y - C ms)/sqrt(diag(C Vs C^T) [+ ev])."""
+    z = dev.alloc_records(B, T, prm.p, obs.dtype, obs.device)
+    fn = getattr(lib(), f"eksb_zscore_{dev._sfx(obs.dtype)}")
+    check(fn(obs.data_ptr(), smth.data_ptr(), prm.C.data_ptr(), prm.shared_mask, B, T, prm.n, prm.p, int(bool(add_ev)),
+             z.data_ptr(), torch.cuda.current_stream(obs.device).cuda_stream), "eksb_zscore")
+    return z

@@ -174,6 +174,36 @@ EKSB_API int eksb_project_f64(const double* state, int rows, const double* C, in
 EKSB_API int eksb_project_f32(const float* state, int rows, const float* C, int shared_mask, long B, long T, int n, int p,
                      float* ym, void* stream);
 
+/* ---- A7: block-tridiagonal Newton solve -------------------------------------------------
+ * One Newton step from q = 0 (the exact MAP path) of the EKS posterior's block-tridiagonal system
+ * (spec: ref/Kalman_smoother.pdf p.1, Simulations.ipynb[16-20]; the shipped eks/block_tridiag.py:4-43
+ * raises NameError).  Block-Thomas forward elimination + back-substitution, both as TMA-fed
+ * warp-specialised kernels.  Parameter names follow eks/block_tridiag.py:4: A (n,n), Bmat (p,n) the
+ * observation matrix (shared_mask bit EKSB_SHARED_C), E (n,n) the process noise (bit EKSB_SHARED_Q);
+ * obs holds y and the per-frame ensemble variances D_t (T,p order, unlike :16's (p,T)).
+ *   work (state-record layout): (z_t, M_t^-1) forward factors
+ *   sol  (state-record layout, may alias work): rows [0,n) = x_t = the Newton step == RTS mean;
+ *        rows [n, ..) = diagonal block t of H^-1, packed == RTS covariance
+ *   ym   optional p-row records: Bmat x_t
+ * State dim n <= 4 (pipelined instantiations only). */
+EKSB_API int eksb_btd_solve_f64(const double* obs, const double* m0, const double* S0, const double* A, const double* Bmat,
+                       const double* E, int shared_mask, long B, long T, int n, int p, int a_mode, double* work,
+                       double* sol, double* ym, int* status, void* stream);
+EKSB_API int eksb_btd_solve_f32(const float* obs, const float* m0, const float* S0, const float* A, const float* Bmat,
+                       const float* E, int shared_mask, long B, long T, int n, int p, int a_mode, float* work,
+                       float* sol, float* ym, int* status, void* stream);
+
+/* ---- A8: z-score and the NLL reduction for smoothing-parameter selection (absent from the
+ * reference: build-side definitions; the NLL itself comes from eksb_kf_forward) ----
+ * z (p-row records) = (y - C ms) / sqrt(diag(C Vs C^T) + add_ev * ev). */
+EKSB_API int eksb_zscore_f64(const double* obs, const double* smth, const double* C, int shared_mask, long B, long T, int n, int p,
+                    int add_ev, double* z, void* stream);
+EKSB_API int eksb_zscore_f32(const float* obs, const float* smth, const float* C, int shared_mask, long B, long T, int n, int p,
+                    int add_ev, float* z, void* stream);
+/* out[g] = sum over the B tracks of nll[g][:] (deterministic order): the per-GPU partial sums that
+ * are all-reduced (NCCL, SUM) across track shards before the argmin over the grid. */
+EKSB_API int eksb_reduce_rows_f64(const double* in, int rows, long B, double* out, void* stream);
+
 /* EKSB_DECLS_END (new declarations go above this line) */
 #ifdef __cplusplus
 }

@@ -91,3 +91,22 @@ def kf_rts_split(y, ev, m0, S0, C, A, Q, dtype=np.float64, first=1):
     if rc < 0:
         raise ValueError(f"unsupported dims n={n} p={p}")
     return dict(rc=rc, mf=filt[:, :n], Vf=sym_unpack(filt[:, n:], n), ms=smth[:, :n], Vs=sym_unpack(smth[:, n:], n))
+
+
+def btd(y, ev, m0, S0, C, A, Q, dtype=np.float64):
+    """Host build of the block-tridiagonal solve (fwd_prep + btd_fwd_chain, btd_bwd_prep + bwd_chain)."""
+    T, p = y.shape
+    n = m0.shape[0]
+    c = lambda a: np.ascontiguousarray(a, dtype=dtype)
+    am = a_mode(A)
+    y, ev, m0, S0, C, A, Q = map(c, (y, ev, m0, S0, C, A, Q))
+    sg = n + n * (n + 1) // 2
+    work = np.zeros((T, sg), dtype=dtype)
+    sol = np.zeros((T, sg), dtype=dtype)
+    fn = lib().hs_btd_f64 if dtype == np.float64 else lib().hs_btd_f32
+    P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    rc = fn(ctypes.c_int(n), ctypes.c_int(p), ctypes.c_int(am), ctypes.c_long(T), P(y), P(ev), P(m0), P(S0), P(C),
+            P(A), P(Q), P(work), P(sol))
+    if rc < 0:
+        raise ValueError(f"unsupported dims n={n} p={p}")
+    return dict(rc=rc, x=sol[:, :n], Sig=sym_unpack(sol[:, n:], n))

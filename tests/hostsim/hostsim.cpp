@@ -110,3 +110,62 @@ extern "C" int hs_split_f32(int n, int p, int am, long Tn, const float* y, const
                             float* smth) {
   return dispatch_split<float>(n, p, am, Tn, y, ev, m0, S0, C, A, Q, first, filt, smth);
 }
+
+// ---- block-tridiagonal solve through the same prep/chain pieces the kernels use ----
+template <typename T, int N, int P, int AM>
+static int run_btd(long Tn, const T* y, const T* ev, const T* m0, const T* S0, const T* C, const T* A, const T* Q,
+                   T* work, T* sol) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
+  Params<T, N, P, AM> prm;
+  load_params<T, N, P, AM>(prm, C, A, Q);
+  bool ok = true;
+  BtdConst<T, N> c;
+  btd_make_const<T, N, P, AM>(prm, c, ok);
+  T S0p[NS], iS0[NS], iS0m0[N];
+  load_sym<T, N>(S0p, S0);
+  sym_inv<T, N>(S0p, iS0, ok);
+  sym_matvec<T, N>(iS0, m0, iS0m0);
+  T z[N], iM[NS];
+  for (int i = 0; i < N; ++i) z[i] = T(0);
+  for (int i = 0; i < NS; ++i) iM[i] = T(0);
+  for (long t = 0; t < Tn; ++t) {
+    T rec[Rec<N>::FWD];
+    fwd_prep<T, N, P, AM>(prm, y + t * P, ev + t * P, rec);
+    btd_fwd_chain<T, N>(c, rec, t == 0, t == Tn - 1, iS0, iS0m0, z, iM, ok);
+    for (int i = 0; i < N; ++i) work[t * SG + i] = z[i];
+    for (int i = 0; i < NS; ++i) work[t * SG + N + i] = iM[i];
+  }
+  T x[N], Sg[NS];
+  for (int i = 0; i < N; ++i) x[i] = T(0);
+  for (int i = 0; i < NS; ++i) Sg[i] = T(0);
+  for (long t = Tn - 1; t >= 0; --t) {
+    T rec[Rec<N>::BWD];
+    btd_bwd_prep<T, N>(c, work + t * SG, work + t * SG + N, t == Tn - 1, rec);
+    bwd_chain<T, N>(rec, x, Sg);
+    for (int i = 0; i < N; ++i) sol[t * SG + i] = x[i];
+    for (int i = 0; i < NS; ++i) sol[t * SG + N + i] = Sg[i];
+  }
+  return ok ? 0 : 1;
+}
+
+template <typename T>
+static int dispatch_btd(int n, int p, int am, long Tn, const T* y, const T* ev, const T* m0, const T* S0, const T* C,
+                        const T* A, const T* Q, T* work, T* sol) {
+#define X(N_, P_)                                                                  \
+  if (n == N_ && p == P_)                                                          \
+    return am ? run_btd<T, N_, P_, 1>(Tn, y, ev, m0, S0, C, A, Q, work, sol)        \
+              : run_btd<T, N_, P_, 0>(Tn, y, ev, m0, S0, C, A, Q, work, sol);
+  EKSB_FOR_EACH_DIM(X)
+#undef X
+  return -1;
+}
+
+extern "C" int hs_btd_f64(int n, int p, int am, long Tn, const double* y, const double* ev, const double* m0,
+                          const double* S0, const double* C, const double* A, const double* Q, double* work,
+                          double* sol) {
+  return dispatch_btd<double>(n, p, am, Tn, y, ev, m0, S0, C, A, Q, work, sol);
+}
+extern "C" int hs_btd_f32(int n, int p, int am, long Tn, const float* y, const float* ev, const float* m0,
+                          const float* S0, const float* C, const float* A, const float* Q, float* work, float* sol) {
+  return dispatch_btd<float>(n, p, am, Tn, y, ev, m0, S0, C, A, Q, work, sol);
+}

@@ -149,3 +149,104 @@ def test_inplace_smoothing_equals_out_of_place():
     a = dev.rts_backward(filt, c["prm"], 40, 150)
     b = dev.rts_backward(filt.clone(), c["prm"], 40, 150, inplace=True)
     assert torch.equal(a["smth"], b["smth"]) and torch.equal(a["ym"], b["ym"])
+
+
+@pytest.mark.parametrize("name", ["p4", "p6", "p8", "n2p4", "n4p6", "T2", "T1"])
+def test_block_tridiagonal_solve_equals_rts(name):
+    """A7 through the reference-named entry point: Newton step == RTS mean, H^-1 blocks == Vs."""
+    from eks_b200.block_tridiag import Block_thomas_algo
+    c = CORE[name]
+    s, cov = Block_thomas_algo(c["y"], c["m0"], c["S0"], c["A"], c["C"], c["Q"], c["ev"], return_cov=True)
+    want_m, want_V = (c["ms"], c["Vs"]) if "ms" in c else (c["mf"], c["Vf"])
+    assert rel(s, want_m) < 1e-9 and rel(cov, want_V) < 1e-9
+    assert rel(s, o.btd_solve(c["y"], c["m0"], c["S0"], c["A"], c["C"], c["Q"], c["ev"])) < 1e-9
+
+
+def test_block_tridiagonal_batched_f32_and_dense_A():
+    import torch
+    from eks_b200 import device as dev
+    for dtname, tol, a_diag in (("float32", 2e-3, True), ("float64", 1e-9, False)):
+        dt = getattr(torch, dtname)
+        B, T, p, n = 45, 131, 4, 3
+        c = _random_batch(B, T, p, n, dt, seed=11, a_diag=a_diag)
+        out = dev.btd_solve(c["obs"], c["prm"], B, T, want_ym=True)
+        assert int(out["status"].sum()) == 0
+        x = dev.unpack_rows(out["sol"], dev.sigma(n), 0, B, T, n).cpu().numpy().astype(np.float64)
+        ymv = dev.unpack_rows(out["ym"], p, 0, B, T, p).cpu().numpy().astype(np.float64)
+        for b in (0, 33, B - 1):
+            yq = c["y"].astype(np.float32).astype(np.float64) if dtname == "float32" else c["y"]
+            evq = c["ev"].astype(np.float32).astype(np.float64) if dtname == "float32" else c["ev"]
+            want = o.btd_solve(yq[b], c["m0"], c["S0"], c["A"], c["C"][b], c["Q"], evq[b])
+            assert rel(x[b], want) < tol and rel(ymv[b], want @ c["C"][b].T) < tol
+
+
+def test_nll_grid_zscore_and_selection():
+    import torch
+    from eks_b200 import device as dev, selection as sel
+    B, T, p, n = 37, 120, 4, 3
+    c = _random_batch(B, T, p, n, torch.float64, seed=21)
+    grid = [0.1, 0.5, 1.0, 4.0, 20.0]
+    nll, st = sel.nll_grid(c["obs"], c["prm"], B, T, grid)
+    assert nll.shape == (len(grid), B) and int(st.sum()) == 0
+    nll_h = nll.cpu().numpy()
+    for gi, s in enumerate(grid):
+        for b in (0, 36):
+            want = o.nll(c["y"][b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], s * c["Q"], c["ev"][b])
+            assert abs(nll_h[gi, b] - want) < 1e-8 * abs(want)
+    sums = sel.nll_sums(nll).cpu().numpy()
+    np.testing.assert_allclose(sums, nll_h.sum(axis=1), rtol=1e-12)
+    best, tot = sel.select_smooth_param(c["obs"], c["prm"], B, T, grid)
+    assert best == grid[int(np.argmin(nll_h.sum(axis=1)))]
+    # z-score of the smoothed path
+    filt, _, _ = dev.kf_forward(c["obs"], c["prm"], B, T)
+    out = dev.rts_backward(filt, c["prm"], B, T)
+    for add_ev in (True, False):
+        z = dev.unpack_rows(sel.zscore(c["obs"], out["smth"], c["prm"], B, T, add_ev), p, 0, B, T, p).cpu().numpy()
+        b = 5
+        mf, Vf, S = o.filtering_pass(c["y"][b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], c["ev"][b])
+        ms, Vs, _ = o.smooth_backward(c["y"][b], mf, Vf, S, c["A"], c["Q"], c["C"][b])
+        np.testing.assert_allclose(z[b], o.zscore(c["y"][b], ms, Vs, c["C"][b], c["ev"][b], add_ev), rtol=1e-8, atol=1e-10)
+
+
+def test_track_sharding_is_bitwise_identical_to_one_batch():
+    """(e) multi-GPU: tracks are independent, so a shard processed alone gives bit-identical results
+    to the same tracks inside the full batch, and shard NLL sums add up to the global sum."""
+    import torch
+    from eks_b200 import device as dev, selection as sel
+    B, T, p, n = 96, 90, 4, 3
+    c = _random_batch(B, T, p, n, torch.float64, seed=31)
+    full, _, _ = dev.kf_forward(c["obs"], c["prm"], B, T)
+    full = dev.rts_backward(full, c["prm"], B, T, inplace=True)["smth"]
+    ms_full = dev.unpack_rows(full, dev.sigma(n), 0, B, T, dev.sigma(n))
+    grid = [0.3, 1.0, 3.0]
+    tot_full = sel.nll_sums(sel.nll_grid(c["obs"], c["prm"], B, T, grid)[0]).cpu().numpy()
+    acc = np.zeros(len(grid))
+    for rank in range(3):
+        lo, hi = sel.shard_bounds(B, rank, 3)
+        assert lo % 32 == 0
+        d = c["obs"].device
+        prm = dev.TrackParams.from_numpy(c["m0"], c["S0"], c["C"][lo:hi], c["A"], c["Q"], device=d)
+        obs = dev.pack_obs(torch.as_tensor(c["y"][lo:hi]).to(d), torch.as_tensor(c["ev"][lo:hi]).to(d))
+        f, _, _ = dev.kf_forward(obs, prm, hi - lo, T)
+        s = dev.rts_backward(f, prm, hi - lo, T, inplace=True)["smth"]
+        got = dev.unpack_rows(s, dev.sigma(n), 0, hi - lo, T, dev.sigma(n))
+        assert torch.equal(got, ms_full[lo:hi])
+        acc += sel.nll_sums(sel.nll_grid(obs, prm, hi - lo, T, grid)[0]).cpu().numpy()
+    np.testing.assert_allclose(acc, tot_full, rtol=1e-12)
+
+
+def test_batched_host_api_matches_oracle():
+    import torch
+    from eks_b200 import batched
+    B, T, p, n = 70, 140, 4, 3
+    c = _random_batch(B, T, p, n, torch.float64, seed=41)
+    cnt = {}
+    out = batched.smooth_tracks(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], block_tracks=32, counters=cnt)
+    assert cnt["launches"] == 7 * 3 and cnt["h2d_bytes"] == 2 * B * T * p * 8
+    iu = np.triu_indices(n)
+    for b in (0, 31, 32, 69):
+        mf, Vf, S = o.filtering_pass(c["y"][b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], c["ev"][b])
+        ms, Vs, _ = o.smooth_backward(c["y"][b], mf, Vf, S, c["A"], c["Q"], c["C"][b])
+        assert rel(out["ms"][b].numpy(), ms) < 1e-9 and rel(out["Vs"][b].numpy(), Vs[:, iu[0], iu[1]]) < 1e-9
+        assert rel(out["ym"][b].numpy(), ms @ c["C"][b].T) < 1e-9
+    assert int(out["status"].sum()) == 0

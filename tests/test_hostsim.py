@@ -79,3 +79,19 @@ def test_split_form_real_data(dtype, tol):
         ms, Vs, _ = o.smooth_backward(st["y"], mf, Vf, S, st["A"], st["Q"], st["C"])
         r = hostsim.kf_rts_split(st["y"], st["ev"], st["m0"], st["S0"], st["C"], st["A"], st["Q"], dtype=dtype)
         assert rel(r["ms"], ms) < tol and rel(r["Vs"], Vs) < tol and rel(r["mf"], mf) < tol
+
+
+@pytest.mark.parametrize("name", [k for k in KF_CASES if "ms" in CORE[k]] + ["T1"])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 2e-3)])
+def test_block_tridiagonal_solve_equals_rts(name, dtype, tol):
+    """A7: one Newton step of the block-tridiagonal system == RTS mean, H^-1 diagonal blocks == Vs
+    (SURVEY fact 0.8), and == the oracle's block-Thomas restatement."""
+    c = CORE[name]
+    r = hostsim.btd(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], dtype=dtype)
+    assert r["rc"] == 0
+    if "ms" in c:
+        assert rel(r["x"], c["ms"]) < tol and rel(r["Sig"], c["Vs"]) < tol
+    else:
+        assert rel(r["x"], c["mf"]) < tol and rel(r["Sig"], c["Vf"]) < tol     # T == 1: smoother == filter
+    x = o.btd_solve(c["y"], c["m0"], c["S0"], c["A"], c["C"], c["Q"], c["ev"])
+    assert rel(r["x"], x) < tol
