@@ -21,7 +21,7 @@ _CTYPES = {
     "int": ctypes.c_int, "long": ctypes.c_long, "double": ctypes.c_double, "float": ctypes.c_float,
     "void*": ctypes.c_void_p, "int*": ctypes.c_void_p, "double*": ctypes.c_void_p, "float*": ctypes.c_void_p,
     "const double*": ctypes.c_void_p, "const float*": ctypes.c_void_p, "const int*": ctypes.c_void_p,
-    "const char*": ctypes.c_char_p,
+    "const char*": ctypes.c_char_p, "size_t": ctypes.c_size_t,
 }
 
 

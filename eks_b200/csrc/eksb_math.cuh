@@ -788,4 +788,184 @@ EKSB_HD void btd_bwd_prep(const BtdConst<T, N>& c, const T* z, const T* iM, bool
   for (int k = 0; k < NS; ++k) rec[N * N + k] = iM[k];
 }
 
+// ---------------------------------------------------------------------------
+// Parallel-in-time (K4): exact chunked scan for long tracks.  Time is cut into chunks; a chunk's
+// effect on the filter is summarised by the element (Phi, b, C, eta, J) of Sarkka &
+// Garcia-Fernandez (IEEE TAC 2021): given the state x_s just before the chunk,
+//     x_end | x_s, y_chunk ~ N(Phi x_s + b, C),     p(y_chunk | x_s)  ~ exp(-1/2 x_s^T J x_s + eta^T x_s).
+// Instead of the generic element combine (a 3x3 inverse + ~8 products per frame) the summary is
+// accumulated sequentially inside the chunk by running the ordinary filter from an exactly known
+// start (mean 0, covariance 0) and carrying the sensitivity Phi of its mean to x_s:
+//     G  = V S^-1            (V, S^-1 from the ordinary step;  I - V I_t = V S^-1)
+//     X  = S^-1 - S^-1 V S^-1 = H^T (R + H S H^T)^-1 H          (innovation information)
+//     Psi = A Phi;  J += Psi^T X Psi;  eta += Psi^T S^-1 (m_new - A b_old);  Phi = G Psi
+// which costs ~2.4x a filter step.  Summaries of consecutive chunks are then folded per track
+// (fwd_apply_summary), and every chunk is re-run from its now exact start state.
+// The smoother's chunk summary is the (E, g, L) element: ms[t0] = E ms[t1] + g, Vs[t0] = E Vs[t1] E^T + L.
+// ---------------------------------------------------------------------------
+template <int N> struct ScanRec {
+  static constexpr int NS = Dim<N>::NS;
+  static constexpr int FWD = N * N + N + NS + N + NS;   // Phi | b | C | eta | J
+  static constexpr int BWD = N * N + NS + N;            // E | L | g   (same order as Rec<N>::BWD)
+};
+
+// One frame of the forward chunk summary.  (b, C) are the running filter state started at (0, 0);
+// Phi starts at I, eta and J at 0.
+template <typename T, int N, int P, int AM>
+EKSB_HD void fwd_summary_step(const Params<T, N, P, AM>& prm, const T* rec, T (*Phi)[N], T* b, T* C, T* eta, T* J,
+                              bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T mp[N], S[NS], Sinv[NS], Lam[NS], V[NS], u[N], Vu[N];
+  predict<T, N, P, AM>(prm, b, C, mp, S);
+  sym_matvec<T, N>(rec, mp, u);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
+  sym_inv<T, N>(S, Sinv, ok);
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) Lam[k] = Sinv[k] + rec[k];
+  sym_inv<T, N>(Lam, V, ok);
+  sym_matvec<T, N>(V, u, Vu);
+  // Psi = A Phi
+  T Psi[N][N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      if (AM == 0) {
+        Psi[i][j] = prm.A[i] * Phi[i][j];
+      } else {
+        T s = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) s += prm.A[i * N + k] * Phi[k][j];
+        Psi[i][j] = s;
+      }
+    }
+  }
+  // SV = S^-1 V (full);  X = S^-1 - SV S^-1 (symmetric)
+  T SV[N][N], X[NS];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += Sinv[sym_idx<N>(i, k)] * V[sym_idx<N>(k, j)];
+      SV[i][j] = s;
+    }
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = i; j < N; ++j) {
+      T s = Sinv[sym_idx<N>(i, j)];
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s -= SV[i][k] * Sinv[sym_idx<N>(k, j)];
+      X[sym_idx<N>(i, j)] = s;
+    }
+  }
+  // J += Psi^T X Psi ; eta += Psi^T S^-1 (V u)
+  T XP[N][N], w[N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += X[sym_idx<N>(i, k)] * Psi[k][j];
+      XP[i][j] = s;
+    }
+  }
+  sym_matvec<T, N>(Sinv, Vu, w);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = i; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += Psi[k][i] * XP[k][j];
+      J[sym_idx<N>(i, j)] += s;
+    }
+    T e = T(0);
+    EKSB_UNROLL
+    for (int k = 0; k < N; ++k) e += Psi[k][i] * w[k];
+    eta[i] += e;
+  }
+  // Phi = (S^-1 V)^T Psi = V S^-1 A Phi ;  state update
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += SV[k][i] * Psi[k][j];
+      Phi[i][j] = s;
+    }
+    b[i] = mp[i] + Vu[i];
+  }
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) C[k] = V[k];
+}
+
+// Fold a chunk summary into the filtered state just before the chunk: (m,P) -> state at the chunk's end.
+template <typename T, int N>
+EKSB_HD void fwd_apply_summary(const T* sum, T* m, T* P, bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  const T* Phi = sum;                 // N*N row-major
+  const T* b = sum + N * N;
+  const T* C = b + N;
+  const T* eta = C + NS;
+  const T* J = eta + N;
+  T Pinv[NS], Lam[NS], P1[NS], r[N], m1[N], Jm[N];
+  sym_inv<T, N>(P, Pinv, ok);
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) Lam[k] = Pinv[k] + J[k];
+  sym_inv<T, N>(Lam, P1, ok);         // cov of x_s given the chunk's data
+  sym_matvec<T, N>(J, m, Jm);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) r[i] = eta[i] - Jm[i];
+  sym_matvec<T, N>(P1, r, m1);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) m1[i] += m[i];
+  T Phim[N][N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    T s = b[i];
+    EKSB_UNROLL
+    for (int k = 0; k < N; ++k) { s += Phi[i * N + k] * m1[k]; Phim[i][k] = Phi[i * N + k]; }
+    m[i] = s;
+  }
+  T PPP[NS];
+  sandwich<T, N>(Phim, P1, PPP);
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) P[k] = PPP[k] + C[k];
+}
+
+// Compose one more (earlier) frame element (J,L,g) onto the chunk's smoothing summary (E,L,g).
+template <typename T, int N>
+EKSB_HD void bwd_summary_step(const T* rec, T* acc) {
+  constexpr int NS = Dim<N>::NS;
+  T Jm[N][N], En[N][N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) Jm[i][j] = rec[i * N + j];
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T s = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) s += Jm[i][k] * acc[k * N + j];
+      En[i][j] = s;
+    }
+  }
+  bwd_chain<T, N>(rec, acc + N * N + NS, acc + N * N);     // g = g_t + J g_acc ; L = L_t + J L_acc J^T
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) acc[i * N + j] = En[i][j];
+  }
+}
+
 }  // namespace eksb

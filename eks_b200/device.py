@@ -265,3 +265,24 @@ def btd_solve(obs, prm: TrackParams, B, T, want_ym=False, inplace=True, status=N
     check(fn(_ptr(obs), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.A), _ptr(prm.C), _ptr(prm.Q), prm.shared_mask, B, T,
              prm.n, prm.p, prm.a_mode, _ptr(work), _ptr(sol), _ptr(ym), _ptr(status), _stream(dev)), "eksb_btd_solve")
     return dict(sol=sol, ym=ym, status=status)
+
+
+# ------------------------------------------------------------------ K4 parallel-in-time scan
+def kf_rts_scan(obs, prm: TrackParams, B, T, chunk=0, smooth=True, inplace=True, want_ym=True, status=None):
+    """Filter (+ RTS smoother) by the exact chunked scan over time; for few, very long tracks.
+    Returns dict(filt, smth, ym, status, chunk)."""
+    _need_cuda(obs, "obs")
+    dev, dt = obs.device, obs.dtype
+    es = obs.element_size()
+    nbytes = lib().eksb_scan_workspace_bytes(B, T, prm.n, chunk, es)
+    ws = torch.empty(max(1, nbytes // es), dtype=dt, device=dev)
+    filt = alloc_records(B, T, sigma(prm.n), dt, dev)
+    smth = (filt if inplace else torch.empty_like(filt)) if smooth else None
+    ym = alloc_records(B, T, prm.p, dt, dev) if (smooth and want_ym) else None
+    if status is None:
+        status = torch.zeros(B, dtype=torch.int32, device=dev)
+    fn = getattr(lib(), f"eksb_kf_rts_scan_{_sfx(dt)}")
+    check(fn(_ptr(obs), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), prm.shared_mask, B, T, prm.n,
+             prm.p, prm.a_mode, chunk, _ptr(ws), nbytes, _ptr(filt), _ptr(smth), _ptr(ym), _ptr(status), _stream(dev)),
+          "eksb_kf_rts_scan")
+    return dict(filt=filt, smth=smth, ym=ym, status=status, chunk=int(lib().eksb_scan_chunk_len(B, T, chunk)))

@@ -250,3 +250,33 @@ def test_batched_host_api_matches_oracle():
         assert rel(out["ms"][b].numpy(), ms) < 1e-9 and rel(out["Vs"][b].numpy(), Vs[:, iu[0], iu[1]]) < 1e-9
         assert rel(out["ym"][b].numpy(), ms @ c["C"][b].T) < 1e-9
     assert int(out["status"].sum()) == 0
+
+
+@pytest.mark.parametrize("dtname,tol", [("float64", 1e-9), ("float32", 2e-3)])
+@pytest.mark.parametrize("B,T,chunk", [(3, 1000, 64), (40, 777, 100), (2, 5000, 0), (33, 129, 200)])
+def test_parallel_in_time_scan_equals_sequential(dtname, tol, B, T, chunk):
+    """K4: the chunked scan reproduces the sequential kernels (and through them the oracle),
+    for ragged last chunks, auto chunk length and a single chunk (chunk > T)."""
+    import torch
+    from eks_b200 import device as dev
+    dt = getattr(torch, dtname)
+    p, n = 4, 3
+    c = _random_batch(B, T, p, n, dt, seed=B + T)
+    filt, _, _ = dev.kf_forward(c["obs"], c["prm"], B, T)
+    mf_seq = dev.unpack_rows(filt, dev.sigma(n), 0, B, T, dev.sigma(n)).cpu().numpy().astype(np.float64)
+    seq = dev.rts_backward(filt, c["prm"], B, T)
+    ms_seq = dev.unpack_rows(seq["smth"], dev.sigma(n), 0, B, T, dev.sigma(n)).cpu().numpy().astype(np.float64)
+    ym_seq = dev.unpack_rows(seq["ym"], p, 0, B, T, p).cpu().numpy().astype(np.float64)
+    f_only = dev.kf_rts_scan(c["obs"], c["prm"], B, T, chunk=chunk, smooth=False)
+    mf_scan = dev.unpack_rows(f_only["filt"], dev.sigma(n), 0, B, T, dev.sigma(n)).cpu().numpy().astype(np.float64)
+    assert rel(mf_scan, mf_seq) < tol
+    out = dev.kf_rts_scan(c["obs"], c["prm"], B, T, chunk=chunk)
+    assert int(out["status"].sum()) == 0
+    ms_scan = dev.unpack_rows(out["smth"], dev.sigma(n), 0, B, T, dev.sigma(n)).cpu().numpy().astype(np.float64)
+    ym_scan = dev.unpack_rows(out["ym"], p, 0, B, T, p).cpu().numpy().astype(np.float64)
+    assert rel(ms_scan, ms_seq) < tol and rel(ym_scan, ym_seq) < tol
+    if dtname == "float64":
+        b = B - 1
+        mf, Vf, S = o.filtering_pass(c["y"][b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], c["ev"][b])
+        ms, Vs, _ = o.smooth_backward(c["y"][b], mf, Vf, S, c["A"], c["Q"], c["C"][b])
+        assert rel(ms_scan[b][:, :n], ms) < 1e-8

@@ -95,3 +95,15 @@ def test_block_tridiagonal_solve_equals_rts(name, dtype, tol):
         assert rel(r["x"], c["mf"]) < tol and rel(r["Sig"], c["Vf"]) < tol     # T == 1: smoother == filter
     x = o.btd_solve(c["y"], c["m0"], c["S0"], c["A"], c["C"], c["Q"], c["ev"])
     assert rel(r["x"], x) < tol
+
+
+@pytest.mark.parametrize("name,chunk", [("p4", 16), ("p4", 257), ("p4", 300), ("p8", 7), ("n2p4", 5), ("n4p6", 9), ("T2", 1)])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 2e-3)])
+def test_chunked_scan_equals_sequential(name, chunk, dtype, tol):
+    """K4: summaries + fold + re-run reproduce the sequential filter and smoother exactly
+    (any chunk length, including ragged last chunks and a single chunk)."""
+    c = CORE[name]
+    r = hostsim.scan(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], chunk, dtype=dtype)
+    assert r["rc"] == 0
+    for k in ("mf", "Vf", "ms", "Vs"):
+        assert rel(r[k], c[k]) < tol, k
