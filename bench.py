@@ -197,7 +197,7 @@ def committed_traffic(dtype):
     """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        return t.get(dtype)
+        return t[dtype]["dram_bytes"]
     except Exception:
         return None
 

@@ -14,7 +14,8 @@ import os
 import re
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libeksb.so")
+# EKSB_LIBRARY: developer override to load a tuning build of the same library (tools/tune.sh)
+LIB_PATH = os.environ.get("EKSB_LIBRARY") or os.path.join(_HERE, "libeksb.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "eksb.h")
 
 _CTYPES = {

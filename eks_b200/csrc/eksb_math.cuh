@@ -147,6 +147,30 @@ template <typename T, int N> struct SymInv {
 
 template <typename T, int N> EKSB_HD T sym_inv(const T* a, T* inv, bool& ok) { return SymInv<T, N>::run(a, inv, ok); }
 
+// Adjugate and determinant of a general (non-symmetric) N x N matrix, N <= 3:  M^-1 = adj / det.
+template <typename T, int N> EKSB_HD void gen_adjugate(const T M[N][N], T adj[N][N], T& det) {
+  if (N == 1) {
+    adj[0][0] = T(1);
+    det = M[0][0];
+  } else if (N == 2) {
+    adj[0][0] = M[1 % N][1 % N]; adj[0][1 % N] = -M[0][1 % N];
+    adj[1 % N][0] = -M[1 % N][0]; adj[1 % N][1 % N] = M[0][0];
+    det = M[0][0] * M[1 % N][1 % N] - M[0][1 % N] * M[1 % N][0];
+  } else {
+    constexpr int a = 1 % N, b = 2 % N;    // (indices written so that N < 3 instantiations still compile)
+    adj[0][0] = M[a][a] * M[b][b] - M[a][b] * M[b][a];
+    adj[0][a] = M[0][b] * M[b][a] - M[0][a] * M[b][b];
+    adj[0][b] = M[0][a] * M[a][b] - M[0][b] * M[a][a];
+    adj[a][0] = M[a][b] * M[b][0] - M[a][0] * M[b][b];
+    adj[a][a] = M[0][0] * M[b][b] - M[0][b] * M[b][0];
+    adj[a][b] = M[0][b] * M[a][0] - M[0][0] * M[a][b];
+    adj[b][0] = M[a][0] * M[b][a] - M[a][a] * M[b][0];
+    adj[b][a] = M[0][a] * M[b][0] - M[0][0] * M[b][a];
+    adj[b][b] = M[0][0] * M[a][a] - M[0][a] * M[a][0];
+    det = M[0][0] * adj[0][0] + M[0][a] * adj[a][0] + M[0][b] * adj[b][0];
+  }
+}
+
 // y = S x  (S packed symmetric)
 template <typename T, int N> EKSB_HD void sym_matvec(const T* S, const T* x, T* y) {
   EKSB_UNROLL
@@ -590,10 +614,41 @@ EKSB_HD void fwd_chain(const Params<T, N, P, AM>& prm, const T* rec, bool do_pre
   sym_matvec<T, N>(rec, mp, u);                   // I mp  (off the covariance chain)
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
-  sym_inv<T, N>(S, Sinv, ok);
-  EKSB_UNROLL
-  for (int k = 0; k < NS; ++k) Lam[k] = Sinv[k] + rec[k];
-  sym_inv<T, N>(Lam, V, ok);
+  if (N <= 3) {
+    // V = (S^-1 + Lam)^-1 = S (Id + Lam S)^-1 : ONE reciprocal on the frame-to-frame dependency
+    // path instead of two (the two nested symmetric inverses cost ~27 dependent DP ops, this ~17;
+    // the forward chain warp is bound by exactly that latency).  det(Id + Lam S) >= 1 for SPD S.
+    T M[N][N];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) {
+        T a = (i == j) ? T(1) : T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) a += rec[sym_idx<N>(i, k)] * S[sym_idx<N>(k, j)];
+        M[i][j] = a;
+      }
+    }
+    T adj[N][N], det;
+    gen_adjugate<T, N>(M, adj, det);
+    ok = ok && (det > T(0)) && (S[0] > T(0));
+    const T r = rcp(det);
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = i; j < N; ++j) {
+        T a = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) a += S[sym_idx<N>(i, k)] * adj[k][j];
+        V[sym_idx<N>(i, j)] = a * r;
+      }
+    }
+  } else {
+    sym_inv<T, N>(S, Sinv, ok);
+    EKSB_UNROLL
+    for (int k = 0; k < NS; ++k) Lam[k] = Sinv[k] + rec[k];
+    sym_inv<T, N>(Lam, V, ok);
+  }
   sym_matvec<T, N>(V, u, Vu);
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) m[i] = mp[i] + Vu[i];

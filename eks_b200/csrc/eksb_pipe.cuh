@@ -60,11 +60,21 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
                : "memory");
 }
 
-// H helper warps per tile, F frames per batch, NST raw batches in flight, TPC tiles per CTA
+// H helper warps per tile, F frames per batch, NST raw batches in flight, at most TPC tiles per CTA
+// (the launch picks the actual tiles per CTA, `tpc` <= TPC, so that tiles spread evenly over the SMs)
 template <int H_, int F_, int NST_, int TPC_> struct PipeCfg {
   static constexpr int H = H_, F = F_, NST = NST_, TPC = TPC_;
-  static constexpr int THREADS = TPC * (H + 1) * kLanes;
-  static_assert(F % H == 0, "helpers split a batch evenly");
+  static constexpr int THREADS = (TPC * (H + 1) + 3) / 4 * 4 * kLanes;   // upper bound incl. filler warps
+};
+
+// Which job each warp of a CTA does.  Warp w of a CTA issues from scheduler (SM sub-partition)
+// w % 4, and with so few warps per SM the pass runs at the pace of the busiest scheduler, so the
+// launch code (eksb_pipe_impl.cuh: make_roles) places chain and helper warps to even out the four
+// schedulers' instruction load instead of using a fixed warp -> role formula.
+constexpr int kMaxWarps = 32;
+struct RoleMap {
+  signed char tile[kMaxWarps];   // tile within the CTA, or -1: idle warp (exits at once)
+  signed char h[kMaxWarps];      // -1: chain warp; 0..H-1: helper index
 };
 
 template <typename T, int ROWS_IN, int REC, typename Cfg> struct PipeSmem {
@@ -84,15 +94,18 @@ template <typename T, int N, int P, int AM, int OP, typename Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS)
 kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                        const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
-                       long B, long Tn, int first, T* __restrict__ filt, int* __restrict__ status) {
+                       long B, long Tn, int first, T* __restrict__ filt, int* __restrict__ status, int tpc,
+                       const __grid_constant__ RoleMap roles) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, REC = Rec<N>::FWD;
-  constexpr int H = Cfg::H, TPC = Cfg::TPC, F = Cfg::F, NST = Cfg::NST;
+  constexpr int H = Cfg::H, F = Cfg::F, NST = Cfg::NST;
+  const int TPC = tpc;
   using SM = PipeSmem<T, R2, REC, Cfg>;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const bool is_chain = warp < TPC;
-  const int tile_in_cta = is_chain ? warp : (warp - TPC) % TPC;
-  const int h = is_chain ? 0 : (warp - TPC) / TPC;
+  const int tile_in_cta = roles.tile[warp];
+  if (tile_in_cta < 0) return;                             // filler warp (keeps w % 4 placement)
+  const bool is_chain = roles.h[warp] < 0;
+  const int h = is_chain ? 0 : roles.h[warp];
   const long g = (long)blockIdx.x * TPC + tile_in_cta;
   if (g >= num_tiles_dev(B)) return;                       // chain + helpers of a tile leave together
   unsigned char* tile_smem = smem_raw + (size_t)tile_in_cta * SM::kTile;
@@ -131,10 +144,12 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
         mbar_wait(&full[st], (uint32_t)((k / NST) & 1));
         const T* src = raw + (size_t)st * F * R2 * kLanes + lane;
         T* dst = recb + (k & 1) * (F * REC * kLanes) + lane;
+        const long rem = Tn - k * F;
+        const int nfr = (int)(rem < F ? rem : F);
 #pragma unroll
-        for (int jj = 0; jj < F / H; ++jj) {
+        for (int jj = 0; jj < (F + H - 1) / H; ++jj) {
           const int j = jj * H + h;
-          if (k * F + j < Tn) {
+          if (j < nfr) {
             T cur[R2], rec[REC];
 #pragma unroll
             for (int r = 0; r < R2; ++r) cur[r] = src[(j * R2 + r) * kLanes];
@@ -182,28 +197,37 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
     for (int i = 0; i < NS; ++i) V[i] = Vi[i];
   }
   T* f = filt + (g * Tn * SG) * kLanes + lane;
+  // one frame of the chain.  FIRST: frame 0 of the track (prior handling); LAST only matters to OP 1.
+  auto frame = [&](const T* src, int j, bool is_first, bool is_last) {
+    T rec[REC];
+#pragma unroll
+    for (int r = 0; r < REC; ++r) rec[r] = src[(j * REC + r) * kLanes];
+    if (OP == 1)
+      btd_fwd_chain<T, N>(bc, rec, is_first, is_last, iS0, iS0m0, m, V, ok);
+    else if (!(is_first && first == kPriorOnly))
+      fwd_chain<T, N, P, AM>(prm, rec, !(is_first && first == kPriorUpdate), m, V, ok);
+    T* o = f + j * (SG * kLanes);
+#pragma unroll
+    for (int i = 0; i < N; ++i) o[i * kLanes] = m[i];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) o[(N + i) * kLanes] = V[i];
+  };
   tile_barrier(bar_id, bar_cnt);                           // (barrier init)
   tile_barrier(bar_id, bar_cnt);                           // batch 0 ready
+  // interior batches (all F frames present, neither frame 0 nor frame T-1 inside): no guards
   for (long k = 0; k < nb; ++k) {
     const T* src = recb + (k & 1) * (F * REC * kLanes) + lane;
+    if (k > 0 && (k + 1) * F < Tn) {
 #pragma unroll
-    for (int j = 0; j < F; ++j) {
-      const long t = k * F + j;
-      if (t < Tn) {
-        T rec[REC];
+      for (int j = 0; j < F; ++j) frame(src, j, false, false);
+    } else {
 #pragma unroll
-        for (int r = 0; r < REC; ++r) rec[r] = src[(j * REC + r) * kLanes];
-        if (OP == 1)
-          btd_fwd_chain<T, N>(bc, rec, t == 0, t == Tn - 1, iS0, iS0m0, m, V, ok);
-        else if (!(t == 0 && first == kPriorOnly))
-          fwd_chain<T, N, P, AM>(prm, rec, !(t == 0 && first == kPriorUpdate), m, V, ok);
-        T* o = f + t * SG * kLanes;
-#pragma unroll
-        for (int i = 0; i < N; ++i) o[i * kLanes] = m[i];
-#pragma unroll
-        for (int i = 0; i < NS; ++i) o[(N + i) * kLanes] = V[i];
+      for (int j = 0; j < F; ++j) {
+        const long t = k * F + j;
+        if (t < Tn) frame(src, j, t == 0, t == Tn - 1);
       }
     }
+    f += F * SG * kLanes;
     tile_barrier(bar_id, bar_cnt);                         // batch k consumed / batch k+1 ready
   }
   if (b < B && status && !ok) status[b] = 1;
@@ -216,19 +240,23 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
 // ------------------------------------------------------------------------------------------
 // OP = 0: RTS smoother (A4/A5).  OP = 1: back-substitution + selected inverse of the
 // block-tridiagonal system from the (z_t, M_t^-1) records (btd_bwd_prep); same chain.
-template <typename T, int N, int P, int AM, int OP, typename Cfg>
+// OUT (compile time, so that unused projections cost no issue slots on the chain warp):
+// bit 0 = write ym = C ms, bit 1 = write yv = diag(C Vs C^T).
+template <typename T, int N, int P, int AM, int OP, int OUT, typename Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS)
 rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
                          int shared_mask, long B, long Tn, T* smth, T* __restrict__ ym, T* __restrict__ yv,
-                         int* __restrict__ status) {
+                         int* __restrict__ status, int tpc, const __grid_constant__ RoleMap roles) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, REC = Rec<N>::BWD;
-  constexpr int H = Cfg::H, TPC = Cfg::TPC, F = Cfg::F, NST = Cfg::NST;
+  constexpr int H = Cfg::H, F = Cfg::F, NST = Cfg::NST;
+  const int TPC = tpc;
   using SM = PipeSmem<T, SG, REC, Cfg>;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const bool is_chain = warp < TPC;
-  const int tile_in_cta = is_chain ? warp : (warp - TPC) % TPC;
-  const int h = is_chain ? 0 : (warp - TPC) / TPC;
+  const int tile_in_cta = roles.tile[warp];
+  if (tile_in_cta < 0) return;
+  const bool is_chain = roles.h[warp] < 0;
+  const int h = is_chain ? 0 : roles.h[warp];
   const long g = (long)blockIdx.x * TPC + tile_in_cta;
   if (g >= num_tiles_dev(B)) return;
   unsigned char* tile_smem = smem_raw + (size_t)tile_in_cta * SM::kTile;
@@ -274,7 +302,7 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
         const T* src = raw + (size_t)st * F * SG * kLanes + lane;
         T* dst = recb + (k & 1) * (F * REC * kLanes) + lane;
 #pragma unroll
-        for (int jj = 0; jj < F / H; ++jj) {
+        for (int jj = 0; jj < (F + H - 1) / H; ++jj) {
           const int j = jj * H + h;
           if (j < nfr) {
             const int off = nfr - 1 - j;
@@ -316,47 +344,58 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
   for (int i = 0; i < N; ++i) ms[i] = T(0);
 #pragma unroll
   for (int i = 0; i < NS; ++i) Vs[i] = T(0);
-  T* so = smth + (g * Tn * SG) * kLanes + lane;
-  T* ymo = ym ? ym + (g * Tn * P) * kLanes + lane : nullptr;
-  T* yvo = yv ? yv + (g * Tn * P) * kLanes + lane : nullptr;
-  tile_barrier(bar_id, bar_cnt);                           // (barrier init)
-  tile_barrier(bar_id, bar_cnt);                           // batch 0 ready
-  for (long k = 0; k < nb; ++k) {
-    const T* src = recb + (k & 1) * (F * REC * kLanes) + lane;
+  constexpr bool kYm = (OUT & 1) != 0, kYv = (OUT & 2) != 0;
+  // running output pointers at frame t = T-1 (the first frame the chain emits); they walk down
+  T* so = smth + ((g * Tn + (Tn - 1)) * SG) * kLanes + lane;
+  T* ymo = kYm ? ym + ((g * Tn + (Tn - 1)) * P) * kLanes + lane : nullptr;
+  T* yvo = kYv ? yv + ((g * Tn + (Tn - 1)) * P) * kLanes + lane : nullptr;
+  // one frame of the chain: record j of the current batch -> frame (base pointers) - j
+  auto frame = [&](const T* src, int j) {
+    T rec[REC];
 #pragma unroll
-    for (int j = 0; j < F; ++j) {
-      const long u = k * F + j;
-      if (u < Tn) {
-        const long t = Tn - 1 - u;
-        T rec[REC];
+    for (int r = 0; r < REC; ++r) rec[r] = src[(j * REC + r) * kLanes];
+    bwd_chain<T, N>(rec, ms, Vs);
+    T* o = so - (long)j * (SG * kLanes);
 #pragma unroll
-        for (int r = 0; r < REC; ++r) rec[r] = src[(j * REC + r) * kLanes];
-        bwd_chain<T, N>(rec, ms, Vs);
-        T* o = so + t * SG * kLanes;
+    for (int i = 0; i < N; ++i) o[i * kLanes] = ms[i];
 #pragma unroll
-        for (int i = 0; i < N; ++i) o[i * kLanes] = ms[i];
+    for (int i = 0; i < NS; ++i) o[(N + i) * kLanes] = Vs[i];
+    if (kYm || kYv) {
 #pragma unroll
-        for (int i = 0; i < NS; ++i) o[(N + i) * kLanes] = Vs[i];
-        if (ymo || yvo) {
+      for (int jj = 0; jj < P; ++jj) {
+        T s = T(0), q = T(0);
 #pragma unroll
-          for (int jj = 0; jj < P; ++jj) {
-            T s = T(0), q = T(0);
+        for (int i = 0; i < N; ++i) {
+          s += prm.C[jj][i] * ms[i];
+          if (kYv) {
+            T a = T(0);
 #pragma unroll
-            for (int i = 0; i < N; ++i) {
-              s += prm.C[jj][i] * ms[i];
-              if (yvo) {
-                T a = T(0);
-#pragma unroll
-                for (int k2 = 0; k2 < N; ++k2) a += Vs[sym_idx<N>(i, k2)] * prm.C[jj][k2];
-                q += prm.C[jj][i] * a;
-              }
-            }
-            if (ymo) ymo[(t * P + jj) * kLanes] = s;
-            if (yvo) yvo[(t * P + jj) * kLanes] = q;
+            for (int k2 = 0; k2 < N; ++k2) a += Vs[sym_idx<N>(i, k2)] * prm.C[jj][k2];
+            q += prm.C[jj][i] * a;
           }
         }
+        if (kYm) ymo[(jj - j * P) * kLanes] = s;
+        if (kYv) yvo[(jj - j * P) * kLanes] = q;
       }
     }
+  };
+  tile_barrier(bar_id, bar_cnt);                           // (barrier init)
+  tile_barrier(bar_id, bar_cnt);                           // batch 0 ready
+  const long nfull = Tn / F;                               // batches with all F frames: no per-frame guards
+  for (long k = 0; k < nb; ++k) {
+    const T* src = recb + (k & 1) * (F * REC * kLanes) + lane;
+    if (k < nfull) {
+#pragma unroll
+      for (int j = 0; j < F; ++j) frame(src, j);
+    } else {
+      const int nfr = (int)(Tn - k * F);
+#pragma unroll
+      for (int j = 0; j < F; ++j)
+        if (j < nfr) frame(src, j);
+    }
+    so -= F * SG * kLanes;
+    if (kYm) ymo -= F * P * kLanes;
+    if (kYv) yvo -= F * P * kLanes;
     tile_barrier(bar_id, bar_cnt);
   }
 }

@@ -1,11 +1,51 @@
 // eksb_pipe_impl.cuh -- launch configuration + dispatch for the warp-specialised kernels.
 #pragma once
+#include <stdlib.h>
 #include "eksb_pipe.cuh"
 
 namespace eksb {
 
-constexpr size_t kCtaSmemBudget = 113 * 1024;   // two CTAs per SM (227 KB usable)
+constexpr size_t kCtaSmemBudget = 227 * 1024;   // one CTA may take the whole SM
 constexpr size_t kTileSmemBudget = 56 * 1024;   // four tiles per SM
+constexpr int kSMs = 148;                       // B200
+
+// Tiles per CTA for a launch over `tiles` track tiles.  A tile lives on one SM for the whole pass, so
+// the pass takes as long as the most loaded SM: aim for ceil(tiles/148) tiles on every busy SM, in ONE
+// CTA (warp w runs on scheduler w % 4, so the chain warps 0..tpc-1 land on distinct schedulers).
+inline int pick_tpc(long tiles, int tpc_max, size_t tile_smem) {
+  long per_sm = (tiles + kSMs - 1) / kSMs;
+  if (per_sm < 1) per_sm = 1;
+  for (int c = 1; c <= 8; ++c) {                  // c co-resident CTAs per SM when one CTA cannot hold per_sm tiles
+    const long tpc = (per_sm + c - 1) / c;
+    if (tpc <= tpc_max && c * (tpc * tile_smem + 1024) <= kCtaSmemBudget) return (int)tpc;
+  }
+  return tpc_max;                                 // more tiles than fit at once: several waves
+}
+
+// Place the warps of a CTA (tpc chain warps + tpc*H helper warps) on the four schedulers so that
+// their instruction loads even out: w_chain / w_helper are instructions per frame of a chain warp
+// and of ALL helpers of a tile together (measured from SASS).  Warp index = 4*k + s
+// for the k-th warp placed on scheduler s; unused slots become filler warps.  Returns warps per CTA.
+inline int make_roles(int tpc, int H, float w_chain, float w_helper, RoleMap& rm) {
+  const int total = tpc * (H + 1), cap = (total + 3) / 4;
+  float load[4] = {0, 0, 0, 0};
+  int len[4] = {0, 0, 0, 0};
+  for (int w = 0; w < kMaxWarps; ++w) { rm.tile[w] = -1; rm.h[w] = -1; }
+  auto place = [&](int tile, int h, float wgt) {
+    int best = -1;
+    for (int s2 = 0; s2 < 4; ++s2)
+      if (len[s2] < cap && (best < 0 || load[s2] < load[best])) best = s2;
+    const int w = 4 * len[best] + best;
+    rm.tile[w] = (signed char)tile;
+    rm.h[w] = (signed char)h;
+    load[best] += wgt;
+    ++len[best];
+  };
+  for (int t = 0; t < tpc; ++t) place(t, -1, w_chain);
+  for (int h = 0; h < H; ++h)
+    for (int t = 0; t < tpc; ++t) place(t, h, w_helper / H);
+  return 4 * cap;
+}
 
 #ifndef EKSB_PIPE_TPC
 #define EKSB_PIPE_TPC 4
@@ -17,48 +57,102 @@ template <typename T, int ROWS_IN, int REC, int H, int F, int NST> struct TileBy
 
 // Largest (F, NST) whose per-tile ring fits the budget: F frames per hand-off batch (fewer
 // barriers when larger), NST raw batches in flight (deeper HBM prefetch when larger).
-template <typename T, int H, int ROWS_IN, int REC> struct AutoCfg {
+template <typename T, int H, int ROWS_IN, int REC, int FORCE_F = 0, int FORCE_NST = 0> struct AutoCfg {
   static constexpr bool f8n3 = TileBytes<T, ROWS_IN, REC, H, 8, 3>::value <= kTileSmemBudget;
   static constexpr bool f4n3 = TileBytes<T, ROWS_IN, REC, H, 4, 3>::value <= kTileSmemBudget;
   static constexpr bool f4n2 = TileBytes<T, ROWS_IN, REC, H, 4, 2>::value <= kTileSmemBudget;
   static constexpr bool f2n3 = TileBytes<T, ROWS_IN, REC, H, 2, 3>::value <= kTileSmemBudget;
-  static constexpr int F = f8n3 ? 8 : (f4n3 || f4n2) ? 4 : 2;
-  static constexpr int NST = f8n3 ? 3 : f4n3 ? 3 : f4n2 ? 2 : 3;
+  static constexpr int F = FORCE_F ? FORCE_F : f8n3 ? 8 : (f4n3 || f4n2) ? 4 : 2;
+  static constexpr int NST = FORCE_NST ? FORCE_NST : f8n3 ? 3 : f4n3 ? 3 : f4n2 ? 2 : 3;
   static constexpr size_t kTileSmem = TileBytes<T, ROWS_IN, REC, H, F, NST>::value;
-  static constexpr int TPC0 = (int)(kCtaSmemBudget / kTileSmem);
+  static constexpr int TPC0 = (int)((kCtaSmemBudget - 1024) / kTileSmem);
   static constexpr int TPC = TPC0 > EKSB_PIPE_TPC ? EKSB_PIPE_TPC : TPC0;
-  static constexpr bool ok = TPC >= 1 && (f8n3 || f4n3 || f4n2 || f2n3);
+  static constexpr bool ok = TPC >= 1 && (FORCE_F || f8n3 || f4n3 || f4n2 || f2n3);
   using type = PipeCfg<H, F, NST, (TPC >= 1 ? TPC : 1)>;
 };
 
-constexpr int kFwdHelpers = 1, kBwdHelpers = 2;
+#ifndef EKSB_FWD_H
+#define EKSB_FWD_H 2
+#endif
+#ifndef EKSB_BWD_H
+#define EKSB_BWD_H 2
+#endif
+#ifndef EKSB_FWD_F      // 0 = automatic (largest batch/stage count that fits the per-tile budget)
+#define EKSB_FWD_F 0
+#endif
+#ifndef EKSB_FWD_NST
+#define EKSB_FWD_NST 0
+#endif
+#ifndef EKSB_BWD_F
+#define EKSB_BWD_F 0
+#endif
+#ifndef EKSB_BWD_NST
+#define EKSB_BWD_NST 0
+#endif
+constexpr int kFwdHelpers = EKSB_FWD_H, kBwdHelpers = EKSB_BWD_H;
+// instructions per frame (n=3, p=4, f64 SASS): forward chain / helper, backward chain / helpers
+constexpr float kFwdChainW = 118, kFwdHelperW = 125, kBwdChainW = 103, kBwdHelperW = 200;
 
 template <typename T, int N, int P, int AM, int OP = 0>
 static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                            long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
-  using Auto = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD>;
+  using Auto = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, EKSB_FWD_F, EKSB_FWD_NST>;
   if (!Auto::ok) return EKSB_EDIM;
   using Cfg = typename Auto::type;
   auto kern = kf_forward_pipe_kernel<T, N, P, AM, OP, Cfg>;
-  const size_t smem = Auto::kTileSmem * Cfg::TPC;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  const unsigned grid = (unsigned)((num_tiles(B) + Cfg::TPC - 1) / Cfg::TPC);
-  kern<<<grid, Cfg::THREADS, smem, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status);
+  const int tpc = pick_tpc(num_tiles(B), Cfg::TPC, Auto::kTileSmem);
+  const size_t smem = Auto::kTileSmem * tpc;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(Auto::kTileSmem * Cfg::TPC));
+  const unsigned grid = (unsigned)((num_tiles(B) + tpc - 1) / tpc);
+  RoleMap rm;
+  const int warps = make_roles(tpc, Cfg::H, kFwdChainW, kFwdHelperW, rm);
+  kern<<<grid, warps * kLanes, smem, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, tpc, rm);
   return check_launch("kf_forward_pipe_kernel");
 }
 
+template <typename T, int N, int P, int AM, int OP, int OUT, typename Auto>
+static int launch_bwd_cfg(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
+                          T* smth, T* ym, T* yv, int* status, cudaStream_t st) {
+  using Cfg = typename Auto::type;
+  auto kern = rts_backward_pipe_kernel<T, N, P, AM, OP, OUT, Cfg>;
+  const int tpc = pick_tpc(num_tiles(B), Cfg::TPC, Auto::kTileSmem);
+  const size_t smem = Auto::kTileSmem * tpc;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(Auto::kTileSmem * Cfg::TPC));
+  const unsigned grid = (unsigned)((num_tiles(B) + tpc - 1) / tpc);
+  RoleMap rm;
+  const int warps = make_roles(tpc, Cfg::H, kBwdChainW, kBwdHelperW, rm);
+  kern<<<grid, warps * kLanes, smem, st>>>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, tpc, rm);
+  return check_launch("rts_backward_pipe_kernel");
+}
+
+// Two ring shapes.  "Wide" (3 helpers, 6-frame batches) keeps the helpers ahead of the chain warp when
+// an SM holds few tiles (measured, f64 8192 tracks: 5.82 -> 4.85 ms per 20 000 frames); it needs
+// 1.5x the shared memory per tile, so when more tiles must share an SM the "narrow" ring (2 helpers,
+// 4-frame batches) is used.  Wide is instantiated for state dim <= 3 only (every shipped config).
+template <typename T, int N, int P, int AM, int OP, int OUT>
+static int launch_bwd_pipe_out(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
+                               T* smth, T* ym, T* yv, int* status, cudaStream_t st) {
+  using Narrow = AutoCfg<T, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_F, EKSB_BWD_NST>;
+  using Wide = AutoCfg<T, 3, Dim<N>::SIGMA, Rec<N>::BWD, 6, 2>;
+  if constexpr (N <= 3 && Wide::ok) {
+    const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
+    static const bool narrow_only = getenv("EKSB_BWD_NARROW") != nullptr;
+    if (!narrow_only && per_sm <= Wide::TPC && per_sm * Wide::kTileSmem + 1024 <= kCtaSmemBudget)
+      return launch_bwd_cfg<T, N, P, AM, OP, OUT, Wide>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+  }
+  if (!Narrow::ok) return EKSB_EDIM;
+  return launch_bwd_cfg<T, N, P, AM, OP, OUT, Narrow>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+}
+
+// The projections are compile-time variants: a runtime `if (yv)` leaves ~50 predicated-off
+// FMAs per frame on the chain warp's issue path (seen in the ncu source page, round 1).
 template <typename T, int N, int P, int AM, int OP = 0>
 static int launch_bwd_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, T* smth,
                            T* ym, T* yv, int* status, cudaStream_t st) {
-  using Auto = AutoCfg<T, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD>;
-  if (!Auto::ok) return EKSB_EDIM;
-  using Cfg = typename Auto::type;
-  auto kern = rts_backward_pipe_kernel<T, N, P, AM, OP, Cfg>;
-  const size_t smem = Auto::kTileSmem * Cfg::TPC;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  const unsigned grid = (unsigned)((num_tiles(B) + Cfg::TPC - 1) / Cfg::TPC);
-  kern<<<grid, Cfg::THREADS, smem, st>>>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status);
-  return check_launch("rts_backward_pipe_kernel");
+  if (ym && yv) return launch_bwd_pipe_out<T, N, P, AM, OP, 3>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+  if (ym) return launch_bwd_pipe_out<T, N, P, AM, OP, 1>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+  if (yv) return launch_bwd_pipe_out<T, N, P, AM, OP, 2>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+  return launch_bwd_pipe_out<T, N, P, AM, OP, 0>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
 }
 
 // pipelined instantiations: state dim <= 4 (larger records do not fit the shared-memory ring)

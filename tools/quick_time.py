@@ -35,6 +35,11 @@ def run(dt, B, T, p=4, n=3, reps=3):
     assert torch.isfinite(ym).all()
 
 if __name__ == "__main__":
-    for dt in (torch.float32, torch.float64):
-        for B, T in ((16384, 10000), (8192, 10000), (49152, 4000)):
-            run(dt, B, T)
+    if len(sys.argv) > 1:                       # bits:B:T ...
+        for a in sys.argv[1:]:
+            bits, B, T = (int(x) for x in a.split(":"))
+            run(torch.float64 if bits == 64 else torch.float32, B, T, reps=2)
+    else:
+        for dt in (torch.float32, torch.float64):
+            for B, T in ((16384, 10000), (8192, 10000), (49152, 4000)):
+                run(dt, B, T)
