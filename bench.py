@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--tracks", type=int, default=0, help="tracks per GPU (default: 8192 f64 / 16384 f32)")
     ap.add_argument("--frames", type=int, default=100_000)
     ap.add_argument("--e2e-tracks", type=int, default=1024)
+    ap.add_argument("--e2e-block", type=int, default=128)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU-baseline sample time")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
@@ -328,7 +329,7 @@ def gpu_main(a):
         outs = batched.alloc_outputs(Be, T, N_LAT, P_OBS, dt, pin=True)
         cnt = {}
         call = lambda c=None: batched.smooth_tracks(y_h, ev_h, pe["m0"], pe["S0"], pe["C"], pe["A"], pe["Q"], dtype=dt,
-                                                    device=d, block_tracks=256, out=outs, counters=c)
+                                                    device=d, block_tracks=a.e2e_block, out=outs, counters=c)
         call()                                                  # warm-up (allocator, first-touch)
         if world > 1:
             dist.barrier()
@@ -344,7 +345,7 @@ def gpu_main(a):
         assert int(outs["status"].sum()) == 0 and bool(torch.isfinite(outs["ym"][::97]).all())
         e2e = {"value": world * Be * T * a.steps / dt_s, "unit": UNIT,
                "h2d_bytes_per_step": cnt["h2d_bytes"] // a.steps, "d2h_bytes_per_step": cnt["d2h_bytes"] // a.steps,
-               "tracks": Be, "frames": T, "api": "eks_b200.batched.smooth_tracks (pinned host in/out, 256-track blocks, 3 streams)",
+               "tracks": Be, "frames": T, "api": f"eks_b200.batched.smooth_tracks (pinned host in/out, {a.e2e_block}-track blocks through the parallel-in-time scan, 3 streams)",
                "ms_per_step": 1e3 * dt_s / a.steps}
         launches += cnt["launches"]
 

@@ -29,7 +29,7 @@ def alloc_outputs(B, T, n, p, dtype=torch.float64, pin=True):
 
 
 def smooth_tracks(y, ev, m0, S0, C, A, Q, *, dtype=torch.float64, device=None, block_tracks=1024, out=None,
-                  counters=None):
+                  counters=None, scan=None):
     """Kalman filter + RTS smoother for B independent tracks (A2 + A4 + A5 of SURVEY section 8a).
 
     y, ev : host (B,T,p) arrays/tensors -- centred ensemble means and ensemble variances.
@@ -37,6 +37,8 @@ def smooth_tracks(y, ev, m0, S0, C, A, Q, *, dtype=torch.float64, device=None, b
     eks/ensemble_kalman.py:59 (a leading B dimension makes a parameter per-track).
     Returns host tensors: ms (B,T,n), Vs (B,T,n(n+1)/2) [upper triangle, row-major],
     ym (B,T,p) = C ms, status (B,) [1 = non-positive pivot, the reference's LinAlgError].
+    scan: None = choose per block size (parallel-in-time scan when a block has fewer tiles than SMs),
+    True / False = force.
     """
     if not torch.cuda.is_available():
         raise RuntimeError("eks_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
@@ -53,10 +55,16 @@ def smooth_tracks(y, ev, m0, S0, C, A, Q, *, dtype=torch.float64, device=None, b
     blk = max(32, (min(block_tracks, B) + 31) // 32 * 32)
     nblk = (B + blk - 1) // blk
     s_in, s_k, s_out = (torch.cuda.Stream(d) for _ in range(3))
-    nbuf = 2
+    nbuf = 3
+    # sequential kernels need >= ~1 tile per SM to be worth their per-frame latency; below that use the scan
+    use_scan = (scan if scan is not None else
+                (dev.num_tiles(blk) < 148 and T >= 4096 and n <= 4 and bool(_lib.lib().eksb_supported_dims(n, p))))
+    es = torch.empty(0, dtype=dtype).element_size()
+    ws_elems = max(1, _lib.lib().eksb_scan_workspace_bytes(blk, T, n, 0, es) // es) if use_scan else 1
     bufs = []
     for _ in range(min(nbuf, nblk)):
         bufs.append(dict(
+            ws=torch.empty(ws_elems, dtype=dtype, device=d),
             y=torch.empty((blk, T, p), dtype=dtype, device=d), ev=torch.empty((blk, T, p), dtype=dtype, device=d),
             obs=dev.alloc_records(blk, T, 2 * p, dtype, d), st=dev.alloc_records(blk, T, sg, dtype, d),
             ymr=dev.alloc_records(blk, T, p, dtype, d),
@@ -84,8 +92,15 @@ def smooth_tracks(y, ev, m0, S0, C, A, Q, *, dtype=torch.float64, device=None, b
             yb, evb = bf["y"][:nb], bf["ev"][:nb]
             dev.pack_rows(yb, bf["obs"], 2 * p, 0, 0.0)
             dev.pack_rows(evb, bf["obs"], 2 * p, p, 1.0)
-            dev.kf_forward(bf["obs"], prm, nb, T, filt=bf["st"], status=bf["status"][:nb])
-            dev.rts_backward(bf["st"], prm, nb, T, inplace=True, ym=bf["ymr"], status=bf["status"][:nb])
+            if use_scan:
+                # few tiles, long tracks: the sequential kernels would run at one warp's pace, so
+                # cut time into chunks (exact parallel-in-time scan, eksb_kf_rts_scan)
+                dev.kf_rts_scan(bf["obs"], prm, nb, T, filt=bf["st"], ym=bf["ymr"], status=bf["status"][:nb],
+                                workspace=bf["ws"])
+                launches += 4                      # 6 scan kernels instead of 2
+            else:
+                dev.kf_forward(bf["obs"], prm, nb, T, filt=bf["st"], status=bf["status"][:nb])
+                dev.rts_backward(bf["st"], prm, nb, T, inplace=True, ym=bf["ymr"], status=bf["status"][:nb])
             for name, rows, r0, R in (("ms", sg, 0, n), ("Vs", sg, n, sg - n)):
                 fn = getattr(_lib.lib(), f"eksb_unpack_rows_{dev._sfx(dtype)}")
                 dev.check(fn(bf["st"].data_ptr(), rows, r0, nb, T, R, bf[name].data_ptr(), s_k.cuda_stream), "eksb_unpack_rows")

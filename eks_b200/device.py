@@ -268,17 +268,27 @@ def btd_solve(obs, prm: TrackParams, B, T, want_ym=False, inplace=True, status=N
 
 
 # ------------------------------------------------------------------ K4 parallel-in-time scan
-def kf_rts_scan(obs, prm: TrackParams, B, T, chunk=0, smooth=True, inplace=True, want_ym=True, status=None):
+def kf_rts_scan(obs, prm: TrackParams, B, T, chunk=0, smooth=True, inplace=True, want_ym=True, status=None,
+                filt=None, ym=None, workspace=None):
     """Filter (+ RTS smoother) by the exact chunked scan over time; for few, very long tracks.
-    Returns dict(filt, smth, ym, status, chunk)."""
+    Returns dict(filt, smth, ym, status, chunk).  filt / ym / workspace may be caller-provided."""
     _need_cuda(obs, "obs")
     dev, dt = obs.device, obs.dtype
     es = obs.element_size()
     nbytes = lib().eksb_scan_workspace_bytes(B, T, prm.n, chunk, es)
-    ws = torch.empty(max(1, nbytes // es), dtype=dt, device=dev)
-    filt = alloc_records(B, T, sigma(prm.n), dt, dev)
+    if workspace is not None:
+        if workspace.numel() * es < nbytes:
+            raise ValueError("scan workspace too small")
+        ws = workspace
+    else:
+        ws = torch.empty(max(1, nbytes // es), dtype=dt, device=dev)
+    if filt is None:
+        filt = alloc_records(B, T, sigma(prm.n), dt, dev)
     smth = (filt if inplace else torch.empty_like(filt)) if smooth else None
-    ym = alloc_records(B, T, prm.p, dt, dev) if (smooth and want_ym) else None
+    if smooth and want_ym and ym is None:
+        ym = alloc_records(B, T, prm.p, dt, dev)
+    if not (smooth and want_ym):
+        ym = None
     if status is None:
         status = torch.zeros(B, dtype=torch.int32, device=dev)
     fn = getattr(lib(), f"eksb_kf_rts_scan_{_sfx(dt)}")

@@ -252,6 +252,25 @@ def test_batched_host_api_matches_oracle():
     assert int(out["status"].sum()) == 0
 
 
+def test_batched_host_api_scan_path_matches_oracle():
+    """smooth_tracks routes small blocks of long tracks through the parallel-in-time scan (the e2e
+    bench path); forced here on a short case and compared with the oracle and the sequential path."""
+    import torch
+    from eks_b200 import batched
+    B, T, p, n = 40, 4500, 4, 3
+    c = _random_batch(B, T, p, n, torch.float64, seed=43)
+    auto = batched.smooth_tracks(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], block_tracks=32)   # T >= 4096 -> scan
+    seq = batched.smooth_tracks(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], block_tracks=32, scan=False)
+    iu = np.triu_indices(n)
+    for k in ("ms", "Vs", "ym"):
+        assert rel(auto[k].numpy(), seq[k].numpy()) < 1e-9
+    for b in (0, 39):
+        mf, Vf, S = o.filtering_pass(c["y"][b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], c["ev"][b])
+        ms, Vs, _ = o.smooth_backward(c["y"][b], mf, Vf, S, c["A"], c["Q"], c["C"][b])
+        assert rel(auto["ms"][b].numpy(), ms) < 1e-9 and rel(auto["Vs"][b].numpy(), Vs[:, iu[0], iu[1]]) < 1e-9
+    assert int(auto["status"].sum()) == 0
+
+
 @pytest.mark.parametrize("dtname,tol", [("float64", 1e-9), ("float32", 2e-3)])
 @pytest.mark.parametrize("B,T,chunk", [(3, 1000, 64), (40, 777, 100), (2, 5000, 0), (33, 129, 200)])
 def test_parallel_in_time_scan_equals_sequential(dtname, tol, B, T, chunk):
