@@ -189,6 +189,29 @@ def ensemble_tiled(preds, B, p, mode="median", offset=None, out=None):
     return obs
 
 
+# ------------------------------------------------------------------ K8 parameter setup on the device
+def pca_setup(obs, B, T, p, quantile, smooth_param, n=3, center=True, status=None):
+    """Per-track (means, C, S0, Q) of the multi-camera smoother from UNcentred obs records
+    (multiview_pca_smoother.py:684-731); with center=True the y rows of `obs` are centred in place.
+    Returns (TrackParams with m0 = 0, A = I, means (B,p) tensor, status (B,) int32)."""
+    _need_cuda(obs, "obs")
+    dev, dt = obs.device, obs.dtype
+    means = torch.empty((B, p), dtype=dt, device=dev)
+    C = torch.empty((B, p, n), dtype=dt, device=dev)
+    S0 = torch.empty((B, n, n), dtype=dt, device=dev)
+    Q = torch.empty((B, n, n), dtype=dt, device=dev)
+    nbytes = lib().eksb_pca_setup_workspace_bytes(B, p)
+    ws = torch.empty(max(1, nbytes // 8), dtype=torch.float64, device=dev)
+    if status is None:
+        status = torch.zeros(B, dtype=torch.int32, device=dev)
+    fn = getattr(lib(), f"eksb_pca_setup_{_sfx(dt)}")
+    check(fn(_ptr(obs), B, T, n, p, float(quantile), float(smooth_param), int(bool(center)), _ptr(means), _ptr(C),
+             _ptr(S0), _ptr(Q), _ptr(ws), nbytes, _ptr(status), _stream(dev)), "eksb_pca_setup")
+    prm = TrackParams(torch.zeros(n, dtype=dt, device=dev), S0, C, torch.eye(n, dtype=dt, device=dev), Q,
+                      a_mode=_lib.A_DIAG)
+    return prm, means, status
+
+
 # ------------------------------------------------------------------ A2 / A6 forward
 def kf_forward(obs, prm: TrackParams, B, T, first=_lib.FIRST_PRIOR_UPDATE, q_scale=None, want_filt=True,
                want_nll=False, filt=None, status=None):

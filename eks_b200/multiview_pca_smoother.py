@@ -107,41 +107,66 @@ def _stack_cameras(markers_list_cameras):
                      for m in range(M)]).astype(np.float64)
 
 
-def _multicam_setup(markers_list_cameras, smooth_param, quantile_keep_pca):
-    stack = _stack_cameras(markers_list_cameras)
-    preds, evars = _ensemble_median(stack)                            # per-camera ensemble() calls fused (:675-682)
-    good = _good_frames(evars, quantile_keep_pca)
-    means = preds[good].mean(axis=0)                                  # :698-700
-    y = preds - means
-    pca_, _ = pca(y[good], 3)                                         # :707-708
-    m0, S0, A, Q, C = _kf_params(pca_, pca_.transform(y)[good], smooth_param)
-    return dict(y=y, ev=evars, m0=m0, S0=S0, A=A, Q=Q, C=C), means
+def smooth_session_multi_cam(stack, smooth_param, quantile_keep_pca, newton=False, dtype=torch.float64):
+    """All keypoints of a session in one pass, nothing but the result leaving the GPU.
+
+    stack: (M, T, B, p) host array or CUDA tensor -- M ensemble members, T frames, B keypoints (tracks),
+    p = 2 * n_cameras columns ordered [cam0_x, cam0_y, cam1_x, ...] (the restack of :645-659).
+    Pipeline, every stage a libeksb kernel: ensemble median + variance fused with the restack
+    (eksb_ensemble_tiled, :675-682) -> per-track good-frame selection, camera means, PCA(3), S0, Q, C and
+    centring (eksb_pca_setup, :684-731) -> filter + RTS + back-projection (or the Newton-recursive filter).
+    Returns dict(y=(B,T,p) smoothed observations with the camera means added back (:745,:761-762),
+    latent=(B,T,3), means=(B,p)) as host float64 arrays."""
+    d = _cuda()
+    t = stack if isinstance(stack, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(stack))
+    M, T, B, p = t.shape
+    preds = t.to(device=d, dtype=dtype).reshape(M, T, B * p).contiguous()
+    obs = dev.ensemble_tiled(preds, B, p, "median")
+    prm, means, status = dev.pca_setup(obs, B, T, p, quantile_keep_pca, smooth_param, n=3, center=True)
+    sg = dev.sigma(3)
+    if newton:
+        filt, _, st2 = dev.kf_forward(obs, prm, B, T, first=_lib.FIRST_PRIOR_ONLY, status=status)
+        lat = dev.unpack_rows(filt, sg, 0, B, T, 3)
+        ym = dev.unpack_rows(dev.project(filt, prm, B, T), p, 0, B, T, p)
+    else:
+        filt, _, _ = dev.kf_forward(obs, prm, B, T, status=status)
+        out = dev.rts_backward(filt, prm, B, T, inplace=True, want_ym=True, status=status)
+        lat = dev.unpack_rows(out["smth"], sg, 0, B, T, 3)
+        ym = dev.unpack_rows(out["ym"], p, 0, B, T, p)
+    if bool(status.any().item()):
+        raise np.linalg.LinAlgError("Singular matrix")
+    y = (ym + means[:, None, :]).cpu().numpy().astype(np.float64)
+    return dict(y=y, latent=lat.cpu().numpy().astype(np.float64), means=means.cpu().numpy().astype(np.float64))
 
 
-def _camera_dfs(ym, means, keypoint_ensemble, camera_names):
+def session_dfs(y, keypoint_names, camera_names):
+    """{camera_df: DataFrame (T, 3*B)} with the DLC column index over ALL keypoints (likelihood = NaN),
+    the layout scripts/multicam_example.py:118-160 assembles keypoint by keypoint."""
+    B, T, _ = y.shape
     out = {}
-    for c, name in enumerate(camera_names):                           # :751-767
-        arr = np.column_stack([ym[:, 2 * c] + means[2 * c], ym[:, 2 * c + 1] + means[2 * c + 1],
-                               np.full(ym.shape[0], np.nan)])
-        out[name + '_df'] = pd.DataFrame(arr, columns=make_dlc_pandas_index([keypoint_ensemble]))
+    for c, name in enumerate(camera_names):
+        arr = np.full((T, 3 * B), np.nan)
+        arr[:, 0::3] = y[:, :, 2 * c].T
+        arr[:, 1::3] = y[:, :, 2 * c + 1].T
+        out[name + '_df'] = pd.DataFrame(arr, columns=make_dlc_pandas_index(list(keypoint_names)))
     return out
 
 
 def ensemble_kalman_smoother_multi_cam(
         markers_list_cameras, keypoint_ensemble, smooth_param, quantile_keep_pca, camera_names):
     """multiview_pca_smoother.py:611-767.  Returns {f'{camera}_df': DataFrame (T,3) [x, y, likelihood=NaN]}."""
-    trk, means = _multicam_setup(markers_list_cameras, smooth_param, quantile_keep_pca)
-    (_, ym), = _run_tracks([trk])
-    return _camera_dfs(ym, means, keypoint_ensemble, camera_names)
+    stack = _stack_cameras(markers_list_cameras)[:, :, None, :]
+    res = smooth_session_multi_cam(stack, smooth_param, quantile_keep_pca)
+    return session_dfs(res["y"], [keypoint_ensemble], camera_names)
 
 
 def eks_opti_smoother_multi_cam(
         markers_list_cameras, keypoint_ensemble, smooth_param, quantile_keep_pca, camera_names, plot=False):
     """multiview_pca_smoother.py:777-933 with the Newton-recursive filter (:902).  `plot` is accepted
     for signature compatibility; the reference's plot branch dereferences undefined names (:907-913)."""
-    trk, means = _multicam_setup(markers_list_cameras, smooth_param, quantile_keep_pca)
-    (_, ym), = _run_tracks([trk], newton=True)
-    return _camera_dfs(ym, means, keypoint_ensemble, camera_names)
+    stack = _stack_cameras(markers_list_cameras)[:, :, None, :]
+    res = smooth_session_multi_cam(stack, smooth_param, quantile_keep_pca, newton=True)
+    return session_dfs(res["y"], [keypoint_ensemble], camera_names)
 
 
 # ---------------------------------------------------------------------------- paw, two async views

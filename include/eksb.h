@@ -222,6 +222,25 @@ EKSB_API int eksb_kf_rts_scan_f32(const float* obs, const float* m0, const float
                          float* workspace, size_t workspace_bytes, float* filt, float* smth, float* ym, int* status,
                          void* stream);
 
+/* ---- K8: Kalman parameter setup of the multi-camera smoother on the device --------
+ * For every track, from its obs records (y = UNcentred ensemble median, ev = ensemble variance):
+ *   good frames = { t : max_j ev[t,j] <= numpy.percentile(max_j ev, quantile) }  (multiview_pca_smoother.py:686-688;
+ *                 exact order statistic + numpy's linear interpolation, bit-identical threshold)
+ *   means (B,p)   = mean of y over good frames                                    (:698-700)
+ *   C (B,p,n)     = components_^T of PCA(n=3) of the centred good rows, rows signed like sklearn's svd_flip (:707-708,:730)
+ *   S0 (B,n,n)    = diag(var(good PCs)), ddof 0                                    (:722)
+ *   Q (B,n,n)     = smooth_param * cov(difference of consecutive good PCs), ddof 1 (:726-728)
+ * (m0 = 0 and A = I are constants, :721,:724).  center != 0 also subtracts means from the y rows in place
+ * (:702-705), leaving obs ready for eksb_kf_forward.  status[b] = 1 if a track has < 3 good frames.
+ * p in {4,6,8}, n = 3.  workspace: eksb_pca_setup_workspace_bytes(B, p) bytes (doubles). */
+EKSB_API size_t eksb_pca_setup_workspace_bytes(long B, int p);
+EKSB_API int eksb_pca_setup_f64(double* obs, long B, long T, int n, int p, double quantile, double smooth_param, int center,
+                       double* means, double* C, double* S0, double* Q, double* workspace, size_t workspace_bytes,
+                       int* status, void* stream);
+EKSB_API int eksb_pca_setup_f32(float* obs, long B, long T, int n, int p, double quantile, double smooth_param, int center,
+                       float* means, float* C, float* S0, float* Q, double* workspace, size_t workspace_bytes,
+                       int* status, void* stream);
+
 /* EKSB_DECLS_END (new declarations go above this line) */
 #ifdef __cplusplus
 }

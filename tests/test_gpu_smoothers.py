@@ -73,3 +73,56 @@ def test_paw_asynchronous():
     np.testing.assert_allclose(out["right_df"].to_numpy(), z["right_df"], rtol=0, atol=TOL, equal_nan=True)
     opt = eks_opti_smoother_paw_asynchronous(left, right, z["ts_left"], z["ts_right"], kp, 0.01, 25)
     assert opt["left_df"].shape == (997, 6) and np.isfinite(opt["left_df"].to_numpy()[:, [0, 1, 3, 4]]).all()
+
+
+def _synthetic_session(B, T, p, M=5, seed=0):
+    rng = np.random.default_rng(seed)
+    C = np.stack([np.linalg.qr(rng.normal(size=(p, 3)))[0] for _ in range(B)])
+    x = np.cumsum(rng.normal(size=(B, T, 3)) * 0.3, axis=1)
+    clean = np.einsum("bpn,btn->btp", C, x) + rng.uniform(50, 400, size=(B, 1, p))
+    sd = np.exp(rng.normal(np.log(0.5), 0.8, size=(B, T, p)))
+    sd[rng.random((B, T, 1)).repeat(p, 2) < 0.02] *= 30
+    return (clean[None] + sd[None] * rng.normal(size=(M, B, T, p))).transpose(0, 2, 1, 3)   # (M,T,B,p)
+
+
+@pytest.mark.parametrize("B,T,p,q", [(5, 700, 4, 25), (37, 333, 6, 50), (3, 1500, 8, 90), (2, 64, 4, 100)])
+def test_device_parameter_setup_matches_oracle(B, T, p, q):
+    """K8: percentile threshold / good-frame means / PCA / S0 / Q computed on the device equal the oracle's
+    restatement of multiview_pca_smoother.py:684-731 (numpy percentile + sklearn PCA) per track."""
+    import torch
+    from eks_b200 import device as dev
+    from oracle import restated_smoothers as osm
+    stack = _synthetic_session(B, T, p, seed=B + T)
+    d = torch.device("cuda", 0)
+    preds = torch.as_tensor(np.ascontiguousarray(stack.reshape(5, T, B * p))).to(d)
+    obs = dev.ensemble_tiled(preds, B, p, "median")
+    prm, means, status = dev.pca_setup(obs, B, T, p, q, 0.01, center=True)
+    assert int(status.sum()) == 0
+    y_c = dev.unpack_rows(obs, 2 * p, 0, B, T, p).cpu().numpy()
+    for b in range(B):
+        want = osm.multicam_setup(stack[:, :, b, :], 0.01, q)
+        np.testing.assert_allclose(means[b].cpu().numpy(), want["means"], rtol=1e-12)
+        np.testing.assert_allclose(y_c[b], want["y"], rtol=0, atol=1e-9)
+        Cg, Cw = prm.C[b].cpu().numpy(), want["C"]
+        sgn = np.sign(np.sum(Cg * Cw, axis=0))                       # component signs are a convention
+        np.testing.assert_allclose(Cg * sgn, Cw, rtol=0, atol=1e-8)
+        np.testing.assert_allclose(prm.S0[b].cpu().numpy(), want["S0"], rtol=1e-8, atol=1e-12)
+        Qw = want["Q"] * np.outer(sgn, sgn)
+        np.testing.assert_allclose(prm.Q[b].cpu().numpy(), Qw, rtol=1e-7, atol=1e-9 * np.abs(Qw).max())
+
+
+def test_session_entry_equals_per_keypoint_calls():
+    """All mirror-mouse keypoints in one batched session call == the per-keypoint drop-in == shipped CSVs."""
+    from eks_b200.multiview_pca_smoother import smooth_session_multi_cam, session_dfs
+    z = cases_of(load_golden("mirror_mouse.npz"))
+    kps = sorted(z)
+    stack = np.stack([z[k]["stack"] for k in kps], axis=2)           # (M,T,B,p)
+    res = smooth_session_multi_cam(stack, 0.01, 25)
+    for i, k in enumerate(kps):
+        np.testing.assert_allclose(res["y"][i], z[k]["shipped_std"], rtol=0, atol=TOL)
+    dfs = session_dfs(res["y"], kps, ["top", "bot"])
+    assert dfs["top_df"].shape == (stack.shape[1], 3 * len(kps))
+    assert list(dfs["bot_df"].columns[:3]) == [("ensemble-kalman_tracker", kps[0], c) for c in ("x", "y", "likelihood")]
+    opt = smooth_session_multi_cam(stack, 0.01, 25, newton=True)
+    for i, k in enumerate(kps):
+        np.testing.assert_allclose(opt["y"][i], z[k]["shipped_opti"], rtol=0, atol=TOL)
