@@ -23,7 +23,7 @@ _CTYPES = {
     "void*": ctypes.c_void_p, "int*": ctypes.c_void_p, "double*": ctypes.c_void_p, "float*": ctypes.c_void_p,
     "const double*": ctypes.c_void_p, "const float*": ctypes.c_void_p, "const int*": ctypes.c_void_p,
     "const char*": ctypes.c_char_p, "size_t": ctypes.c_size_t,
-    "const long*": ctypes.c_void_p, "long*": ctypes.c_void_p,
+    "const long*": ctypes.c_void_p, "long*": ctypes.c_void_p, "char*": ctypes.c_void_p,
 }
 
 

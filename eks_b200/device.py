@@ -189,6 +189,20 @@ def ensemble_tiled(preds, B, p, mode="median", offset=None, out=None):
     return obs
 
 
+# ------------------------------------------------------------------ view alignment
+def interp_rows(ts_src, src, ts_q, flip=None):
+    """src (S,Ts,K) sampled at ts_src (Ts) -> (S,Tq,K) at ts_q (Tq); flip (K): out = flip - value where != 0
+    (multiview_pca_smoother.py:70-101, scipy interp1d arithmetic, bit-identical)."""
+    _need_cuda(src, "src")
+    S, Ts, K = src.shape
+    Tq = ts_q.shape[0]
+    out = torch.empty((S, Tq, K), dtype=src.dtype, device=src.device)
+    fn = getattr(lib(), f"eksb_interp_rows_{_sfx(src.dtype)}")
+    check(fn(_ptr(ts_src), _ptr(src), S, Ts, K, _ptr(ts_q), Tq, _ptr(flip), _ptr(out), _stream(src.device)),
+          "eksb_interp_rows")
+    return out
+
+
 # ------------------------------------------------------------------ K8 parameter setup on the device
 def pca_setup(obs, B, T, p, quantile, smooth_param, n=3, center=True, status=None):
     """Per-track (means, C, S0, Q) of the multi-camera smoother from UNcentred obs records

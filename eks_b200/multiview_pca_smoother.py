@@ -170,31 +170,28 @@ def eks_opti_smoother_multi_cam(
 
 
 # ---------------------------------------------------------------------------- paw, two async views
-def _align_views(left_np, right_np, ts_left, ts_right):
-    """Right view linearly interpolated onto left timestamps, x flipped (:70-101).
-    Left frames before the right camera's first timestamp are skipped and the loop stops at the
-    first one beyond its last (:83-86).  Returns (left (T',4), right (T',4)), columns [0,1,3,4]."""
+def _align_views(left_stack, right_stack, ts_left, ts_right):
+    """Right view linearly interpolated onto left timestamps, x flipped (:70-101), all ensemble members
+    in one eksb_interp_rows launch.  Left frames before the right camera's first timestamp are skipped and
+    the loop stops at the first one beyond its last (:83-86).
+    left_stack (M,T_l,6), right_stack (M,T_r,6) -> (left (M,T',4), right (M,T',4)), columns [0,1,3,4]."""
+    d = _cuda()
     ts_left, ts_right = np.asarray(ts_left, dtype=np.float64), np.asarray(ts_right, dtype=np.float64)
     beyond = np.nonzero(ts_left > ts_right[-1])[0]
     stop = beyond[0] if beyond.size else ts_left.shape[0]
     keep = np.nonzero(ts_left[:stop] >= ts_right[0])[0]
     cols = [0, 1, 3, 4]
-    t = ts_left[keep]
-    hi = np.clip(np.searchsorted(ts_right, t, side="left"), 1, ts_right.shape[0] - 1)
-    lo = hi - 1
-    r_lo, r_hi = right_np[lo][:, cols].astype(np.float64), right_np[hi][:, cols].astype(np.float64)
-    slope = (r_hi - r_lo) / (ts_right[hi] - ts_right[lo])[:, None]     # scipy interp1d(kind='linear') arithmetic
-    right = slope * (t - ts_right[lo])[:, None] + r_lo
-    right[:, 0] = IMG_WIDTH - right[:, 0]
-    right[:, 2] = IMG_WIDTH - right[:, 2]
-    return left_np[keep][:, cols].astype(np.float64), right
+    to = lambda a: torch.as_tensor(np.ascontiguousarray(a, dtype=np.float64)).to(d)
+    flip = to([IMG_WIDTH, 0.0, IMG_WIDTH, 0.0])                        # x -> img_width - x (:90-91)
+    right = dev.interp_rows(to(ts_right), to(right_stack[:, :, cols]), to(ts_left[keep]), flip)
+    return left_stack[:, keep][:, :, cols].astype(np.float64), right.cpu().numpy()
 
 
 def _paw_setup(markers_list_left_cam, markers_list_right_cam, ts_left, ts_right, smooth_param, quantile_keep_pca):
-    aligned = [_align_views(l.to_numpy(), r.to_numpy(), ts_left, ts_right)
-               for l, r in zip(markers_list_left_cam, markers_list_right_cam)]
+    left, right = _align_views(np.stack([l.to_numpy() for l in markers_list_left_cam]),
+                               np.stack([r.to_numpy() for r in markers_list_right_cam]), ts_left, ts_right)
     # one ensemble launch over both views: columns [left l_x l_y r_x r_y | right l_x l_y r_x r_y]  (:115-118)
-    stack = np.stack([np.concatenate(a, axis=1) for a in aligned])
+    stack = np.concatenate([left, right], axis=2)
     preds, evars = _ensemble_median(stack)
     good = _good_frames(evars, quantile_keep_pca)                      # max over both views (:123-126)
     lp, rp, lv, rv = preds[:, :4], preds[:, 4:], evars[:, :4], evars[:, 4:]

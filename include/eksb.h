@@ -8,7 +8,7 @@
  * INTEGRATION.md shows the stub a reference maintainer would add.
  *
  * Conventions
- *  - Every pointer is a DEVICE pointer unless the name ends in _host.  The caller owns all
+ *  - Every pointer is a DEVICE pointer unless the name ends in _host (only the eksb_csv_* functions).  The caller owns all
  *    buffers; the library never allocates.  `stream` is a cudaStream_t passed as void*.
  *  - All calls are asynchronous on `stream` and return 0, or a negative EKSB_E* code
  *    (message via eksb_last_error_string()).  Numerical trouble inside a track (a
@@ -240,6 +240,34 @@ EKSB_API int eksb_pca_setup_f64(double* obs, long B, long T, int n, int p, doubl
 EKSB_API int eksb_pca_setup_f32(float* obs, long B, long T, int n, int p, double quantile, double smooth_param, int center,
                        float* means, float* C, float* S0, float* Q, double* workspace, size_t workspace_bytes,
                        int* status, void* stream);
+
+/* ---- asynchronous-view alignment (multiview_pca_smoother.py:70-101) -----------------
+ * out[s][q][j] = linear interpolation of series s (src (S,Ts,K) row-major, sampled at the increasing times
+ * ts_src (Ts)) at query time ts_q[q], with scipy interp1d's arithmetic (slope * (x - x_lo) + y_lo, no FMA:
+ * bit-identical); queries outside [ts_src[0], ts_src[Ts-1]] extrapolate from the end interval (the reference
+ * drops such frames before calling, :83-86).  flip (K) may be null; where flip[j] != 0 the result is
+ * flip[j] - value (the mirror flip x -> img_width - x of :90-91).  out is (S,Tq,K). */
+EKSB_API int eksb_interp_rows_f64(const double* ts_src, const double* src, long S, long Ts, int K, const double* ts_q, long Tq,
+                         const double* flip, double* out, void* stream);
+EKSB_API int eksb_interp_rows_f32(const float* ts_src, const float* src, long S, long Ts, int K, const float* ts_q, long Tq,
+                         const float* flip, float* out, void* stream);
+
+/* ---- on-disk format either side of the path: DLC / Lightning-Pose CSVs -------------
+ * HOST functions (the only ones in this header taking host pointers; no stream).  File layout: 3 header rows
+ * (scorer / bodyparts / coords), an integer index column, then n_cols numeric fields per row -- what the
+ * reference reads with pd.read_csv(header=[0,1,2], index_col=0) (scripts/multicam_example.py:85) and writes
+ * with DataFrame.to_csv (:139,:157).
+ *   shape: numeric body size (index column excluded).
+ *   read : body -> data_host (n_rows, n_cols) row-major float64 (correctly rounded, std::from_chars; empty or
+ *          "nan" fields -> NaN), index column -> index_host (nullable), the three raw header lines ->
+ *          header_host (nullable, NUL-terminated, truncated to header_cap).  n_threads <= 0: all host cores.
+ *   write: header lines + rows "index,v0,v1,..." with the shortest round-trip decimal in Python repr layout
+ *          (identical text to DataFrame.to_csv), NaN -> empty field. */
+EKSB_API int eksb_csv_dlc_shape_host(const char* path, long* n_rows, int* n_cols);
+EKSB_API int eksb_csv_dlc_read_host(const char* path, double* data_host, long n_rows, int n_cols, long* index_host,
+                           char* header_host, size_t header_cap, int n_threads);
+EKSB_API int eksb_csv_dlc_write_host(const char* path, const char* header_host, const long* index_host,
+                            const double* data_host, long n_rows, int n_cols);
 
 /* EKSB_DECLS_END (new declarations go above this line) */
 #ifdef __cplusplus

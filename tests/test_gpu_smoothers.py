@@ -126,3 +126,50 @@ def test_session_entry_equals_per_keypoint_calls():
     opt = smooth_session_multi_cam(stack, 0.01, 25, newton=True)
     for i, k in enumerate(kps):
         np.testing.assert_allclose(opt["y"][i], z[k]["shipped_opti"], rtol=0, atol=TOL)
+
+
+def test_view_alignment_kernel_is_bit_identical_to_interp1d():
+    """eksb_interp_rows == the oracle's paw_align (scipy interp1d arithmetic) bit for bit, incl. the x flip
+    and ragged timestamp ranges."""
+    from eks_b200.multiview_pca_smoother import _align_views
+    from oracle import restated_smoothers as osm
+    rng = np.random.default_rng(3)
+    Tl, Tr, M = 400, 1000, 5
+    ts_r = np.sort(rng.uniform(0.0, 10.0, Tr))
+    ts_l = np.sort(rng.uniform(-0.5, 10.5, Tl))                      # some left frames fall outside the right range
+    ts_l[50] = ts_r[123]                                             # an exact hit on a source timestamp
+    left = rng.uniform(0, 128, size=(M, Tl, 6)); right = rng.uniform(0, 128, size=(M, Tr, 6))
+    gl, gr = _align_views(left, right, ts_l, ts_r)
+    for m in range(M):
+        wl, wr = osm.paw_align(left[m], right[m], ts_l, ts_r)
+        assert gl[m].shape == wl.shape and np.array_equal(gl[m], wl)
+        assert np.array_equal(gr[m], wr)
+
+
+def test_csv_to_csv_session_matches_shipped_eks_csv(tmp_path):
+    """scripts/multicam_example.py end to end: member CSVs in -> eks.csv out, compared with the values the
+    reference shipped in data/mirror-mouse/output/eks.csv (frozen in tests/golden/mirror_mouse.npz)."""
+    from eks_b200 import io
+    from eks_b200.session import smooth_multicam_csvs
+    z = cases_of(load_golden("mirror_mouse.npz"))
+    kps, cams = sorted(z), ["top", "bot"]
+    M, T = z[kps[0]]["stack"].shape[:2]
+    names = [f"{k}_{c}" for c in cams for k in kps]                  # file order: all top views, then all bot views
+    cols = pd.MultiIndex.from_product([["tracker"], names, ["x", "y", "likelihood"]], names=["scorer", "bodyparts", "coords"])
+    paths = []
+    for m in range(M):
+        body = np.full((T, len(cols)), 0.9)
+        for k in kps:
+            for ci, c in enumerate(cams):
+                j = 3 * names.index(f"{k}_{c}")
+                body[:, j:j + 2] = z[k]["stack"][m][:, 2 * ci:2 * ci + 2]
+        path = tmp_path / f"member{m}.csv"
+        pd.DataFrame(body, columns=cols).to_csv(path)
+        paths.append(str(path))
+    out = smooth_multicam_csvs(paths, kps, cams, 0.01, 25, save_path=str(tmp_path / "out" / "eks.csv"))
+    back = pd.read_csv(tmp_path / "out" / "eks.csv", header=[0, 1, 2], index_col=0, float_precision="round_trip")
+    assert back.columns[0][0] == "ensemble-kalman_tracker" and back.shape == (T, len(cols))
+    for k in kps:
+        got = np.column_stack([back[("ensemble-kalman_tracker", f"{k}_{c}", xy)].to_numpy() for c in cams for xy in ("x", "y")])
+        np.testing.assert_allclose(got, z[k]["shipped_std"], rtol=0, atol=TOL)
+        assert (back[("ensemble-kalman_tracker", f"{k}_top", "likelihood")] == 1.0).all()
