@@ -19,9 +19,40 @@
 
 namespace eksb {
 
-constexpr int kSelWarps = 8;      // warps per tile in the select kernel
-constexpr int kMomSlices = 16;    // time slices (= warps) per tile in the moments kernel
 constexpr int kMomWarpsPerCta = 4;
+constexpr int kSetupSMs = 148;
+
+// time slices per tile: enough (tile, slice) work items to fill the GPU even for a few long tracks
+inline int select_slices(long tiles, long Tn) {      // one 8-warp CTA per (tile, slice)
+  long s = (kSetupSMs * 4 + tiles - 1) / tiles;
+  const long cap = (Tn + 2047) / 2048;
+  if (s > cap) s = cap;
+  return (int)(s < 1 ? 1 : s);
+}
+inline int moment_slices(long tiles, long Tn) {      // one warp per (tile, slice)
+  long s = (kSetupSMs * 32 + tiles - 1) / tiles;
+  if (s < 16) s = 16;
+  const long cap = (Tn + 255) / 256;
+  if (s > cap) s = cap;
+  if (s > 4096) s = 4096;
+  return (int)(s < 1 ? 1 : s);
+}
+template <int P> constexpr int mom_rows() { return 2 + 4 * P + P * (P + 1); }
+struct SetupWs {                  // workspace layout in 8-byte words
+  size_t thr, state, ghist, part, mx, total;
+};
+inline SetupWs setup_layout(long B, long Tn, int p, int elem_size) {
+  const size_t tiles = (size_t)num_tiles(B);
+  const int npass = elem_size;                       // 8-bit digits: 8 passes for f64, 4 for f32
+  SetupWs w;
+  w.thr = 0;
+  w.state = w.thr + tiles * kLanes;
+  w.ghist = w.state + tiles * 4 * kLanes;
+  w.part = w.ghist + (size_t)npass * tiles * 256 * kLanes / 2;
+  w.mx = w.part + tiles * (size_t)moment_slices((long)tiles, Tn) * (2 + 4 * p + p * (p + 1)) * kLanes;
+  w.total = w.mx + (tiles * (size_t)Tn * kLanes * elem_size + 7) / 8;
+  return w;
+}
 
 template <typename T> struct KeyOf;
 template <> struct KeyOf<double> {
@@ -60,71 +91,134 @@ __host__ __device__ inline void percentile_position(long T, double q, long& lo, 
 }
 
 // ---- 1. per-track percentile threshold ------------------------------------------------------------
+// Parallel over (tile, time slice) so that a handful of long tracks still fills the GPU:
+//   mx kernel    : max_vars[t] per track, once, into a compact [tile][t][32] buffer (8 B / track-frame)
+//   8 (4) passes : 8-bit digit histogram of the keys that match the prefix selected so far; per-CTA
+//                  shared-memory histogram [256][32 lanes], flushed with one global atomic per non-empty bin
+//   pick kernel  : one warp per tile walks its 256 bins to the digit holding rank k (between passes)
+//   tail kernel  : count(key <= v_lo) and min(key > v_lo)  ->  sorted[lo+1]
+//   thr kernel   : numpy's interpolation
+struct SelState {            // per track, [tile][field][32 lanes] as 64-bit words
+  static constexpr int PREFIX = 0, RANK = 1, CNT_LE = 2, NEXT = 3, WORDS = 4;
+};
+
 template <typename T, int P>
-__global__ void __launch_bounds__(kSelWarps* kLanes)
-setup_select_kernel(const T* __restrict__ obs, long B, long Tn, double q, double* __restrict__ thr) {
+__global__ void __launch_bounds__(256)
+setup_mx_kernel(const T* __restrict__ obs, long tiles, long Tn, T* __restrict__ mx) {
+  const long line = (long)blockIdx.x * 8 + (threadIdx.x >> 5);      // (g, t)
+  const int lane = threadIdx.x & 31;
+  if (line >= tiles * Tn) return;
+  mx[line * kLanes + lane] = frame_max_var<T, P>(obs + line * (2 * P) * kLanes + lane);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+setup_hist_kernel(const T* __restrict__ mx, long Tn, int slices, int shift, const unsigned long long* __restrict__ state,
+                  unsigned int* __restrict__ ghist /* [tile][256][32], this pass */) {
   using K = KeyOf<T>;
   using Key = typename K::type;
   __shared__ unsigned int hist[256][kLanes];
-  __shared__ Key s_prefix[kLanes];
-  __shared__ long s_rank[kLanes];
-  __shared__ unsigned int s_cnt_le[kLanes];
-  __shared__ Key s_next[kSelWarps][kLanes];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long g = blockIdx.x / slices;
+  const int sl = (int)(blockIdx.x - g * slices);
+  for (int i = threadIdx.x; i < 256 * kLanes; i += blockDim.x) (&hist[0][0])[i] = 0;
+  __syncthreads();
+  const Key prefix = (Key)state[(g * SelState::WORDS + SelState::PREFIX) * kLanes + lane];
+  const bool top = (shift == K::kBits - 8);
+  const long len = (Tn + slices - 1) / slices;
+  const long t0 = sl * len, t1 = (t0 + len < Tn) ? t0 + len : Tn;
+  const T* base = mx + g * Tn * kLanes + lane;
+  for (long t = t0 + warp; t < t1; t += 8) {
+    const Key key = K::of(base[t * kLanes]);
+    if (top || (key >> ((shift + 8) & (K::kBits - 1))) == (prefix >> ((shift + 8) & (K::kBits - 1))))
+      atomicAdd(&hist[(unsigned)(key >> shift) & 255u][lane], 1u);
+  }
+  __syncthreads();
+  unsigned int* gh = ghist + g * 256 * kLanes;
+  for (int i = threadIdx.x; i < 256 * kLanes; i += blockDim.x) {
+    const unsigned int c = (&hist[0][0])[i];
+    if (c) atomicAdd(&gh[i], c);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kLanes)
+setup_pick_kernel(const unsigned int* __restrict__ ghist, int shift, unsigned long long* __restrict__ state) {
+  using Key = typename KeyOf<T>::type;
   const long g = blockIdx.x;
-  const T* base = obs + (g * Tn * (2 * P)) * kLanes + lane;
+  const int lane = threadIdx.x;
+  unsigned long long* st = state + g * SelState::WORDS * kLanes + lane;
+  long k = (long)st[SelState::RANK * kLanes];
+  const unsigned int* gh = ghist + g * 256 * kLanes + lane;
+  int d = 0;
+  for (; d < 255; ++d) {
+    const unsigned c = gh[d * kLanes];
+    if (k < (long)c) break;
+    k -= c;
+  }
+  st[SelState::RANK * kLanes] = (unsigned long long)k;
+  st[SelState::PREFIX * kLanes] |= (unsigned long long)((Key)d << shift);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+setup_tail_kernel(const T* __restrict__ mx, long Tn, int slices, unsigned long long* __restrict__ state) {
+  using K = KeyOf<T>;
+  using Key = typename K::type;
+  __shared__ unsigned int s_cnt[kLanes];
+  __shared__ unsigned long long s_next[kLanes];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long g = blockIdx.x / slices;
+  const int sl = (int)(blockIdx.x - g * slices);
+  if (warp == 0) { s_cnt[lane] = 0; s_next[lane] = ~0ull; }
+  __syncthreads();
+  unsigned long long* st = state + g * SelState::WORDS * kLanes + lane;
+  const Key klo = (Key)st[SelState::PREFIX * kLanes];
+  const long len = (Tn + slices - 1) / slices;
+  const long t0 = sl * len, t1 = (t0 + len < Tn) ? t0 + len : Tn;
+  const T* base = mx + g * Tn * kLanes + lane;
+  unsigned cnt = 0;
+  unsigned long long nxt = ~0ull;
+  for (long t = t0 + warp; t < t1; t += 8) {
+    const Key key = K::of(base[t * kLanes]);
+    if (key <= klo) ++cnt;
+    else if ((unsigned long long)key < nxt) nxt = key;
+  }
+  atomicAdd(&s_cnt[lane], cnt);
+  atomicMin(&s_next[lane], nxt);
+  __syncthreads();
+  if (warp == 0) {
+    if (s_cnt[lane]) atomicAdd(&st[SelState::CNT_LE * kLanes], (unsigned long long)s_cnt[lane]);
+    if (s_next[lane] != ~0ull) atomicMin(&st[SelState::NEXT * kLanes], s_next[lane]);
+  }
+}
+
+__global__ void setup_init_state_kernel(unsigned long long* __restrict__ state, long lo) {
+  unsigned long long* st = state + (long)blockIdx.x * SelState::WORDS * kLanes + threadIdx.x;
+  st[SelState::RANK * kLanes] = (unsigned long long)lo;
+  st[SelState::NEXT * kLanes] = ~0ull;
+}
+
+template <typename T>
+__global__ void setup_thr_kernel(const unsigned long long* __restrict__ state, long B, long Tn, double q,
+                                 double* __restrict__ thr) {
+  using K = KeyOf<T>;
+  using Key = typename K::type;
+  const long b = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const long g = b / kLanes;
+  const int lane = (int)(b - g * kLanes);
+  const unsigned long long* st = state + g * SelState::WORDS * kLanes + lane;
   long lo;
   double gamma;
   percentile_position(Tn, q, lo, gamma);
-  if (warp == 0) { s_prefix[lane] = 0; s_rank[lane] = lo; }
-  for (int shift = K::kBits - 8; shift >= 0; shift -= 8) {
-    for (int i = threadIdx.x; i < 256 * kLanes; i += blockDim.x) (&hist[0][0])[i] = 0;
-    __syncthreads();
-    const Key prefix = s_prefix[lane];
-    const bool top = (shift == K::kBits - 8);
-    for (long t = warp; t < Tn; t += kSelWarps) {
-      const Key key = K::of(frame_max_var<T, P>(base + t * (2 * P) * kLanes));
-      if (top || (key >> (shift + 8)) == (prefix >> (shift + 8)))
-        atomicAdd(&hist[(unsigned)(key >> shift) & 255u][lane], 1u);
-    }
-    __syncthreads();
-    if (warp == 0) {
-      long k = s_rank[lane];
-      int d = 0;
-      for (; d < 255; ++d) {
-        const unsigned c = hist[d][lane];
-        if (k < (long)c) break;
-        k -= c;
-      }
-      s_rank[lane] = k;
-      s_prefix[lane] = prefix | ((Key)d << shift);
-    }
-    __syncthreads();
-  }
-  // v_lo = sorted[lo] is now known exactly; sorted[lo+1] = v_lo if enough copies, else the next larger value
-  const Key klo = s_prefix[lane];
-  unsigned cnt_le = 0;
-  Key nxt = ~(Key)0;
-  for (long t = warp; t < Tn; t += kSelWarps) {
-    const Key key = K::of(frame_max_var<T, P>(base + t * (2 * P) * kLanes));
-    if (key <= klo) ++cnt_le;
-    else if (key < nxt) nxt = key;
-  }
-  if (warp == 0) s_cnt_le[lane] = 0;
-  __syncthreads();
-  atomicAdd(&s_cnt_le[lane], cnt_le);
-  s_next[warp][lane] = nxt;
-  __syncthreads();
-  if (warp == 0) {
-    for (int w = 1; w < kSelWarps; ++w) nxt = s_next[w][lane] < nxt ? s_next[w][lane] : nxt;
-    const double a = (double)K::back(klo);
-    const double b2 = ((long)s_cnt_le[lane] >= lo + 2 || lo + 1 >= Tn) ? a : (double)K::back(nxt);
-    const double diff = __dsub_rn(b2, a);
-    double v = __dadd_rn(a, __dmul_rn(diff, gamma));
-    if (gamma >= 0.5) v = __dsub_rn(b2, __dmul_rn(diff, __dsub_rn(1.0, gamma)));
-    const long b = g * kLanes + lane;
-    if (b < B) thr[b] = v;
-  }
+  const double a = (double)K::back((Key)st[SelState::PREFIX * kLanes]);
+  const bool same = (long)st[SelState::CNT_LE * kLanes] >= lo + 2 || lo + 1 >= Tn || st[SelState::NEXT * kLanes] == ~0ull;
+  const double b2 = same ? a : (double)K::back((Key)st[SelState::NEXT * kLanes]);
+  const double diff = __dsub_rn(b2, a);
+  double v = __dadd_rn(a, __dmul_rn(diff, gamma));
+  if (gamma >= 0.5) v = __dsub_rn(b2, __dmul_rn(diff, __dsub_rn(1.0, gamma)));
+  thr[b] = v;
 }
 
 // ---- 2. masked moments of y and of dy over the good frames ----------------------------------------
@@ -139,19 +233,19 @@ template <int P> struct MomRows {
 
 template <typename T, int P>
 __global__ void __launch_bounds__(kMomWarpsPerCta* kLanes)
-setup_moments_kernel(const T* __restrict__ obs, long B, long Tn, const double* __restrict__ thr,
+setup_moments_kernel(const T* __restrict__ obs, long B, long Tn, int slices, const double* __restrict__ thr,
                      double* __restrict__ part) {
   using MR = MomRows<P>;
   constexpr int PS = MR::PS;
   const int lane = threadIdx.x & 31;
   const long w = (long)blockIdx.x * kMomWarpsPerCta + (threadIdx.x >> 5);
-  const long g = w / kMomSlices;
-  const int sl = (int)(w - g * kMomSlices);
+  const long g = w / slices;
+  const int sl = (int)(w - g * slices);
   if (g >= num_tiles_dev(B)) return;
   const long b = g * kLanes + lane;
   const double th = thr[b < B ? b : B - 1];
   const T* base = obs + (g * Tn * (2 * P)) * kLanes + lane;
-  const long len = (Tn + kMomSlices - 1) / kMomSlices;
+  const long len = (Tn + slices - 1) / slices;
   const long t0 = sl * len, t1 = (t0 + len < Tn) ? t0 + len : Tn;
   double sh[P], sy[P], syy[PS], sd[P], sdd[PS], first[P], last[P];
   double n0 = 0, nd = 0;
@@ -192,7 +286,7 @@ setup_moments_kernel(const T* __restrict__ obs, long B, long Tn, const double* _
       n0 += 1;
     }
   }
-  double* o = part + ((g * kMomSlices + sl) * MR::ROWS) * kLanes + lane;
+  double* o = part + ((g * slices + sl) * MR::ROWS) * kLanes + lane;
   o[MR::N0 * kLanes] = n0;
   o[MR::ND * kLanes] = nd;
 #pragma unroll
@@ -269,7 +363,7 @@ template <int P> __device__ __noinline__ void jacobi_eig(double* a, double* d, d
 
 template <typename T, int P, int N>
 __global__ void setup_finalize_kernel(const T* __restrict__ obs, const double* __restrict__ part, long B, long Tn,
-                                      double smooth_param, T* __restrict__ means, T* __restrict__ Cout,
+                                      int slices, double smooth_param, T* __restrict__ means, T* __restrict__ Cout,
                                       T* __restrict__ S0, T* __restrict__ Q, int* __restrict__ status) {
   using MR = MomRows<P>;
   constexpr int PS = MR::PS;
@@ -281,8 +375,8 @@ __global__ void setup_finalize_kernel(const T* __restrict__ obs, const double* _
   for (int j = 0; j < P; ++j) sy[j] = sd[j] = last[j] = 0;
   for (int j = 0; j < PS; ++j) syy[j] = sdd[j] = 0;
   bool have = false;
-  for (int sl = 0; sl < kMomSlices; ++sl) {
-    const double* r = part + ((g * kMomSlices + sl) * MR::ROWS) * kLanes + lane;
+  for (int sl = 0; sl < slices; ++sl) {
+    const double* r = part + ((g * slices + sl) * MR::ROWS) * kLanes + lane;
     const double n_s = r[MR::N0 * kLanes];
     if (n_s == 0) continue;
     if (have) {                                 // stitch: first good frame of this slice follows `last`
@@ -367,21 +461,41 @@ __global__ void center_rows_kernel(T* __restrict__ rec, const T* __restrict__ me
 template <typename T, int P>
 static int setup_run(T* obs, long B, long Tn, int n, double q, double s, int center, T* means, T* C, T* S0, T* Q,
                      double* ws, int* status, cudaStream_t st) {
-  using MR = MomRows<P>;
-  const long tiles = num_tiles(B);
-  double* thr = ws;
-  double* part = ws + tiles * kLanes;
-  setup_select_kernel<T, P><<<(unsigned)tiles, kSelWarps * kLanes, 0, st>>>(obs, B, Tn, q, thr);
-  const long warps = tiles * kMomSlices;
-  setup_moments_kernel<T, P><<<(unsigned)((warps + kMomWarpsPerCta - 1) / kMomWarpsPerCta), kMomWarpsPerCta * kLanes, 0, st>>>(
-      obs, B, Tn, thr, part);
+  using Key = typename KeyOf<T>::type;
+  static_assert(MomRows<P>::ROWS == mom_rows<P>(), "workspace row count");
   if (n != 3) { set_error("pca_setup: n=%d (the reference fits 3 components)", n); return EKSB_EDIM; }
-  setup_finalize_kernel<T, P, 3><<<(unsigned)((B + 63) / 64), 64, 0, st>>>(obs, part, B, Tn, s, means, C, S0, Q, status);
+  const long tiles = num_tiles(B);
+  const SetupWs L = setup_layout(B, Tn, P, (int)sizeof(T));
+  double* thr = ws + L.thr;
+  unsigned long long* state = reinterpret_cast<unsigned long long*>(ws + L.state);
+  unsigned int* ghist = reinterpret_cast<unsigned int*>(ws + L.ghist);
+  double* part = ws + L.part;
+  T* mx = reinterpret_cast<T*>(ws + L.mx);
+  const int npass = (int)sizeof(Key), ssl = select_slices(tiles, Tn), msl = moment_slices(tiles, Tn);
+  // state: prefix 0, rank = lo, cnt_le 0, next = ~0 ; histograms 0
+  long lo;
+  double gamma;
+  percentile_position(Tn, q, lo, gamma);
+  cudaMemsetAsync(ghist, 0, (size_t)npass * tiles * 256 * kLanes * sizeof(unsigned int), st);
+  cudaMemsetAsync(state, 0, (size_t)tiles * SelState::WORDS * kLanes * 8, st);
+  setup_init_state_kernel<<<(unsigned)tiles, kLanes, 0, st>>>(state, lo);
+  setup_mx_kernel<T, P><<<(unsigned)((tiles * Tn + 7) / 8), 256, 0, st>>>(obs, tiles, Tn, mx);
+  for (int pass = 0; pass < npass; ++pass) {
+    const int shift = 8 * (npass - 1 - pass);
+    unsigned int* gh = ghist + (size_t)pass * tiles * 256 * kLanes;
+    setup_hist_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, ssl, shift, state, gh);
+    setup_pick_kernel<T><<<(unsigned)tiles, kLanes, 0, st>>>(gh, shift, state);
+  }
+  setup_tail_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, ssl, state);
+  setup_thr_kernel<T><<<(unsigned)((B + 127) / 128), 128, 0, st>>>(state, B, Tn, q, thr);
+  const long warps = tiles * msl;
+  setup_moments_kernel<T, P><<<(unsigned)((warps + kMomWarpsPerCta - 1) / kMomWarpsPerCta), kMomWarpsPerCta * kLanes, 0, st>>>(
+      obs, B, Tn, msl, thr, part);
+  setup_finalize_kernel<T, P, 3><<<(unsigned)((B + 63) / 64), 64, 0, st>>>(obs, part, B, Tn, msl, s, means, C, S0, Q, status);
   if (center) {
     const long lines = tiles * Tn * P;
     center_rows_kernel<T><<<(unsigned)((lines + 7) / 8), 8 * kLanes, 0, st>>>(obs, means, B, Tn, 2 * P, P);
   }
-  (void)sizeof(MR);
   return check_launch("pca_setup kernels");
 }
 
@@ -390,7 +504,7 @@ static int setup_api(T* obs, long B, long Tn, int n, int p, double q, double s, 
                      double* ws, size_t ws_bytes, int* status, void* stream) {
   if (!obs || !means || !C || !S0 || !Q || !ws || B <= 0 || Tn <= 1) { set_error("pca_setup: null pointer or empty batch"); return EKSB_EARG; }
   if (!(q >= 0.0 && q <= 100.0)) { set_error("pca_setup: quantile %g outside [0,100]", q); return EKSB_EARG; }
-  if (ws_bytes < eksb_pca_setup_workspace_bytes(B, p)) { set_error("pca_setup: workspace too small"); return EKSB_EARG; }
+  if (ws_bytes < eksb_pca_setup_workspace_bytes(B, Tn, p, (int)sizeof(T))) { set_error("pca_setup: workspace too small"); return EKSB_EARG; }
   cudaStream_t st = (cudaStream_t)stream;
   switch (p) {
     case 4: return setup_run<T, 4>(obs, B, Tn, n, q, s, center, means, C, S0, Q, ws, status, st);
@@ -405,10 +519,9 @@ static int setup_api(T* obs, long B, long Tn, int n, int p, double q, double s, 
 
 using namespace eksb;
 
-extern "C" size_t eksb_pca_setup_workspace_bytes(long B, int p) {
-  if (B <= 0 || p <= 0) return 0;
-  const size_t rows = 3 + 4 * (size_t)p + (size_t)p * (p + 1);
-  return (size_t)num_tiles(B) * kLanes * sizeof(double) * (1 + kMomSlices * rows);
+extern "C" size_t eksb_pca_setup_workspace_bytes(long B, long T, int p, int elem_size) {
+  if (B <= 0 || T <= 0 || p <= 0 || (elem_size != 4 && elem_size != 8)) return 0;
+  return setup_layout(B, T, p, elem_size).total * 8;
 }
 extern "C" int eksb_pca_setup_f64(double* obs, long B, long T, int n, int p, double quantile, double smooth_param,
                                   int center, double* means, double* C, double* S0, double* Q, double* workspace,

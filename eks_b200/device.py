@@ -214,7 +214,7 @@ def pca_setup(obs, B, T, p, quantile, smooth_param, n=3, center=True, status=Non
     C = torch.empty((B, p, n), dtype=dt, device=dev)
     S0 = torch.empty((B, n, n), dtype=dt, device=dev)
     Q = torch.empty((B, n, n), dtype=dt, device=dev)
-    nbytes = lib().eksb_pca_setup_workspace_bytes(B, p)
+    nbytes = lib().eksb_pca_setup_workspace_bytes(B, T, p, obs.element_size())
     ws = torch.empty(max(1, nbytes // 8), dtype=torch.float64, device=dev)
     if status is None:
         status = torch.zeros(B, dtype=torch.int32, device=dev)

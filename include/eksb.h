@@ -232,8 +232,9 @@ EKSB_API int eksb_kf_rts_scan_f32(const float* obs, const float* m0, const float
  *   Q (B,n,n)     = smooth_param * cov(difference of consecutive good PCs), ddof 1 (:726-728)
  * (m0 = 0 and A = I are constants, :721,:724).  center != 0 also subtracts means from the y rows in place
  * (:702-705), leaving obs ready for eksb_kf_forward.  status[b] = 1 if a track has < 3 good frames.
- * p in {4,6,8}, n = 3.  workspace: eksb_pca_setup_workspace_bytes(B, p) bytes (doubles). */
-EKSB_API size_t eksb_pca_setup_workspace_bytes(long B, int p);
+ * p in {4,6,8}, n = 3.  workspace: eksb_pca_setup_workspace_bytes(B, T, p, sizeof(scalar)) bytes (mostly the
+ * B*T max-variance buffer the radix select re-reads). */
+EKSB_API size_t eksb_pca_setup_workspace_bytes(long B, long T, int p, int elem_size);
 EKSB_API int eksb_pca_setup_f64(double* obs, long B, long T, int n, int p, double quantile, double smooth_param, int center,
                        double* means, double* C, double* S0, double* Q, double* workspace, size_t workspace_bytes,
                        int* status, void* stream);
