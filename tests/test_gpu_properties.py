@@ -1,0 +1,88 @@
+"""GPU: size-independent properties of the hot path at sizes the CPU oracle cannot reach
+(thousands of tracks / a million frames), complementing the oracle comparisons in test_gpu_core.py:
+  * the smoothed mean is LINEAR in the observations and the covariances do not depend on them
+    (eks/ensemble_kalman.py:102-105,160-161: y only enters through the innovation);
+  * the block-tridiagonal Newton solve equals filter + RTS;
+  * the parallel-in-time scan equals the sequential kernels;
+  * a shard of tracks processed alone equals the same tracks inside the full batch, bit for bit.
+Tolerances: fp64 1e-8 relative to the largest smoothed value (north_star bar 1e-5)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _batch(B, T, p=4, n=3, seed=0, dt=None):
+    import torch
+    from eks_b200 import device as dev
+    dt = dt or torch.float64
+    d = torch.device("cuda", 0)
+    g = torch.Generator(device=d); g.manual_seed(seed)
+    tiles = dev.num_tiles(B)
+    obs = torch.empty(tiles, T, 2 * p, 32, dtype=dt, device=d)
+    obs[:, :, :p] = torch.randn(tiles, T, p, 32, dtype=dt, device=d, generator=g).cumsum_(1).mul_(0.05)
+    obs[:, :, p:] = torch.exp(torch.randn(tiles, T, p, 32, dtype=dt, device=d, generator=g) * 0.8 - 1.5)
+    rng = np.random.default_rng(seed)
+    C = np.linalg.qr(rng.normal(size=(B, p, n)))[0]
+    prm = dev.TrackParams.from_numpy(np.zeros(n), np.eye(n), C, np.diag([1.0, 0.999, 0.99]), 1e-3 * np.eye(n), dtype=dt, device=d)
+    return obs, prm
+
+
+def _smooth(obs, prm, B, T):
+    from eks_b200 import device as dev
+    filt, _, st = dev.kf_forward(obs.reshape(-1), prm, B, T)
+    out = dev.rts_backward(filt, prm, B, T, inplace=True, status=st)
+    assert int(st.sum()) == 0
+    return out["smth"].reshape(-1, T, 9, 32), out["ym"].reshape(-1, T, 4, 32)
+
+
+def test_smoothed_mean_is_linear_in_y_and_covariance_ignores_y():
+    import torch
+    B, T = 4096, 5000
+    obs1, prm = _batch(B, T, seed=1)
+    obs2, _ = _batch(B, T, seed=2)
+    obs2[:, :, 4:] = obs1[:, :, 4:]                                   # same ensemble variances
+    a, b = 0.7, -1.9
+    mix = obs1.clone(); mix[:, :, :4] = a * obs1[:, :, :4] + b * obs2[:, :, :4]
+    s1, y1 = _smooth(obs1, prm, B, T); s2, y2 = _smooth(obs2, prm, B, T); sm, ym = _smooth(mix, prm, B, T)
+    scale = float(sm[:, :, :3].abs().max())
+    assert float((sm[:, :, :3] - (a * s1[:, :, :3] + b * s2[:, :, :3])).abs().max()) < 1e-8 * scale
+    assert float((ym - (a * y1 + b * y2)).abs().max()) < 1e-8 * scale
+    assert torch.equal(sm[:, :, 3:], s1[:, :, 3:]) and torch.equal(s2[:, :, 3:], s1[:, :, 3:])   # covariances: bit-identical
+
+
+def test_block_tridiagonal_solve_equals_filter_plus_rts_at_scale():
+    from eks_b200 import device as dev
+    B, T = 2048, 20000
+    obs, prm = _batch(B, T, seed=3)
+    sm, _ = _smooth(obs, prm, B, T)
+    sol = dev.btd_solve(obs.reshape(-1), prm, B, T)
+    assert int(sol["status"].sum()) == 0
+    x = sol["sol"].reshape(-1, T, 9, 32)
+    scale = float(sm[:, :, :3].abs().max())
+    assert float((x[:, :, :3] - sm[:, :, :3]).abs().max()) < 1e-8 * scale
+    assert float((x[:, :, 3:] - sm[:, :, 3:]).abs().max()) < 1e-8 * float(sm[:, :, 3:].abs().max())
+
+
+def test_scan_equals_sequential_on_long_tracks():
+    from eks_b200 import device as dev
+    B, T = 64, 1_000_000
+    obs, prm = _batch(B, T, seed=4)
+    sm, ym = _smooth(obs, prm, B, T)
+    sc = dev.kf_rts_scan(obs.reshape(-1), prm, B, T)
+    assert int(sc["status"].sum()) == 0
+    scale = float(sm[:, :, :3].abs().max())
+    assert float((sc["smth"].reshape(-1, T, 9, 32)[:, :, :3] - sm[:, :, :3]).abs().max()) < 1e-8 * scale
+    assert float((sc["ym"].reshape(-1, T, 4, 32) - ym).abs().max()) < 1e-8 * scale
+
+
+def test_shard_of_a_large_batch_is_bitwise_identical():
+    import torch
+    from eks_b200 import device as dev
+    B, T = 8192, 2000
+    obs, prm = _batch(B, T, seed=5)
+    full, _ = _smooth(obs, prm, B, T)
+    lo, hi = 3072, 5120                                                # tile-aligned shard, as selection.shard_bounds yields
+    sub = dev.TrackParams(prm.m0, prm.S0, prm.C[lo:hi].contiguous(), prm.A, prm.Q, a_mode=prm.a_mode)
+    part, _ = _smooth(obs[lo // 32:hi // 32].contiguous(), sub, hi - lo, T)
+    assert torch.equal(part, full[lo // 32:hi // 32])
