@@ -57,6 +57,29 @@ EKSB_HD double rcp(double x) {
 #endif
 }
 
+// Shorter-latency reciprocal for the forward chain's critical path: one Newton step on the MUFU seed
+// (double: seed 2^-23 -> ~2^-45 relative, i.e. ~3e-14; float: the seed itself, ~1e-7).  The filter is
+// contractive, so this error does not accumulate; parity bars are 1e-5 (f64) / 1e-3 (f32) relative.
+EKSB_HD float rcp_chain(float x) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return 1.0f / x;
+#endif
+}
+EKSB_HD double rcp_chain(double x) {
+#if defined(__CUDA_ARCH__)
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  const double e = fma(-x, r, 1.0);
+  return fma(r, e, r);
+#else
+  return 1.0 / x;
+#endif
+}
+
 // ---------------------------------------------------------------------------
 // SPD inverse of a packed symmetric matrix.  Returns det(a) (used by the NLL).
 // N<=3: closed-form adjugate (one reciprocal, short dependency chain);
@@ -652,6 +675,62 @@ EKSB_HD void fwd_chain(const Params<T, N, P, AM>& prm, const T* rec, bool do_pre
   sym_matvec<T, N>(V, u, Vu);
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) m[i] = mp[i] + Vu[i];
+}
+
+// Forward chain with the covariance carried as V = Nm * r (numerator matrix and the scalar 1/det of the
+// last update) so that the scaling by r folds into the next predict:  S = AA o (Nm r) + Q = fma(AA o Nm, r, Q).
+// Per frame the dependency path is  S (1) -> Id + Lam S (3) -> adjugate (2) -> det (3) -> rcp_chain (~4)
+// instead of ... -> rcp (~7) -> scale (1) -> predict (1).  Diagonal A and N <= 3 only (every shipped config);
+// Vout receives the normalised covariance (off the path).  First use: Nm = V, r = 1.
+template <typename T, int N, int P>
+EKSB_HD void fwd_chain_scaled(const Params<T, N, P, 0>& prm, const T* rec, bool do_predict, T* m, T* Nm, T& r, T* Vout,
+                              bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T mp[N], S[NS], u[N], Nu[N];
+  if (do_predict) {
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) mp[i] = prm.A[i] * m[i];
+    EKSB_UNROLL
+    for (int k = 0; k < NS; ++k) S[k] = (prm.AA[k] * Nm[k]) * r + prm.Q[k];
+  } else {
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) mp[i] = m[i];
+    EKSB_UNROLL
+    for (int k = 0; k < NS; ++k) S[k] = Nm[k] * r;
+  }
+  sym_matvec<T, N>(rec, mp, u);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
+  T M[N][N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T a = (i == j) ? T(1) : T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) a += rec[sym_idx<N>(i, k)] * S[sym_idx<N>(k, j)];
+      M[i][j] = a;
+    }
+  }
+  T adj[N][N], det;
+  gen_adjugate<T, N>(M, adj, det);
+  ok = ok && (det > T(0)) && (S[0] > T(0));
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = i; j < N; ++j) {
+      T a = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) a += S[sym_idx<N>(i, k)] * adj[k][j];
+      Nm[sym_idx<N>(i, j)] = a;
+    }
+  }
+  r = rcp_chain(det);
+  sym_matvec<T, N>(Nm, u, Nu);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) m[i] = mp[i] + Nu[i] * r;
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) Vout[k] = Nm[k] * r;
 }
 
 template <typename T, int N, int P, int AM>

@@ -197,15 +197,25 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
     for (int i = 0; i < NS; ++i) V[i] = Vi[i];
   }
   T* f = filt + (g * Tn * SG) * kLanes + lane;
+  // covariance carried as V = Nm * rr between frames (fwd_chain_scaled) where the fast path applies
+  constexpr bool kScaled = (OP == 0 && AM == 0 && N <= 3);
+  T Nm[NS], rr = T(1);
+#pragma unroll
+  for (int i = 0; i < NS; ++i) Nm[i] = V[i];
   // one frame of the chain.  FIRST: frame 0 of the track (prior handling); LAST only matters to OP 1.
   auto frame = [&](const T* src, int j, bool is_first, bool is_last) {
     T rec[REC];
 #pragma unroll
     for (int r = 0; r < REC; ++r) rec[r] = src[(j * REC + r) * kLanes];
-    if (OP == 1)
+    if constexpr (OP == 1) {
       btd_fwd_chain<T, N>(bc, rec, is_first, is_last, iS0, iS0m0, m, V, ok);
-    else if (!(is_first && first == kPriorOnly))
-      fwd_chain<T, N, P, AM>(prm, rec, !(is_first && first == kPriorUpdate), m, V, ok);
+    } else if constexpr (kScaled) {
+      if (!(is_first && first == kPriorOnly))
+        fwd_chain_scaled<T, N, P>(prm, rec, !(is_first && first == kPriorUpdate), m, Nm, rr, V, ok);
+    } else {
+      if (!(is_first && first == kPriorOnly))
+        fwd_chain<T, N, P, AM>(prm, rec, !(is_first && first == kPriorUpdate), m, V, ok);
+    }
     T* o = f + j * (SG * kLanes);
 #pragma unroll
     for (int i = 0; i < N; ++i) o[i * kLanes] = m[i];

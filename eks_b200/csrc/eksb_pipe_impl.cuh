@@ -89,15 +89,16 @@ template <typename T, int H, int ROWS_IN, int REC, int FORCE_F = 0, int FORCE_NS
 #ifndef EKSB_BWD_NST
 #define EKSB_BWD_NST 0
 #endif
+#ifndef EKSB_BWD_WIDE_NST
+#define EKSB_BWD_WIDE_NST 3
+#endif
 constexpr int kFwdHelpers = EKSB_FWD_H, kBwdHelpers = EKSB_BWD_H;
 // instructions per frame (n=3, p=4, f64 SASS): forward chain / helper, backward chain / helpers
 constexpr float kFwdChainW = 118, kFwdHelperW = 125, kBwdChainW = 103, kBwdHelperW = 200;
 
-template <typename T, int N, int P, int AM, int OP = 0>
-static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
-                           long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
-  using Auto = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, EKSB_FWD_F, EKSB_FWD_NST>;
-  if (!Auto::ok) return EKSB_EDIM;
+template <typename T, int N, int P, int AM, int OP, typename Auto>
+static int launch_fwd_cfg(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
+                          long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
   using Cfg = typename Auto::type;
   auto kern = kf_forward_pipe_kernel<T, N, P, AM, OP, Cfg>;
   const int tpc = pick_tpc(num_tiles(B), Cfg::TPC, Auto::kTileSmem);
@@ -108,6 +109,25 @@ static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, c
   const int warps = make_roles(tpc, Cfg::H, kFwdChainW, kFwdHelperW, rm);
   kern<<<grid, warps * kLanes, smem, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, tpc, rm);
   return check_launch("kf_forward_pipe_kernel");
+}
+
+// Two ring shapes, like the backward pass.  With few tiles per SM the bytes in flight per SM (stages x
+// frames x record) bound the read bandwidth (Little's law: 256 tiles x 24 KB = 6 MB in flight sustained
+// ~5.7 TB/s algorithmic in f64); the "deep" ring (8-frame batches, 4 stages: 4x the bytes in flight) lifts
+// that to ~6.4 TB/s.  It needs ~100 KB per f64 tile, so it is used when the tiles of an SM fit.
+template <typename T, int N, int P, int AM, int OP = 0>
+static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
+                           long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
+  using Shallow = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, EKSB_FWD_F, EKSB_FWD_NST>;
+  using Deep = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, 8, 4>;
+  if constexpr (N <= 3 && Deep::ok) {
+    const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
+    static const bool shallow_only = getenv("EKSB_FWD_SHALLOW") != nullptr;
+    if (!shallow_only && per_sm <= Deep::TPC && per_sm * Deep::kTileSmem + 1024 <= kCtaSmemBudget)
+      return launch_fwd_cfg<T, N, P, AM, OP, Deep>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, st);
+  }
+  if (!Shallow::ok) return EKSB_EDIM;
+  return launch_fwd_cfg<T, N, P, AM, OP, Shallow>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, st);
 }
 
 template <typename T, int N, int P, int AM, int OP, int OUT, typename Auto>
@@ -133,7 +153,7 @@ template <typename T, int N, int P, int AM, int OP, int OUT>
 static int launch_bwd_pipe_out(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
                                T* smth, T* ym, T* yv, int* status, cudaStream_t st) {
   using Narrow = AutoCfg<T, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_F, EKSB_BWD_NST>;
-  using Wide = AutoCfg<T, 3, Dim<N>::SIGMA, Rec<N>::BWD, 6, 2>;
+  using Wide = AutoCfg<T, 3, Dim<N>::SIGMA, Rec<N>::BWD, 6, EKSB_BWD_WIDE_NST>;
   if constexpr (N <= 3 && Wide::ok) {
     const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
     static const bool narrow_only = getenv("EKSB_BWD_NARROW") != nullptr;

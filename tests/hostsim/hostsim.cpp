@@ -61,14 +61,25 @@ static int run_split(long Tn, const T* y, const T* ev, const T* m0, const T* S0,
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
   Params<T, N, P, AM> prm;
   load_params<T, N, P, AM>(prm, C, A, Q);
-  T m[N], V[NS];
+  T m[N], V[NS], Nm[NS], rr = T(1);
   for (int i = 0; i < N; ++i) m[i] = m0[i];
   load_sym<T, N>(V, S0);
+  for (int i = 0; i < NS; ++i) Nm[i] = V[i];
   bool ok = true;
   for (long t = 0; t < Tn; ++t) {
     T rec[Rec<N>::FWD];
     fwd_prep<T, N, P, AM>(prm, y + t * P, ev + t * P, rec);
-    if (!(t == 0 && first == kPriorOnly)) fwd_chain<T, N, P, AM>(prm, rec, !(t == 0 && first == kPriorUpdate), m, V, ok);
+    if (!(t == 0 && first == kPriorOnly)) {
+      if constexpr (AM == 0 && N <= 3) {     // same selection as kf_forward_pipe_kernel (kScaled)
+        if (t == 0) { for (int i = 0; i < NS; ++i) Nm[i] = V[i]; rr = T(1); }
+        fwd_chain_scaled<T, N, P>(prm, rec, !(t == 0 && first == kPriorUpdate), m, Nm, rr, V, ok);
+      } else {
+        fwd_chain<T, N, P, AM>(prm, rec, !(t == 0 && first == kPriorUpdate), m, V, ok);
+      }
+    } else {
+      for (int i = 0; i < NS; ++i) Nm[i] = V[i];
+      rr = T(1);
+    }
     for (int i = 0; i < N; ++i) filt[t * SG + i] = m[i];
     for (int i = 0; i < NS; ++i) filt[t * SG + N + i] = V[i];
   }
