@@ -949,16 +949,11 @@ template <typename T, int N, int P, int AM>
 EKSB_HD void fwd_summary_step(const Params<T, N, P, AM>& prm, const T* rec, T (*Phi)[N], T* b, T* C, T* eta, T* J,
                               bool& ok) {
   constexpr int NS = Dim<N>::NS;
-  T mp[N], S[NS], Sinv[NS], Lam[NS], V[NS], u[N], Vu[N];
+  T mp[N], S[NS], u[N], Vu[N];
   predict<T, N, P, AM>(prm, b, C, mp, S);
   sym_matvec<T, N>(rec, mp, u);
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
-  sym_inv<T, N>(S, Sinv, ok);
-  EKSB_UNROLL
-  for (int k = 0; k < NS; ++k) Lam[k] = Sinv[k] + rec[k];
-  sym_inv<T, N>(Lam, V, ok);
-  sym_matvec<T, N>(V, u, Vu);
   // Psi = A Phi
   T Psi[N][N];
   EKSB_UNROLL
@@ -975,64 +970,110 @@ EKSB_HD void fwd_summary_step(const Params<T, N, P, AM>& prm, const T* rec, T (*
       }
     }
   }
-  // SV = S^-1 V (full);  X = S^-1 - SV S^-1 (symmetric)
-  T SV[N][N], X[NS];
-  EKSB_UNROLL
-  for (int i = 0; i < N; ++i) {
+  // Everything below hangs off ONE matrix, Mi = (Id + Lam S)^-1 (Lam = rec[0..NS)):
+  //   V = S Mi,   S^-1 V = Mi,   G = V S^-1 = Mi^T,   X = S^-1 - S^-1 V S^-1 = Mi Lam   (symmetric)
+  // so the step needs no S^-1 and a single reciprocal (N <= 3: adjugate; else via two symmetric inverses).
+  T Mi[N][N], V[NS], X[NS];
+  if (N <= 3) {
+    T M[N][N], adj[N][N], det;
     EKSB_UNROLL
-    for (int j = 0; j < N; ++j) {
-      T s = T(0);
+    for (int i = 0; i < N; ++i) {
       EKSB_UNROLL
-      for (int k = 0; k < N; ++k) s += Sinv[sym_idx<N>(i, k)] * V[sym_idx<N>(k, j)];
-      SV[i][j] = s;
+      for (int j = 0; j < N; ++j) {
+        T a = (i == j) ? T(1) : T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) a += rec[sym_idx<N>(i, k)] * S[sym_idx<N>(k, j)];
+        M[i][j] = a;
+      }
+    }
+    gen_adjugate<T, N>(M, adj, det);
+    ok = ok && (det > T(0)) && (S[0] > T(0));
+    const T r = rcp(det);
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) Mi[i][j] = adj[i][j] * r;
+    }
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = i; j < N; ++j) {
+        T a = T(0), x = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) {
+          a += S[sym_idx<N>(i, k)] * Mi[k][j];
+          x += Mi[i][k] * rec[sym_idx<N>(k, j)];
+        }
+        V[sym_idx<N>(i, j)] = a;
+        X[sym_idx<N>(i, j)] = x;
+      }
+    }
+  } else {
+    T Sinv[NS], Lam[NS];
+    sym_inv<T, N>(S, Sinv, ok);
+    EKSB_UNROLL
+    for (int k = 0; k < NS; ++k) Lam[k] = Sinv[k] + rec[k];
+    sym_inv<T, N>(Lam, V, ok);
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) {
+        T a = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) a += Sinv[sym_idx<N>(i, k)] * V[sym_idx<N>(k, j)];
+        Mi[i][j] = a;
+      }
+    }
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = i; j < N; ++j) {
+        T a = Sinv[sym_idx<N>(i, j)];
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) a -= Mi[i][k] * Sinv[sym_idx<N>(k, j)];
+        X[sym_idx<N>(i, j)] = a;
+      }
     }
   }
-  EKSB_UNROLL
-  for (int i = 0; i < N; ++i) {
-    EKSB_UNROLL
-    for (int j = i; j < N; ++j) {
-      T s = Sinv[sym_idx<N>(i, j)];
-      EKSB_UNROLL
-      for (int k = 0; k < N; ++k) s -= SV[i][k] * Sinv[sym_idx<N>(k, j)];
-      X[sym_idx<N>(i, j)] = s;
-    }
-  }
-  // J += Psi^T X Psi ; eta += Psi^T S^-1 (V u)
+  sym_matvec<T, N>(V, u, Vu);
+  // J += Psi^T X Psi ; eta += Psi^T (S^-1 V u) = Psi^T (Mi u)
   T XP[N][N], w[N];
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) {
+    T wi = T(0);
     EKSB_UNROLL
     for (int j = 0; j < N; ++j) {
-      T s = T(0);
+      T a = T(0);
       EKSB_UNROLL
-      for (int k = 0; k < N; ++k) s += X[sym_idx<N>(i, k)] * Psi[k][j];
-      XP[i][j] = s;
+      for (int k = 0; k < N; ++k) a += X[sym_idx<N>(i, k)] * Psi[k][j];
+      XP[i][j] = a;
+      wi += Mi[i][j] * u[j];
     }
+    w[i] = wi;
   }
-  sym_matvec<T, N>(Sinv, Vu, w);
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) {
     EKSB_UNROLL
     for (int j = i; j < N; ++j) {
-      T s = T(0);
+      T a = T(0);
       EKSB_UNROLL
-      for (int k = 0; k < N; ++k) s += Psi[k][i] * XP[k][j];
-      J[sym_idx<N>(i, j)] += s;
+      for (int k = 0; k < N; ++k) a += Psi[k][i] * XP[k][j];
+      J[sym_idx<N>(i, j)] += a;
     }
     T e = T(0);
     EKSB_UNROLL
     for (int k = 0; k < N; ++k) e += Psi[k][i] * w[k];
     eta[i] += e;
   }
-  // Phi = (S^-1 V)^T Psi = V S^-1 A Phi ;  state update
+  // Phi = G Psi = Mi^T Psi ;  state update
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) {
     EKSB_UNROLL
     for (int j = 0; j < N; ++j) {
-      T s = T(0);
+      T a = T(0);
       EKSB_UNROLL
-      for (int k = 0; k < N; ++k) s += SV[k][i] * Psi[k][j];
-      Phi[i][j] = s;
+      for (int k = 0; k < N; ++k) a += Mi[k][i] * Psi[k][j];
+      Phi[i][j] = a;
     }
     b[i] = mp[i] + Vu[i];
   }

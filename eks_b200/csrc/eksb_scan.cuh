@@ -21,20 +21,51 @@ template <typename T> __device__ __forceinline__ void store_rows(T* dst, const T
   for (int i = 0; i < n; ++i) dst[i * kLanes] = v[i];
 }
 
-// ---- 1a. forward chunk summaries, chunks [1, nc) ------------------------------------------------
+// ---- 1a. forward chunk summaries, chunks [1, nc), plus the sequential run of chunk 0 -----------------
+// Work items [0, tiles): chunk 0 of each tile, run as the ordinary filter from the prior (it needs no
+// summary, only its end state, and would otherwise be a serial 1-warp-per-tile launch of its own).
+// Work items [tiles, tiles*nc): summary of chunk c >= 1.  Once the sensitivity Phi of a chunk's running
+// mean to its unknown start state has decayed below kPhiCut for all 32 tracks of the warp (the filter
+// forgets its start exponentially), J and eta have stopped changing and Phi is numerically zero, so the
+// rest of the chunk is the plain filter step (2.4x cheaper); the element is exact to ~kPhiCut * |x_start|.
+template <typename T> struct PhiCut;
+template <> struct PhiCut<double> { static constexpr double value = 1e-26; };
+template <> struct PhiCut<float> { static constexpr float value = 1e-13f; };
+
 template <typename T, int N, int P, int AM>
 __global__ void __launch_bounds__(kScanWarps* kLanes)
-scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ C, const T* __restrict__ A,
-                        const T* __restrict__ Q, int shared_mask, long B, long Tn, long L, long nc,
-                        T* __restrict__ fsum, int* __restrict__ status) {
-  constexpr int NS = Dim<N>::NS, R2 = 2 * P, SR = ScanRec<N>::FWD;
+scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
+                        const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
+                        long B, long Tn, long L, long nc, T* __restrict__ fsum, T* __restrict__ filt,
+                        int* __restrict__ status) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, SR = ScanRec<N>::FWD;
   const int lane = threadIdx.x & 31;
-  const long w = (long)blockIdx.x * kScanWarps + (threadIdx.x >> 5);     // work item = g*(nc-1) + (c-1)
-  const long g = w / (nc - 1);
-  const long c = w - g * (nc - 1) + 1;
-  if (g >= num_tiles_dev(B)) return;
-  const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
+  const long tiles = num_tiles_dev(B);
+  const long w = (long)blockIdx.x * kScanWarps + (threadIdx.x >> 5);
+  if (w >= tiles * nc) return;
   Params<T, N, P, AM> prm;
+  if (w < tiles) {                                         // chunk 0: ordinary filter from (m0, S0)
+    const long g = w;
+    const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
+    load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
+    T m[N], V[NS];
+    const T* pm = m0 + ((shared_mask & EKSB_SHARED_M0) ? 0 : bp * N);
+    const T* ps = S0 + ((shared_mask & EKSB_SHARED_S0) ? 0 : bp * (N * N));
+#pragma unroll
+    for (int i = 0; i < N; ++i) m[i] = pm[i];
+    load_sym<T, N>(V, ps);
+    const long t1 = L < Tn ? L : Tn;
+    double acc = 0.0;
+    const bool ok0 = kf_forward_range<T, N, P, AM, kLanes, 2, false>(prm, obs + (g * Tn * R2) * kLanes + lane,
+                                                                    filt + (g * Tn * SG) * kLanes + lane, t1,
+                                                                    kPriorUpdate, m, V, acc);
+    if (b < B && status && !ok0) status[b] = 1;
+    return;
+  }
+  const long wi = w - tiles;                               // work item = g*(nc-1) + (c-1)
+  const long g = wi / (nc - 1);
+  const long c = wi - g * (nc - 1) + 1;
+  const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
   T Phi[N][N], bb[N], Cc[NS], eta[N], J[NS];
 #pragma unroll
@@ -48,12 +79,34 @@ scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ C, cons
   bool ok = true;
   const long t1 = (c + 1) * L < Tn ? (c + 1) * L : Tn;
   const T* o = obs + (g * Tn * R2) * kLanes + lane;
-  for (long t = c * L; t < t1; ++t) {
+  long t = c * L;
+  for (; t < t1; ++t) {
     T cur[R2], rec[Rec<N>::FWD];
 #pragma unroll
     for (int r = 0; r < R2; ++r) cur[r] = o[(t * R2 + r) * kLanes];
     fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
     fwd_summary_step<T, N, P, AM>(prm, rec, Phi, bb, Cc, eta, J, ok);
+    if (((t - c * L) & 15) == 15) {                        // every 16 frames: has Phi died out for the whole warp?
+      T mx = T(0);
+#pragma unroll
+      for (int i = 0; i < N; ++i)
+#pragma unroll
+        for (int j = 0; j < N; ++j) mx = fmax(mx, fabs(Phi[i][j]));
+      if (__all_sync(0xffffffffu, mx < PhiCut<T>::value)) { ++t; break; }
+    }
+  }
+  if (t < t1) {                                            // tail: plain filter on (bb, Cc), Phi == 0
+#pragma unroll
+    for (int i = 0; i < N; ++i)
+#pragma unroll
+      for (int j = 0; j < N; ++j) Phi[i][j] = T(0);
+    for (; t < t1; ++t) {
+      T cur[R2], rec[Rec<N>::FWD];
+#pragma unroll
+      for (int r = 0; r < R2; ++r) cur[r] = o[(t * R2 + r) * kLanes];
+      fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
+      fwd_chain<T, N, P, AM>(prm, rec, true, bb, Cc, ok);
+    }
   }
   T* out = fsum + ((g * nc + c) * SR) * kLanes + lane;
 #pragma unroll
@@ -149,20 +202,38 @@ scan_fwd_rerun_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const
   if (b < B && status && !ok) status[b] = 1;
 }
 
-// ---- 1b. backward chunk summaries, chunks [0, nc-1) ----------------------------------------------
+// ---- 1b. backward chunk summaries, chunks [0, nc-1), plus the sequential run of the last chunk --------
+// Work items [0, tiles): the terminal chunk of each tile, smoothed directly (ms = mf at T-1); it only
+// touches its own frames, so it can ride in the launch that summarises the other chunks (smth may alias
+// filt).  Work items [tiles, tiles*nc): (E, g, L) summary of chunk c < nc-1.
 template <typename T, int N, int P, int AM>
 __global__ void __launch_bounds__(kScanWarps* kLanes)
-scan_bwd_summary_kernel(const T* __restrict__ filt, const T* __restrict__ C, const T* __restrict__ A,
+scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A,
                         const T* __restrict__ Q, int shared_mask, long B, long Tn, long L, long nc,
-                        T* __restrict__ bsum, int* __restrict__ status) {
-  constexpr int SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
+                        T* __restrict__ bsum, T* smth, T* __restrict__ ym, int* __restrict__ status) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
   const int lane = threadIdx.x & 31;
+  const long tiles = num_tiles_dev(B);
   const long w = (long)blockIdx.x * kScanWarps + (threadIdx.x >> 5);
-  const long g = w / (nc - 1);
-  const long c = w - g * (nc - 1);
-  if (g >= num_tiles_dev(B)) return;
-  const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
+  if (w >= tiles * nc) return;
   Params<T, N, P, AM> prm;
+  if (w < tiles) {
+    const long g = w;
+    const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
+    load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
+    T ms[N], Vs[NS];
+    const long t0 = (nc - 1) * L;
+    const long base = (g * Tn + t0) * kLanes;
+    const bool ok0 = rts_backward_range<T, N, P, AM, kLanes, 2>(prm, filt + base * SG + lane, smth + base * SG + lane,
+                                                               ym ? ym + base * P + lane : nullptr, nullptr, nullptr,
+                                                               Tn - t0, true, ms, Vs);
+    if (b < B && status && !ok0) status[b] = 1;
+    return;
+  }
+  const long wi = w - tiles;
+  const long g = wi / (nc - 1);
+  const long c = wi - g * (nc - 1);
+  const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
   T acc[SR];
 #pragma unroll

@@ -32,18 +32,22 @@ static int scan_run(const T* obs, const T* m0, const T* S0, const T* C, const T*
   auto blocks = [&](long items) { return (unsigned)((items + kScanWarps - 1) / kScanWarps); };
   const int thr = kScanWarps * kLanes;
   // forward pass
-  scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 0, 1, finit, filt, status);
-  if (nc > 1) {
-    scan_fwd_summary_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, fsum, status);
+  if (nc == 1) {
+    scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 0, 1, finit, filt, status);
+  } else {
+    // chunk 0 (sequential from the prior) rides in the same launch as the summaries of chunks >= 1
+    scan_fwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, fsum, filt, status);
     scan_fwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(filt, fsum, B, Tn, L, nc, finit, status);
     scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 1, nc, finit, filt, status);
   }
   int rc = check_launch("scan forward kernels");
   if (rc != EKSB_OK || !smth) return rc;
   // backward pass (smth may alias filt: a chunk only reads and writes its own frames)
-  scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, nc - 1, nc, binit, smth, ym, status);
-  if (nc > 1) {
-    scan_bwd_summary_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, bsum, status);
+  if (nc == 1) {
+    scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, nc - 1, nc, binit, smth, ym, status);
+  } else {
+    // the terminal chunk (sequential from the end of the track) rides in the summary launch
+    scan_bwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, bsum, smth, ym, status);
     scan_bwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(smth, bsum, B, Tn, L, nc, binit);
     scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, 0, nc - 1, binit, smth, ym, status);
   }

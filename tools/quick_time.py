@@ -38,7 +38,7 @@ if __name__ == "__main__":
     if len(sys.argv) > 1:                       # bits:B:T ...
         for a in sys.argv[1:]:
             bits, B, T = (int(x) for x in a.split(":"))
-            run(torch.float64 if bits == 64 else torch.float32, B, T, reps=2)
+            run(torch.float64 if bits == 64 else torch.float32, B, T, reps=int(os.environ.get("REPS", "2")))
     else:
         for dt in (torch.float32, torch.float64):
             for B, T in ((16384, 10000), (8192, 10000), (49152, 4000)):
