@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU-baseline sample time")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-sustained", action="store_true", help="skip the sustained device-copy context measurement")
     return ap.parse_args()
 
 
@@ -306,11 +307,42 @@ def gpu_main(a):
         k1 = {"kernel": "ensemble_tiled", "keypoint_frames_per_s": k1_tf / (k1_ms * 1e-3),
               "achieved_gbs": k1_tf * k1b / (k1_ms * 1e-3) / 1e9, "frac": k1_tf * k1b / (k1_ms * 1e-3) / 1e9 / peak}
 
+    # ---- context for the roofline: what a plain device copy SUSTAINS on this board right now (the peak in
+    # MEASURED_PEAKS.json is a best-of-10 burst; back-to-back launches of HBM-bound kernels sit at the
+    # board's power cap, where SM / fabric clocks -- and with them achievable bandwidth -- are lower)
+    sustained = None
+    if rank == 0 and not a.no_sustained:
+        del filt, ym
+        torch.cuda.empty_cache()
+        nbytes = 8 << 30
+        src = torch.empty(nbytes, dtype=torch.uint8, device=d); dst = torch.empty_like(src)
+        src.zero_(); dst.zero_()
+        sc = ClockSampler(local); sc.start()
+        for _ in range(20):
+            dst.copy_(src)
+        torch.cuda.synchronize()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 400
+        c0.record()
+        for _ in range(reps):
+            dst.copy_(src)
+        c1.record(); torch.cuda.synchronize()
+        sclk = sc.stop()
+        sustained = {"gbs": 2 * nbytes * reps / (c0.elapsed_time(c1) * 1e-3) / 1e9, "seconds": c0.elapsed_time(c1) * 1e-3,
+                     "how": "dst.copy_(src), 8 GiB buffers, 400 back-to-back copies after 20 warm-up copies",
+                     "sm_mhz": sclk["sm_mhz"], "reasons": sclk["reasons"]}
+        del src, dst
+        filt = ym = None
+    roof["sustained_copy"] = sustained
+    if sustained:
+        roof["step_frac_of_sustained_copy"] = roof["step_achieved"] / sustained["gbs"]
+
     # ---- e2e: public host API, H2D + D2H inside the timed region
     e2e = None
     launches = 2 * a.steps
     if not a.no_e2e:
-        del filt, ym, obs
+        filt = ym = None
+        del obs
         torch.cuda.empty_cache()
         Be = a.e2e_tracks
         pe = model_params(Be, 99 + rank)

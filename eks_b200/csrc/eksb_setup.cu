@@ -254,36 +254,51 @@ setup_moments_kernel(const T* __restrict__ obs, long B, long Tn, int slices, con
 #pragma unroll
   for (int j = 0; j < PS; ++j) syy[j] = sdd[j] = 0;
   bool have = false;
-  for (long t = t0; t < t1; ++t) {
-    const T* r = base + t * (2 * P) * kLanes;
-    if ((double)frame_max_var<T, P>(r) <= th) {
-      double y[P];
+  constexpr int kUn = 4;                       // frames whose records are loaded before any is processed
+  for (long tb = t0; tb < t1; tb += kUn) {
+    T raw[kUn][2 * P];
 #pragma unroll
-      for (int j = 0; j < P; ++j) y[j] = (double)r[j * kLanes];
-      if (have) {
-        double d[P];
+    for (int f = 0; f < kUn; ++f)
+      if (tb + f < t1) {
+        const T* r = base + (tb + f) * (2 * P) * kLanes;
 #pragma unroll
-        for (int j = 0; j < P; ++j) { d[j] = y[j] - last[j]; sd[j] += d[j]; }
+        for (int j = 0; j < 2 * P; ++j) raw[f][j] = r[j * kLanes];
+      }
+#pragma unroll
+    for (int f = 0; f < kUn; ++f) {
+      if (tb + f >= t1) break;
+      T mxv = raw[f][P];
+#pragma unroll
+      for (int j = 1; j < P; ++j) mxv = raw[f][P + j] > mxv ? raw[f][P + j] : mxv;
+      if ((double)(mxv + T(0)) <= th) {
+        double y[P];
+#pragma unroll
+        for (int j = 0; j < P; ++j) y[j] = (double)raw[f][j];
+        if (have) {
+          double d[P];
+#pragma unroll
+          for (int j = 0; j < P; ++j) { d[j] = y[j] - last[j]; sd[j] += d[j]; }
+          int k = 0;
+#pragma unroll
+          for (int i = 0; i < P; ++i)
+#pragma unroll
+            for (int j = i; j < P; ++j) sdd[k++] += d[i] * d[j];
+          nd += 1;
+        } else {
+#pragma unroll
+          for (int j = 0; j < P; ++j) first[j] = y[j];
+          have = true;
+        }
+        double c[P];
+#pragma unroll
+        for (int j = 0; j < P; ++j) { last[j] = y[j]; c[j] = y[j] - sh[j]; sy[j] += c[j]; }
         int k = 0;
 #pragma unroll
         for (int i = 0; i < P; ++i)
 #pragma unroll
-          for (int j = i; j < P; ++j) sdd[k++] += d[i] * d[j];
-        nd += 1;
-      } else {
-#pragma unroll
-        for (int j = 0; j < P; ++j) first[j] = y[j];
-        have = true;
+          for (int j = i; j < P; ++j) syy[k++] += c[i] * c[j];
+        n0 += 1;
       }
-      double c[P];
-#pragma unroll
-      for (int j = 0; j < P; ++j) { last[j] = y[j]; c[j] = y[j] - sh[j]; sy[j] += c[j]; }
-      int k = 0;
-#pragma unroll
-      for (int i = 0; i < P; ++i)
-#pragma unroll
-        for (int j = i; j < P; ++j) syy[k++] += c[i] * c[j];
-      n0 += 1;
     }
   }
   double* o = part + ((g * slices + sl) * MR::ROWS) * kLanes + lane;
@@ -444,18 +459,37 @@ __global__ void setup_finalize_kernel(const T* __restrict__ obs, const double* _
 }
 
 // ---- 4. centre the observations in place: y[t,j] -= means[b,j]  (:702-705) ---------------------------
-template <typename T>
-__global__ void center_rows_kernel(T* __restrict__ rec, const T* __restrict__ means, long B, long Tn, int rows, int R) {
-  const long line = (long)blockIdx.x * (blockDim.x / kLanes) + (threadIdx.x >> 5);   // (g, t, r<R)
+// One warp per (tile, block of kCenterFrames frames): all R x kCenterFrames lines are loaded before the
+// first store so that enough bytes are in flight per SM to saturate HBM.
+constexpr int kCenterFrames = 8;
+template <typename T, int R>
+__global__ void __launch_bounds__(256)
+center_rows_kernel(T* __restrict__ rec, const T* __restrict__ means, long B, long Tn, int rows) {
+  const long nblk = (Tn + kCenterFrames - 1) / kCenterFrames;
+  const long w = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
-  const long total = num_tiles_dev(B) * Tn * R;
-  if (line >= total) return;
-  const int r = (int)(line % R);
-  const long gt = line / R;
-  const long g = gt / Tn;
+  if (w >= num_tiles_dev(B) * nblk) return;
+  const long g = w / nblk;
+  const long t0 = (w - g * nblk) * kCenterFrames;
   const long b = g * kLanes + lane;
   if (b >= B) return;
-  rec[(gt * rows + r) * kLanes + lane] -= means[b * R + r];
+  T mu[R], v[kCenterFrames][R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) mu[r] = means[b * R + r];
+  T* base = rec + ((g * Tn + t0) * rows) * kLanes + lane;
+  const int nf = (int)(Tn - t0 < kCenterFrames ? Tn - t0 : kCenterFrames);
+#pragma unroll
+  for (int f = 0; f < kCenterFrames; ++f)
+    if (f < nf) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) v[f][r] = base[((long)f * rows + r) * kLanes];
+    }
+#pragma unroll
+  for (int f = 0; f < kCenterFrames; ++f)
+    if (f < nf) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) base[((long)f * rows + r) * kLanes] = v[f][r] - mu[r];
+    }
 }
 
 template <typename T, int P>
@@ -493,8 +527,8 @@ static int setup_run(T* obs, long B, long Tn, int n, double q, double s, int cen
       obs, B, Tn, msl, thr, part);
   setup_finalize_kernel<T, P, 3><<<(unsigned)((B + 63) / 64), 64, 0, st>>>(obs, part, B, Tn, msl, s, means, C, S0, Q, status);
   if (center) {
-    const long lines = tiles * Tn * P;
-    center_rows_kernel<T><<<(unsigned)((lines + 7) / 8), 8 * kLanes, 0, st>>>(obs, means, B, Tn, 2 * P, P);
+    const long warps_c = tiles * ((Tn + kCenterFrames - 1) / kCenterFrames);
+    center_rows_kernel<T, P><<<(unsigned)((warps_c + 7) / 8), 256, 0, st>>>(obs, means, B, Tn, 2 * P);
   }
   return check_launch("pca_setup kernels");
 }
