@@ -622,6 +622,35 @@ EKSB_HD void fwd_prep(const Params<T, N, P, AM>& prm, const T* y, const T* r, T*
   }
 }
 
+// fwd_prep with the outer products C_j C_j^T precomputed once per track (helper warps of the pipelined
+// kernel): per observation 1 reciprocal + 1 + N + NS multiply-adds instead of 1 + 2N + NS, and the
+// one-Newton-step reciprocal (3e-14 relative in f64).  Same record as fwd_prep up to rounding.
+template <typename T, int N, int P> EKSB_HD void make_outer(const T C[P][N], T CC[P][Dim<N>::NS]) {
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) {
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int k = i; k < N; ++k) CC[j][sym_idx<N>(i, k)] = C[j][i] * C[j][k];
+    }
+  }
+}
+template <typename T, int N, int P>
+EKSB_HD void fwd_prep_outer(const T C[P][N], const T CC[P][Dim<N>::NS], const T* y, const T* r, T* rec) {
+  constexpr int NS = Dim<N>::NS;
+  EKSB_UNROLL
+  for (int k = 0; k < NS + N; ++k) rec[k] = T(0);
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) {
+    const T w = rcp_chain(r[j]);
+    const T wy = w * y[j];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) rec[NS + i] += C[j][i] * wy;
+    EKSB_UNROLL
+    for (int k = 0; k < NS; ++k) rec[k] += w * CC[j][k];
+  }
+}
+
 template <typename T, int N, int P, int AM>
 EKSB_HD void fwd_chain(const Params<T, N, P, AM>& prm, const T* rec, bool do_predict, T* m, T* V, bool& ok) {
   constexpr int NS = Dim<N>::NS;

@@ -123,6 +123,9 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
 
   if (!is_chain) {
     const bool issuer = (h == 0 && lane == 0);
+    constexpr bool kOuter = (P * NS <= 36);                // outer products C_j C_j^T kept in registers
+    T CC[kOuter ? P : 1][NS];
+    if (kOuter) make_outer<T, N, kOuter ? P : 1>(prm.C, CC);
     if (issuer) {
       for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
       mbar_fence_init();
@@ -153,7 +156,8 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
             T cur[R2], rec[REC];
 #pragma unroll
             for (int r = 0; r < R2; ++r) cur[r] = src[(j * R2 + r) * kLanes];
-            fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
+            if constexpr (kOuter) fwd_prep_outer<T, N, P>(prm.C, CC, cur, cur + P, rec);
+            else fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
 #pragma unroll
             for (int r = 0; r < REC; ++r) dst[(j * REC + r) * kLanes] = rec[r];
           }
@@ -311,17 +315,15 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
         const int nfr = (int)(rem < F ? rem : F);
         const T* src = raw + (size_t)st * F * SG * kLanes + lane;
         T* dst = recb + (k & 1) * (F * REC * kLanes) + lane;
+        // one frame: filtered record at run offset `off` -> smoothing element j of this batch
+        auto prep = [&](int j, int off, bool terminal) {
+          T cur[SG], rec[REC];
 #pragma unroll
-        for (int jj = 0; jj < (F + H - 1) / H; ++jj) {
-          const int j = jj * H + h;
-          if (j < nfr) {
-            const int off = nfr - 1 - j;
-            T cur[SG], rec[REC];
-#pragma unroll
-            for (int r = 0; r < SG; ++r) cur[r] = src[(off * SG + r) * kLanes];
-            if (OP == 1) {
-              btd_bwd_prep<T, N>(bc, cur, cur + N, k == 0 && j == 0, rec);
-            } else if (k == 0 && j == 0) {                 // last frame: ms = mf, Vs = Vf  (:152-153)
+          for (int r = 0; r < SG; ++r) cur[r] = src[(off * SG + r) * kLanes];
+          if constexpr (OP == 1) {
+            btd_bwd_prep<T, N>(bc, cur, cur + N, terminal, rec);
+          } else {
+            if (terminal) {                                // last frame: ms = mf, Vs = Vf  (:152-153)
 #pragma unroll
               for (int r = 0; r < N * N; ++r) rec[r] = T(0);
 #pragma unroll
@@ -331,8 +333,21 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
             } else {
               bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
             }
+          }
 #pragma unroll
-            for (int r = 0; r < REC; ++r) dst[(j * REC + r) * kLanes] = rec[r];
+          for (int r = 0; r < REC; ++r) dst[(j * REC + r) * kLanes] = rec[r];
+        };
+        if (k > 0 && nfr == F) {                           // interior batch: no per-frame guards
+#pragma unroll
+          for (int jj = 0; jj < (F + H - 1) / H; ++jj) {
+            const int j = jj * H + h;
+            if ((jj + 1) * H <= F || j < F) prep(j, F - 1 - j, false);
+          }
+        } else {
+#pragma unroll
+          for (int jj = 0; jj < (F + H - 1) / H; ++jj) {
+            const int j = jj * H + h;
+            if (j < nfr) prep(j, nfr - 1 - j, k == 0 && j == 0);
           }
         }
       }

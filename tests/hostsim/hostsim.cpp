@@ -68,7 +68,13 @@ static int run_split(long Tn, const T* y, const T* ev, const T* m0, const T* S0,
   bool ok = true;
   for (long t = 0; t < Tn; ++t) {
     T rec[Rec<N>::FWD];
-    fwd_prep<T, N, P, AM>(prm, y + t * P, ev + t * P, rec);
+    if constexpr (P * NS <= 36) {            // same selection as the kernel's helper warps (kOuter)
+      T CC[P][NS];
+      make_outer<T, N, P>(prm.C, CC);
+      fwd_prep_outer<T, N, P>(prm.C, CC, y + t * P, ev + t * P, rec);
+    } else {
+      fwd_prep<T, N, P, AM>(prm, y + t * P, ev + t * P, rec);
+    }
     if (!(t == 0 && first == kPriorOnly)) {
       if constexpr (AM == 0 && N <= 3) {     // same selection as kf_forward_pipe_kernel (kScaled)
         if (t == 0) { for (int i = 0; i < NS; ++i) Nm[i] = V[i]; rr = T(1); }
