@@ -86,3 +86,38 @@ def test_shard_of_a_large_batch_is_bitwise_identical():
     sub = dev.TrackParams(prm.m0, prm.S0, prm.C[lo:hi].contiguous(), prm.A, prm.Q, a_mode=prm.a_mode)
     part, _ = _smooth(obs[lo // 32:hi // 32].contiguous(), sub, hi - lo, T)
     assert torch.equal(part, full[lo // 32:hi // 32])
+
+
+@pytest.mark.parametrize("B", [148 * 32 + 7, 148 * 64 + 1, 148 * 96 - 31, 16384])
+@pytest.mark.parametrize("dtname,tol", [("float64", 1e-9), ("float32", 2e-3)])
+def test_every_tiles_per_cta_choice_matches_the_oracle(B, dtname, tol):
+    """The launch packs ceil(tiles/148) tiles into a CTA (1..4) and places warp roles per scheduler; every
+    choice must give the oracle's numbers (checked on a few tracks spread over the batch, ragged last tile)."""
+    import torch
+    from eks_b200 import device as dev
+    from oracle import restated as o
+    dt = getattr(torch, dtname)
+    T, p, n = 61, 4, 3
+    d = torch.device("cuda", 0)
+    rng = np.random.default_rng(B)
+    pick = sorted({0, 31, 32, B // 3, B // 2, B - 33, B - 1})
+    C = np.linalg.qr(rng.normal(size=(B, p, n)))[0]
+    A = np.diag([1.0, 0.99, 0.95]); Q = 0.01 * np.eye(n) + 0.001; S0 = np.diag([1.0, 2.0, 0.5]); m0 = np.array([0.3, -0.2, 0.1])
+    y = rng.normal(size=(B, T, p)).cumsum(1) * 0.1
+    ev = np.exp(rng.normal(np.log(0.05), 1.0, size=(B, T, p)))
+    prm = dev.TrackParams.from_numpy(m0, S0, C, A, Q, dtype=dt, device=d)
+    obs = dev.pack_obs(torch.as_tensor(y, dtype=dt).to(d), torch.as_tensor(ev, dtype=dt).to(d))
+    filt, _, st = dev.kf_forward(obs, prm, B, T)
+    out = dev.rts_backward(filt, prm, B, T, inplace=True, status=st)
+    assert int(st.sum()) == 0
+    sm = dev.unpack_rows(out["smth"], 9, 0, B, T, 9)[pick].cpu().numpy().astype(np.float64)
+    ym = dev.unpack_rows(out["ym"], p, 0, B, T, p)[pick].cpu().numpy().astype(np.float64)
+    iu = np.triu_indices(n)
+    for i, b in enumerate(pick):
+        yb, evb = (y[b], ev[b]) if dtname == "float64" else (y[b].astype(np.float32).astype(np.float64), ev[b].astype(np.float32).astype(np.float64))
+        mf, Vf, S = o.filtering_pass(yb, m0, S0, C[b], np.eye(p), A, Q, evb)
+        ms, Vs, _ = o.smooth_backward(yb, mf, Vf, S, A, Q, C[b])
+        sc = max(1.0, np.abs(ms).max())
+        assert np.abs(sm[i][:, :n] - ms).max() < tol * sc
+        assert np.abs(sm[i][:, n:] - Vs[:, iu[0], iu[1]]).max() < tol * np.abs(Vs).max()
+        assert np.abs(ym[i] - ms @ C[b].T).max() < tol * sc
