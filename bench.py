@@ -73,14 +73,49 @@ def synth_preds_block(torch, C_blk, T, dtype, device, gen):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    """SM clock / power / throttle reasons sampled DURING the timed region (B200_PROFILING.md) through NVML --
+    the source nvidia-smi reads -- from a thread of this process (no start-up delay, so short timed regions are
+    still covered); falls back to an `nvidia-smi -lms` child process if pynvml is unavailable."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
-        self.rows, self.proc, self.index = [], None, index
+        self.rows, self.proc, self.index, self.stop_flag, self.thread, self.nv = [], None, index, False, None, None
 
     def start(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[self.index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else self.index
+            h = nv.nvmlDeviceGetHandleByIndex(phys)
+            self.nv = nv
+            masks = [getattr(nv, n, 0) for n in ("nvmlClocksEventReasonHwSlowdown", "nvmlClocksEventReasonHwThermalSlowdown",
+                                                  "nvmlClocksEventReasonSwThermalSlowdown", "nvmlClocksEventReasonSwPowerCap")]
+            fallb = [getattr(nv, n, 0) for n in ("nvmlClocksThrottleReasonHwSlowdown", "nvmlClocksThrottleReasonHwThermalSlowdown",
+                                                  "nvmlClocksThrottleReasonSwThermalSlowdown", "nvmlClocksThrottleReasonSwPowerCap")]
+            masks = [m or f for m, f in zip(masks, fallb)]
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+
+            def loop():
+                while not self.stop_flag:
+                    try:
+                        sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                        pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                        try:
+                            r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                        except Exception:
+                            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        self.rows.append([str(sm), str(mx), f"{pw:.2f}"] + ["Active" if (r & m) else "Not Active" for m in masks])
+                    except Exception:
+                        pass
+                    time.sleep(0.004)
+            self.thread = threading.Thread(target=loop, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nv = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "20"],
@@ -94,17 +129,52 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
-        pw = [float(r[2]) for r in self.rows if len(r) >= 7 and r[2].replace(".", "").isdigit()]
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=1.0)
+        elif self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+        else:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampling unavailable"]}
+        rows = [r for r in self.rows if len(r) >= 7]
+        sm = [float(r[0]) for r in rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in rows if r[1].replace(".", "").isdigit()]
+        reasons = sorted({self.NAMES[i] for r in rows for i in range(4) if r[3 + i].lower().startswith("active")})
+        pw = [float(r[2]) for r in rows if r[2].replace(".", "").isdigit()]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons,
+                "source": "nvml" if self.thread is not None else "nvidia-smi"}
+
+
+def bind_to_gpu_numa_node(local_index):
+    """Pin this process to the CPUs of the NUMA node its GPU hangs off (first-touch then places the pinned
+    staging buffers of the e2e path on that node; with 8 ranks on one box this is what keeps eight PCIe
+    streams from sharing one socket's memory controller).  Best effort; returns the node or None."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(vis.split(",")[local_index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else local_index
+        bus = nv.nvmlDeviceGetPciInfo(nv.nvmlDeviceGetHandleByIndex(phys)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        bus = bus.lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        return None
+    return None
 
 
 # ----------------------------------------------------------------------------------------------
@@ -216,6 +286,7 @@ def gpu_main(a):
     d = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=d)
+    numa_node = bind_to_gpu_numa_node(local) if world > 1 else None
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu:
@@ -377,7 +448,7 @@ def gpu_main(a):
         assert int(outs["status"].sum()) == 0 and bool(torch.isfinite(outs["ym"][::97]).all())
         e2e = {"value": world * Be * T * a.steps / dt_s, "unit": UNIT,
                "h2d_bytes_per_step": cnt["h2d_bytes"] // a.steps, "d2h_bytes_per_step": cnt["d2h_bytes"] // a.steps,
-               "tracks": Be, "frames": T, "api": f"eks_b200.batched.smooth_tracks (pinned host in/out, {a.e2e_block}-track blocks through the parallel-in-time scan, 3 streams)",
+               "tracks": Be, "frames": T, "numa_node": numa_node, "api": f"eks_b200.batched.smooth_tracks (pinned host in/out, {a.e2e_block}-track blocks through the parallel-in-time scan, 3 streams)",
                "ms_per_step": 1e3 * dt_s / a.steps}
         launches += cnt["launches"]
 
