@@ -64,7 +64,12 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
 // (the launch picks the actual tiles per CTA, `tpc` <= TPC, so that tiles spread evenly over the SMs)
 template <int H_, int F_, int NST_, int TPC_> struct PipeCfg {
   static constexpr int H = H_, F = F_, NST = NST_, TPC = TPC_;
-  static constexpr int THREADS = (TPC * (H + 1) + 3) / 4 * 4 * kLanes;   // upper bound incl. filler warps
+  // upper bound on warps per CTA incl. filler warps (eksb_pipe_impl.cuh roles_warps): dedicated-scheduler
+  // placement for 1-2 tiles may need 4*H warps
+  static constexpr int WARPS_A = (TPC * (H + 1) + 3) / 4 * 4;
+  static constexpr int WARPS_B = 4 * H;
+  static constexpr int WARPS_C = (WARPS_A > WARPS_B ? WARPS_A : WARPS_B);
+  static constexpr int THREADS = (WARPS_C > 32 ? 32 : WARPS_C) * kLanes;
 };
 
 // Which job each warp of a CTA does.  Warp w of a CTA issues from scheduler (SM sub-partition)

@@ -22,24 +22,48 @@ inline int pick_tpc(long tiles, int tpc_max, size_t tile_smem) {
   return tpc_max;                                 // more tiles than fit at once: several waves
 }
 
-// Place the warps of a CTA (tpc chain warps + tpc*H helper warps) on the four schedulers so that
-// their instruction loads even out: w_chain / w_helper are instructions per frame of a chain warp
-// and of ALL helpers of a tile together (measured from SASS).  Warp index = 4*k + s
-// for the k-th warp placed on scheduler s; unused slots become filler warps.  Returns warps per CTA.
+// Place the warps of a CTA (tpc chain warps + tpc*H helper warps) on the SM's four schedulers; warp index =
+// 4*k + s for the k-th warp placed on scheduler s, unused slots become filler warps that exit at once.
+// Returns warps per CTA.
+//  * tpc <= 2: every chain warp gets a scheduler to ITSELF and the helpers share the remaining ones.  The pass
+//    runs at the chain warp's pace, and a helper on the same scheduler steals its issue slots (measured, f64
+//    8192 tracks sustained: backward 24.6 ms with a shared scheduler, 22.2 ms with a dedicated one).
+//  * tpc >= 3: not enough schedulers to dedicate; greedy by instruction weight (w_chain per chain warp,
+//    w_helper for all helpers of a tile together), at most ceil(total/4) warps per scheduler.
+inline int roles_warps(int tpc, int H) {
+  if (tpc <= 2) {
+    const int per = (tpc * H + (4 - tpc) - 1) / (4 - tpc);
+    return 4 * (per < 1 ? 1 : per);
+  }
+  return 4 * ((tpc * (H + 1) + 3) / 4);
+}
 inline int make_roles(int tpc, int H, float w_chain, float w_helper, RoleMap& rm) {
+  for (int w = 0; w < kMaxWarps; ++w) { rm.tile[w] = -1; rm.h[w] = -1; }
+  int len[4] = {0, 0, 0, 0};
+  auto put = [&](int s2, int tile, int h) {
+    const int w = 4 * len[s2] + s2;
+    rm.tile[w] = (signed char)tile;
+    rm.h[w] = (signed char)h;
+    ++len[s2];
+  };
+  if (tpc <= 2) {
+    for (int t = 0; t < tpc; ++t) put(t, t, -1);
+    int s2 = tpc;
+    for (int h = 0; h < H; ++h)
+      for (int t = 0; t < tpc; ++t) {
+        put(s2, t, h);
+        if (++s2 == 4) s2 = tpc;
+      }
+    return roles_warps(tpc, H);
+  }
   const int total = tpc * (H + 1), cap = (total + 3) / 4;
   float load[4] = {0, 0, 0, 0};
-  int len[4] = {0, 0, 0, 0};
-  for (int w = 0; w < kMaxWarps; ++w) { rm.tile[w] = -1; rm.h[w] = -1; }
   auto place = [&](int tile, int h, float wgt) {
     int best = -1;
     for (int s2 = 0; s2 < 4; ++s2)
       if (len[s2] < cap && (best < 0 || load[s2] < load[best])) best = s2;
-    const int w = 4 * len[best] + best;
-    rm.tile[w] = (signed char)tile;
-    rm.h[w] = (signed char)h;
+    put(best, tile, h);
     load[best] += wgt;
-    ++len[best];
   };
   for (int t = 0; t < tpc; ++t) place(t, -1, w_chain);
   for (int h = 0; h < H; ++h)
@@ -66,7 +90,9 @@ template <typename T, int H, int ROWS_IN, int REC, int FORCE_F = 0, int FORCE_NS
   static constexpr int NST = FORCE_NST ? FORCE_NST : f8n3 ? 3 : f4n3 ? 3 : f4n2 ? 2 : 3;
   static constexpr size_t kTileSmem = TileBytes<T, ROWS_IN, REC, H, F, NST>::value;
   static constexpr int TPC0 = (int)((kCtaSmemBudget - 1024) / kTileSmem);
-  static constexpr int TPC = TPC0 > EKSB_PIPE_TPC ? EKSB_PIPE_TPC : TPC0;
+  static constexpr int TPC1 = TPC0 > EKSB_PIPE_TPC ? EKSB_PIPE_TPC : TPC0;
+  static constexpr int TPCW = kMaxWarps / (H + 1);           // warps of a CTA: tpc * (H + 1) <= 32
+  static constexpr int TPC = TPC1 > TPCW ? TPCW : TPC1;
   static constexpr bool ok = TPC >= 1 && (FORCE_F || f8n3 || f4n3 || f4n2 || f2n3);
   using type = PipeCfg<H, F, NST, (TPC >= 1 ? TPC : 1)>;
 };
@@ -88,6 +114,12 @@ template <typename T, int H, int ROWS_IN, int REC, int FORCE_F = 0, int FORCE_NS
 #endif
 #ifndef EKSB_BWD_NST
 #define EKSB_BWD_NST 0
+#endif
+#ifndef EKSB_BWD_WIDE_H
+#define EKSB_BWD_WIDE_H 2
+#endif
+#ifndef EKSB_FWD_DEEP_H
+#define EKSB_FWD_DEEP_H 2
 #endif
 #ifndef EKSB_BWD_WIDE_NST
 #define EKSB_BWD_WIDE_NST 3
@@ -119,7 +151,7 @@ template <typename T, int N, int P, int AM, int OP = 0>
 static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                            long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
   using Shallow = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, EKSB_FWD_F, EKSB_FWD_NST>;
-  using Deep = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, 8, 4>;
+  using Deep = AutoCfg<T, EKSB_FWD_DEEP_H, 2 * P, Rec<N>::FWD, 8, 4>;
   if constexpr (N <= 3 && Deep::ok) {
     const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
     static const bool shallow_only = getenv("EKSB_FWD_SHALLOW") != nullptr;
@@ -153,7 +185,7 @@ template <typename T, int N, int P, int AM, int OP, int OUT>
 static int launch_bwd_pipe_out(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
                                T* smth, T* ym, T* yv, int* status, cudaStream_t st) {
   using Narrow = AutoCfg<T, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_F, EKSB_BWD_NST>;
-  using Wide = AutoCfg<T, 3, Dim<N>::SIGMA, Rec<N>::BWD, 6, EKSB_BWD_WIDE_NST>;
+  using Wide = AutoCfg<T, EKSB_BWD_WIDE_H, Dim<N>::SIGMA, Rec<N>::BWD, 6, EKSB_BWD_WIDE_NST>;
   if constexpr (N <= 3 && Wide::ok) {
     const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
     static const bool narrow_only = getenv("EKSB_BWD_NARROW") != nullptr;
