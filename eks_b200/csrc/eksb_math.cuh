@@ -706,11 +706,38 @@ EKSB_HD void fwd_chain(const Params<T, N, P, AM>& prm, const T* rec, bool do_pre
   for (int i = 0; i < N; ++i) m[i] = mp[i] + Vu[i];
 }
 
-// Forward chain with the covariance carried as V = Nm * r (numerator matrix and the scalar 1/det of the
-// last update) so that the scaling by r folds into the next predict:  S = AA o (Nm r) + Q = fma(AA o Nm, r, Q).
-// Per frame the dependency path is  S (1) -> Id + Lam S (3) -> adjugate (2) -> det (3) -> rcp_chain (~4)
-// instead of ... -> rcp (~7) -> scale (1) -> predict (1).  Diagonal A and N <= 3 only (every shipped config);
-// Vout receives the normalised covariance (off the path).  First use: Nm = V, r = 1.
+// Adjugate (packed symmetric) and determinant of a packed symmetric N x N matrix, N <= 3.
+template <typename T, int N> EKSB_HD void sym_adjugate(const T* a, T* adj, T& det) {
+  if (N == 1) {
+    adj[0] = T(1);
+    det = a[0];
+  } else if (N == 2) {
+    adj[0] = a[2 % Dim<N>::NS]; adj[1 % Dim<N>::NS] = -a[1 % Dim<N>::NS]; adj[2 % Dim<N>::NS] = a[0];
+    det = a[0] * a[2 % Dim<N>::NS] - a[1 % Dim<N>::NS] * a[1 % Dim<N>::NS];
+  } else {
+    constexpr int M = Dim<N>::NS;          // (indices mod M so that N < 3 instantiations still compile)
+    // a = [a00 a01 a02 a11 a12 a22]
+    adj[0] = a[3 % M] * a[5 % M] - a[4 % M] * a[4 % M];
+    adj[1 % M] = a[2 % M] * a[4 % M] - a[1 % M] * a[5 % M];
+    adj[2 % M] = a[1 % M] * a[4 % M] - a[2 % M] * a[3 % M];
+    adj[3 % M] = a[0] * a[5 % M] - a[2 % M] * a[2 % M];
+    adj[4 % M] = a[1 % M] * a[2 % M] - a[0] * a[4 % M];
+    adj[5 % M] = a[0] * a[3 % M] - a[1 % M] * a[1 % M];
+    det = a[0] * adj[0] + a[1 % M] * adj[1 % M] + a[2 % M] * adj[2 % M];
+  }
+}
+
+// Forward chain with the covariance carried between frames as V = Nm * r (a symmetric numerator and a
+// scalar), so that no matrix is ever divided on the frame-to-frame path and only ONE reciprocal is taken:
+//   S  = AA o (Nm r) + Q                      = fma(AA o Nm, r, Q)
+//   Lt = det(S) (S^-1 + Lam)                  = adj(S) + det(S) Lam            (Lam = C^T R^-1 C from the helpers)
+//   V  = (S^-1 + Lam)^-1 = det(S) adj(Lt) / det(Lt)    ->   Nm = adj(Lt),  r = det(S) / det(Lt)
+// ~82 double-precision instructions per frame on the chain warp (the two nested symmetric inverses of
+// fwd_chain need two dependent reciprocals; the Id + Lam S form needs ~114 instructions).  The chain warp has a
+// scheduler to itself and each DP instruction occupies its FP64 pipe for 2 cycles, so instruction count, not
+// dependency depth, sets the frame time.  Diagonal A and N <= 3 only (every shipped config); Vout receives the
+// normalised covariance (off the path).  First use: Nm = V, r = 1.  Magnitudes: det(Lt) ~ (det S * Lam)^N,
+// comfortably inside both float ranges for ensemble variances in [1e-4, 1e3].
 template <typename T, int N, int P>
 EKSB_HD void fwd_chain_scaled(const Params<T, N, P, 0>& prm, const T* rec, bool do_predict, T* m, T* Nm, T& r, T* Vout,
                               bool& ok) {
@@ -730,31 +757,13 @@ EKSB_HD void fwd_chain_scaled(const Params<T, N, P, 0>& prm, const T* rec, bool 
   sym_matvec<T, N>(rec, mp, u);
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
-  T M[N][N];
+  T adjS[NS], detS, Lt[NS], detL;
+  sym_adjugate<T, N>(S, adjS, detS);
   EKSB_UNROLL
-  for (int i = 0; i < N; ++i) {
-    EKSB_UNROLL
-    for (int j = 0; j < N; ++j) {
-      T a = (i == j) ? T(1) : T(0);
-      EKSB_UNROLL
-      for (int k = 0; k < N; ++k) a += rec[sym_idx<N>(i, k)] * S[sym_idx<N>(k, j)];
-      M[i][j] = a;
-    }
-  }
-  T adj[N][N], det;
-  gen_adjugate<T, N>(M, adj, det);
-  ok = ok && (det > T(0)) && (S[0] > T(0));
-  EKSB_UNROLL
-  for (int i = 0; i < N; ++i) {
-    EKSB_UNROLL
-    for (int j = i; j < N; ++j) {
-      T a = T(0);
-      EKSB_UNROLL
-      for (int k = 0; k < N; ++k) a += S[sym_idx<N>(i, k)] * adj[k][j];
-      Nm[sym_idx<N>(i, j)] = a;
-    }
-  }
-  r = rcp_chain(det);
+  for (int k = 0; k < NS; ++k) Lt[k] = detS * rec[k] + adjS[k];
+  sym_adjugate<T, N>(Lt, Nm, detL);
+  ok = ok && (detS > T(0)) && (detL > T(0)) && (S[0] > T(0));
+  r = detS * rcp_chain(detL);
   sym_matvec<T, N>(Nm, u, Nu);
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) m[i] = mp[i] + Nu[i] * r;
