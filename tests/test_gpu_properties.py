@@ -121,3 +121,18 @@ def test_every_tiles_per_cta_choice_matches_the_oracle(B, dtname, tol):
         assert np.abs(sm[i][:, :n] - ms).max() < tol * sc
         assert np.abs(sm[i][:, n:] - Vs[:, iu[0], iu[1]]).max() < tol * np.abs(Vs).max()
         assert np.abs(ym[i] - ms @ C[b].T).max() < tol * sc
+
+
+def test_nccl_grid_search_over_two_ranks():
+    """The path's one collective on real GPUs: sharded NLL grid sums all-reduced over NCCL equal the
+    single-rank sums (tools/nccl_selection_check.py).  Needs 2 GPUs; skipped on a 1-GPU box (the host-side
+    logic is covered by the gloo world-2 test on CPU)."""
+    import os, subprocess, sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29547", os.path.join(root, "tools", "nccl_selection_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and " OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
