@@ -15,8 +15,9 @@
 //     shared-memory ring; the chain warp runs only the true dependency chain (fwd_chain /
 //     bwd_chain) and stores the results with full-line writes.
 // Hand-off is one named barrier (bar.sync id, (H+1)*32) per batch of F frames, per tile, so
-// tiles sharing a CTA do not couple.  TPC tiles per CTA spreads chain warps over the SM's 4
-// warp schedulers.
+// tiles sharing a CTA do not couple.  The launch (eksb_pipe_impl.cuh) packs ceil(tiles/148) tiles
+// into a CTA so every busy SM carries the same number of tiles, and hands the kernel a RoleMap that
+// puts each chain warp on a scheduler (SM sub-partition) of its own where the CTA is small enough.
 #pragma once
 #include <stdint.h>
 #include "eksb_common.cuh"

@@ -17,10 +17,6 @@ namespace eksb {
 
 constexpr int kScanWarps = 4;   // warps (= chunks) per CTA
 
-template <typename T> __device__ __forceinline__ void store_rows(T* dst, const T* v, int n) {
-  for (int i = 0; i < n; ++i) dst[i * kLanes] = v[i];
-}
-
 // ---- 1a. forward chunk summaries, chunks [1, nc), plus the sequential run of chunk 0 -----------------
 // Work items [0, tiles): chunk 0 of each tile, run as the ordinary filter from the prior (it needs no
 // summary, only its end state, and would otherwise be a serial 1-warp-per-tile launch of its own).
