@@ -84,19 +84,20 @@ EKSB_HD double rcp_chain(double x) {
 // SPD inverse of a packed symmetric matrix.  Returns det(a) (used by the NLL).
 // N<=3: closed-form adjugate (one reciprocal, short dependency chain);
 // N>3 : unrolled LDL^T, inverse = L^-T D^-1 L^-1.
-// ok is cleared when a pivot / determinant is not strictly positive (the
-// reference would raise numpy.linalg.LinAlgError or silently produce garbage).
+// ok is cleared when a pivot / determinant is <= 0 (the reference would raise
+// numpy.linalg.LinAlgError or silently produce garbage).  The tests are written !(x <= 0) so that NaN
+// does NOT clear it: the reference propagates NaN silently and so does this library.
 // ---------------------------------------------------------------------------
 template <typename T, int N> struct SymInv;
 
 template <typename T> struct SymInv<T, 1> {
-  static EKSB_HD T run(const T* a, T* inv, bool& ok) { ok = ok && (a[0] > T(0)); inv[0] = rcp(a[0]); return a[0]; }
+  static EKSB_HD T run(const T* a, T* inv, bool& ok) { ok = ok && !(a[0] <= T(0)); inv[0] = rcp(a[0]); return a[0]; }
 };
 
 template <typename T> struct SymInv<T, 2> {
   static EKSB_HD T run(const T* a, T* inv, bool& ok) {
     T det = a[0] * a[2] - a[1] * a[1];
-    ok = ok && (det > T(0)) && (a[0] > T(0));
+    ok = ok && !(det <= T(0)) && !(a[0] <= T(0));
     T r = rcp(det);
     inv[0] = a[2] * r; inv[1] = -a[1] * r; inv[2] = a[0] * r;
     return det;
@@ -113,7 +114,7 @@ template <typename T> struct SymInv<T, 3> {
     T c12 = a[1] * a[2] - a[0] * a[4];
     T c22 = a[0] * a[3] - a[1] * a[1];
     T det = a[0] * c00 + a[1] * c01 + a[2] * c02;
-    ok = ok && (det > T(0)) && (a[0] > T(0)) && (c22 > T(0));
+    ok = ok && !(det <= T(0)) && !(a[0] <= T(0)) && !(c22 <= T(0));
     T r = rcp(det);
     inv[0] = c00 * r; inv[1] = c01 * r; inv[2] = c02 * r;
     inv[3] = c11 * r; inv[4] = c12 * r; inv[5] = c22 * r;
@@ -131,7 +132,7 @@ template <typename T, int N> struct SymInv {
       T s = a[sym_idx<N>(j, j)];
       EKSB_UNROLL
       for (int k = 0; k < j; ++k) s -= L[j][k] * L[j][k] * d[k];
-      d[j] = s; ok = ok && (s > T(0)); rd[j] = rcp(s); det *= s;
+      d[j] = s; ok = ok && !(s <= T(0)); rd[j] = rcp(s); det *= s;
       EKSB_UNROLL
       for (int i = j + 1; i < N; ++i) {
         T v = a[sym_idx<N>(j, i)];
@@ -683,7 +684,7 @@ EKSB_HD void fwd_chain(const Params<T, N, P, AM>& prm, const T* rec, bool do_pre
     }
     T adj[N][N], det;
     gen_adjugate<T, N>(M, adj, det);
-    ok = ok && (det > T(0)) && (S[0] > T(0));
+    ok = ok && !(det <= T(0)) && !(S[0] <= T(0));
     const T r = rcp(det);
     EKSB_UNROLL
     for (int i = 0; i < N; ++i) {
@@ -762,7 +763,7 @@ EKSB_HD void fwd_chain_scaled(const Params<T, N, P, 0>& prm, const T* rec, bool 
   EKSB_UNROLL
   for (int k = 0; k < NS; ++k) Lt[k] = detS * rec[k] + adjS[k];
   sym_adjugate<T, N>(Lt, Nm, detL);
-  ok = ok && (detS > T(0)) && (detL > T(0)) && (S[0] > T(0));
+  ok = ok && !(detS <= T(0)) && !(detL <= T(0)) && !(S[0] <= T(0));
   r = detS * rcp_chain(detL);
   sym_matvec<T, N>(Nm, u, Nu);
   EKSB_UNROLL
@@ -1025,7 +1026,7 @@ EKSB_HD void fwd_summary_step(const Params<T, N, P, AM>& prm, const T* rec, T (*
       }
     }
     gen_adjugate<T, N>(M, adj, det);
-    ok = ok && (det > T(0)) && (S[0] > T(0));
+    ok = ok && !(det <= T(0)) && !(S[0] <= T(0));
     const T r = rcp(det);
     EKSB_UNROLL
     for (int i = 0; i < N; ++i) {

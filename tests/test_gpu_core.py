@@ -299,3 +299,34 @@ def test_parallel_in_time_scan_equals_sequential(dtname, tol, B, T, chunk):
         mf, Vf, S = o.filtering_pass(c["y"][b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], c["ev"][b])
         ms, Vs, _ = o.smooth_backward(c["y"][b], mf, Vf, S, c["A"], c["Q"], c["C"][b])
         assert rel(ms_scan[b][:, :n], ms) < 1e-8
+
+
+@pytest.mark.parametrize("pipe", ["1", "0"])
+def test_nan_propagates_like_the_reference_and_stays_in_its_track(pipe, monkeypatch):
+    """A NaN observation poisons the means of ITS track from that frame on and leaves the covariances alone
+    (y only enters the innovation, eks/ensemble_kalman.py:102-105); a NaN ensemble variance poisons both.
+    Neither raises in the reference (numpy.linalg.solve returns NaN), so neither sets `status`; other tracks
+    of the tile are untouched.  Same NaN pattern as the oracle, frame by frame."""
+    import torch
+    from eks_b200 import device as dev
+    monkeypatch.setenv("EKSB_PIPE", pipe)
+    B, T, p, n = 40, 90, 4, 3
+    c = _random_batch(B, T, p, n, torch.float64, seed=77)
+    y, ev = c["y"].copy(), c["ev"].copy()
+    y[3, 20, 1] = np.nan
+    ev[35, 50, 2] = np.nan
+    d = torch.device("cuda", 0)
+    obs = dev.pack_obs(torch.as_tensor(y).to(d), torch.as_tensor(ev).to(d))
+    filt, _, st = dev.kf_forward(obs, c["prm"], B, T)
+    out = dev.rts_backward(filt, c["prm"], B, T, inplace=False, status=st)
+    assert int(st.sum()) == 0
+    mfV = dev.unpack_rows(filt, 9, 0, B, T, 9).cpu().numpy()
+    sm = dev.unpack_rows(out["smth"], 9, 0, B, T, 9).cpu().numpy()
+    iu = np.triu_indices(n)
+    for b in (3, 35, 4, 34):
+        mf, Vf, S = o.filtering_pass(y[b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], ev[b])
+        ms, Vs, _ = o.smooth_backward(y[b], mf, Vf, S, c["A"], c["Q"], c["C"][b])
+        for got, want in ((mfV[b][:, :n], mf), (mfV[b][:, n:], Vf[:, iu[0], iu[1]]), (sm[b][:, :n], ms), (sm[b][:, n:], Vs[:, iu[0], iu[1]])):
+            assert np.array_equal(np.isnan(got), np.isnan(want))
+            np.testing.assert_allclose(got[~np.isnan(want)], want[~np.isnan(want)], rtol=1e-9, atol=1e-12)
+    assert np.isnan(mfV[3][20:, :n]).all() and not np.isnan(mfV[3][:, n:]).any() and not np.isnan(mfV[4]).any()
