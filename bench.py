@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU-baseline sample time")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-setup", action="store_true", help="skip the K8 parameter-setup timing")
     ap.add_argument("--no-sustained", action="store_true", help="skip the sustained device-copy context measurement")
     return ap.parse_args()
 
@@ -372,11 +373,34 @@ def gpu_main(a):
             "step_achieved": tf * (3 * P_OBS + 3 * SIGMA) * es / ((fwd_ms + bwd_ms) * 1e-3) / 1e9,
             "step_frac": tf * (3 * P_OBS + 3 * SIGMA) * es / ((fwd_ms + bwd_ms) * 1e-3) / 1e9 / peak,
             "kernels": kern}
+    launches = 2 * a.steps
     k1 = None
     if k1_ms > 0:
         k1b = (M_ENS * P_OBS + 2 * P_OBS) * es
         k1 = {"kernel": "ensemble_tiled", "keypoint_frames_per_s": k1_tf / (k1_ms * 1e-3),
               "achieved_gbs": k1_tf * k1b / (k1_ms * 1e-3) / 1e9, "frac": k1_tf * k1b / (k1_ms * 1e-3) / 1e9 / peak}
+
+    # ---- K8 (parameter setup on the device) on the same resident batch, after the timed region: it centres the
+    # obs records in place, which nothing below needs.  Reported beside the ensemble kernel; not part of `value`.
+    setup = None
+    if not a.no_setup:
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dev.pca_setup(obs, B, T, P_OBS, 25.0, 0.01, center=True)      # warm-up: workspace allocation (6.5 GB), first launch
+        torch.cuda.synchronize()
+        s0.record()
+        _, _, st_setup = dev.pca_setup(obs, B, T, P_OBS, 25.0, 0.01, center=True)
+        s1.record(); torch.cuda.synchronize()
+        sms = s0.elapsed_time(s1)
+        sb = 4 * P_OBS * es                                        # read y,ev once + read/write y for centring
+        setup = {"kernel": "pca_setup (percentile select + masked moments + PCA + centring)", "ms": sms,
+                 "keypoint_frames_per_s": tf / (sms * 1e-3), "achieved_gbs": tf * sb / (sms * 1e-3) / 1e9,
+                 "frac": tf * sb / (sms * 1e-3) / 1e9 / peak, "failed_tracks": int(st_setup.sum())}
+        launches += 48
+    session = None
+    if k1 and setup:
+        per_tf = 1.0 / k1["keypoint_frames_per_s"] + 1.0 / setup["keypoint_frames_per_s"] + (fwd_ms + bwd_ms) * 1e-3 / tf
+        session = {"keypoint_frames_per_s": 1.0 / per_tf, "stages": "ensemble_tiled + pca_setup + kf_forward + rts_backward",
+                   "note": "raw [models x frames x keypoints] predictions in HBM -> smoothed records, sum of the measured stage times"}
 
     # ---- context for the roofline: what a plain device copy SUSTAINS on this board right now (the peak in
     # MEASURED_PEAKS.json is a best-of-10 burst; back-to-back launches of HBM-bound kernels sit at the
@@ -410,7 +434,6 @@ def gpu_main(a):
 
     # ---- e2e: public host API, H2D + D2H inside the timed region
     e2e = None
-    launches = 2 * a.steps
     if not a.no_e2e:
         filt = ym = None
         del obs
@@ -462,7 +485,7 @@ def gpu_main(a):
                        "tracks_per_gpu": B, "frames": T, "parallelism": f"track-sharded x{world}, no data-path collective",
                        "l2": "inputs (obs records) exceed L2 by >100x; no flush needed",
                        "smoothing": "in place (smth overwrites filt), ym = C ms written"},
-            "roofline": roof, "ensemble_kernel": k1, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+            "roofline": roof, "ensemble_kernel": k1, "setup_kernel": setup, "session_pipeline": session, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
             "clocks": clk,
         }
         print(json.dumps(line), flush=True)
