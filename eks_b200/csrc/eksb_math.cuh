@@ -739,37 +739,49 @@ template <typename T, int N> EKSB_HD void sym_adjugate(const T* a, T* adj, T& de
 // dependency depth, sets the frame time.  Diagonal A and N <= 3 only (every shipped config); Vout receives the
 // normalised covariance (off the path).  First use: Nm = V, r = 1.  Magnitudes: det(Lt) ~ (det S * Lam)^N,
 // comfortably inside both float ranges for ensemble variances in [1e-4, 1e3].
+// The covariance half: (Nm, r) of frame t-1 and Lam = C^T R^-1 C of frame t  ->  (Nm, r) of frame t.
+// Independent of the mean, so the three-role forward kernel runs it on a warp of its own.
 template <typename T, int N, int P>
-EKSB_HD void fwd_chain_scaled(const Params<T, N, P, 0>& prm, const T* rec, bool do_predict, T* m, T* Nm, T& r, T* Vout,
-                              bool& ok) {
+EKSB_HD void fwd_cov_scaled(const Params<T, N, P, 0>& prm, const T* lam, bool do_predict, T* Nm, T& r, bool& ok) {
   constexpr int NS = Dim<N>::NS;
-  T mp[N], S[NS], u[N], Nu[N];
+  T S[NS];
   if (do_predict) {
-    EKSB_UNROLL
-    for (int i = 0; i < N; ++i) mp[i] = prm.A[i] * m[i];
     EKSB_UNROLL
     for (int k = 0; k < NS; ++k) S[k] = (prm.AA[k] * Nm[k]) * r + prm.Q[k];
   } else {
     EKSB_UNROLL
-    for (int i = 0; i < N; ++i) mp[i] = m[i];
-    EKSB_UNROLL
     for (int k = 0; k < NS; ++k) S[k] = Nm[k] * r;
   }
-  sym_matvec<T, N>(rec, mp, u);
-  EKSB_UNROLL
-  for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
   T adjS[NS], detS, Lt[NS], detL;
   sym_adjugate<T, N>(S, adjS, detS);
   EKSB_UNROLL
-  for (int k = 0; k < NS; ++k) Lt[k] = detS * rec[k] + adjS[k];
+  for (int k = 0; k < NS; ++k) Lt[k] = detS * lam[k] + adjS[k];
   sym_adjugate<T, N>(Lt, Nm, detL);
   ok = ok && !(detS <= T(0)) && !(detL <= T(0)) && !(S[0] <= T(0));
   r = detS * rcp_chain(detL);
+}
+// The mean half: m of frame t-1, the record of frame t and (Nm, r) of frame t  ->  m and the normalised V of frame t.
+template <typename T, int N, int P>
+EKSB_HD void fwd_mean_scaled(const Params<T, N, P, 0>& prm, const T* rec, bool do_predict, const T* Nm, T r, T* m,
+                             T* Vout) {
+  constexpr int NS = Dim<N>::NS;
+  T mp[N], u[N], Nu[N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) mp[i] = do_predict ? prm.A[i] * m[i] : m[i];
+  sym_matvec<T, N>(rec, mp, u);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
   sym_matvec<T, N>(Nm, u, Nu);
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) m[i] = mp[i] + Nu[i] * r;
   EKSB_UNROLL
   for (int k = 0; k < NS; ++k) Vout[k] = Nm[k] * r;
+}
+template <typename T, int N, int P>
+EKSB_HD void fwd_chain_scaled(const Params<T, N, P, 0>& prm, const T* rec, bool do_predict, T* m, T* Nm, T& r, T* Vout,
+                              bool& ok) {
+  fwd_cov_scaled<T, N, P>(prm, rec, do_predict, Nm, r, ok);
+  fwd_mean_scaled<T, N, P>(prm, rec, do_predict, Nm, r, m, Vout);
 }
 
 template <typename T, int N, int P, int AM>

@@ -254,6 +254,205 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
 }
 
 // ------------------------------------------------------------------------------------------
+// forward, three roles per tile (Kalman filter with diagonal A, N <= 3): the chain is split in two.
+//   helpers   : obs frames -> info records (Lam, iv)                      batch k     in period k
+//   cov warp  : (Nm, r) recursion, needs only Lam; writes (Nm, r) records  batch k - 1 in period k
+//   mean warp : m recursion from (Lam, iv) and (Nm, r); stores (m, V)      batch k - 2 in period k
+// One named barrier per period among the H + 2 warps of the tile.  The info ring has 3 slots (written at k,
+// read at k-1 and k-2), the (Nm, r) ring 2.  The covariance recursion is the pass's critical path; with the
+// mean update, the normalisation V = Nm r and all global stores on another warp (and scheduler) it carries
+// ~70 instead of ~110 instructions per frame.  Used when every chain warp can have a scheduler of its own
+// (<= 2 tiles per CTA); results are identical to kf_forward_pipe_kernel (same arithmetic, same order).
+// ------------------------------------------------------------------------------------------
+constexpr int kRoleCov = -1, kRoleMean = -2;
+
+template <typename T, int ROWS_IN, int REC, int VR, typename Cfg> struct Pipe3Smem {
+  static constexpr size_t kRaw = (size_t)Cfg::NST * Cfg::F * ROWS_IN * kLanes * sizeof(T);
+  static constexpr size_t kRec = (size_t)3 * Cfg::F * REC * kLanes * sizeof(T);
+  static constexpr size_t kV = (size_t)2 * Cfg::F * VR * kLanes * sizeof(T);
+  static constexpr size_t kBar = 128;
+  static constexpr size_t kTile = kRaw + kRec + kV + kBar;
+};
+
+template <typename T, int N, int P, typename Cfg>
+__global__ void __launch_bounds__(Cfg::THREADS)
+kf_forward_pipe3_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
+                        const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
+                        long B, long Tn, int first, T* __restrict__ filt, int* __restrict__ status, int tpc,
+                        const __grid_constant__ RoleMap roles) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, REC = Rec<N>::FWD, VR = NS + 1;
+  constexpr int H = Cfg::H, F = Cfg::F, NST = Cfg::NST;
+  using SM = Pipe3Smem<T, R2, REC, VR, Cfg>;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile_in_cta = roles.tile[warp];
+  if (tile_in_cta < 0) return;
+  const int role = roles.h[warp];
+  const long g = (long)blockIdx.x * tpc + tile_in_cta;
+  if (g >= num_tiles_dev(B)) return;
+  unsigned char* tile_smem = smem_raw + (size_t)tile_in_cta * SM::kTile;
+  T* raw = reinterpret_cast<T*>(tile_smem);
+  T* recb = reinterpret_cast<T*>(tile_smem + SM::kRaw);
+  T* vb = reinterpret_cast<T*>(tile_smem + SM::kRaw + SM::kRec);
+  uint64_t* full = reinterpret_cast<uint64_t*>(tile_smem + SM::kRaw + SM::kRec + SM::kV);
+  const int bar_id = tile_in_cta + 1, bar_cnt = (H + 2) * kLanes;
+  const long b = g * kLanes + lane;
+  const long bp = b < B ? b : B - 1;
+  Params<T, N, P, 0> prm;
+  load_track_params<T, N, P, 0>(prm, C, A, Q, shared_mask, bp);
+  const long nb = (Tn + F - 1) / F;
+  constexpr uint32_t kFrameBytes = R2 * kLanes * sizeof(T);
+
+  if (role >= 0) {                                         // ---------------- helper
+    const int h = role;
+    const T* gsrc = obs + (g * Tn * R2) * kLanes;
+    const bool issuer = (h == 0 && lane == 0);
+    constexpr bool kOuter = (P * NS <= 36);
+    T CC[kOuter ? P : 1][NS];
+    if constexpr (kOuter) make_outer<T, N, P>(prm.C, CC);
+    if (issuer) {
+      for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
+      mbar_fence_init();
+    }
+    tile_barrier(bar_id, bar_cnt);                         // barriers initialised
+    if (issuer) {
+      for (int s = 0; s < NST; ++s)
+        if (s < nb) {
+          const long t0 = (long)s * F;
+          const uint32_t bytes = (uint32_t)((Tn - t0 < F ? Tn - t0 : F)) * kFrameBytes;
+          mbar_expect_tx(&full[s], bytes);
+          bulk_g2s(raw + (size_t)s * F * R2 * kLanes, gsrc + t0 * R2 * kLanes, bytes, &full[s]);
+        }
+    }
+    for (long k = 0; k < nb + 2; ++k) {
+      const int st = (int)(k % NST);
+      if (k < nb) {
+        mbar_wait(&full[st], (uint32_t)((k / NST) & 1));
+        const T* src = raw + (size_t)st * F * R2 * kLanes + lane;
+        T* dst = recb + (k % 3) * (F * REC * kLanes) + lane;
+        const long rem = Tn - k * F;
+        const int nfr = (int)(rem < F ? rem : F);
+#pragma unroll
+        for (int jj = 0; jj < (F + H - 1) / H; ++jj) {
+          const int j = jj * H + h;
+          if (j < nfr) {
+            T cur[R2], rec[REC];
+#pragma unroll
+            for (int r = 0; r < R2; ++r) cur[r] = src[(j * R2 + r) * kLanes];
+            if constexpr (kOuter) fwd_prep_outer<T, N, P>(prm.C, CC, cur, cur + P, rec);
+            else fwd_prep<T, N, P, 0>(prm, cur, cur + P, rec);
+#pragma unroll
+            for (int r = 0; r < REC; ++r) dst[(j * REC + r) * kLanes] = rec[r];
+          }
+        }
+      }
+      tile_barrier(bar_id, bar_cnt);                       // end of period k
+      if (issuer && k + NST < nb) {
+        const long t0 = (k + NST) * F;
+        const uint32_t bytes = (uint32_t)((Tn - t0 < F ? Tn - t0 : F)) * kFrameBytes;
+        mbar_expect_tx(&full[st], bytes);
+        bulk_g2s(raw + (size_t)st * F * R2 * kLanes, gsrc + t0 * R2 * kLanes, bytes, &full[st]);
+      }
+    }
+    return;
+  }
+
+  // prior: both chain warps start from (m0, S0); kPriorOnly starts from (m0, S0^-1) and frame 0 is emitted as is
+  T m[N], Nm[NS], rr = T(1);
+  bool ok = true;
+  {
+    const T* pm = m0 + ((shared_mask & EKSB_SHARED_M0) ? 0 : bp * N);
+    const T* ps = S0 + ((shared_mask & EKSB_SHARED_S0) ? 0 : bp * (N * N));
+#pragma unroll
+    for (int i = 0; i < N; ++i) m[i] = pm[i];
+    load_sym<T, N>(Nm, ps);
+    if (first == kPriorOnly) {
+      T Vi[NS];
+      sym_inv<T, N>(Nm, Vi, ok);
+#pragma unroll
+      for (int i = 0; i < NS; ++i) Nm[i] = Vi[i];
+    }
+  }
+  tile_barrier(bar_id, bar_cnt);                           // (barrier init)
+
+  if (role == kRoleCov) {                                  // ---------------- covariance chain
+    for (long k = 0; k < nb + 2; ++k) {
+      if (k >= 1 && k <= nb) {
+        const long kb = k - 1;
+        const T* src = recb + (kb % 3) * (F * REC * kLanes) + lane;
+        T* dst = vb + (kb & 1) * (F * VR * kLanes) + lane;
+        const long rem = Tn - kb * F;
+        const int nfr = (int)(rem < F ? rem : F);
+        auto frame = [&](int j, bool is_first) {
+          if (!(is_first && first == kPriorOnly)) {
+            T lam[NS];
+#pragma unroll
+            for (int r = 0; r < NS; ++r) lam[r] = src[(j * REC + r) * kLanes];
+            fwd_cov_scaled<T, N, P>(prm, lam, !(is_first && first == kPriorUpdate), Nm, rr, ok);
+          }
+#pragma unroll
+          for (int r = 0; r < NS; ++r) dst[(j * VR + r) * kLanes] = Nm[r];
+          dst[(j * VR + NS) * kLanes] = rr;
+        };
+        if (kb > 0 && nfr == F) {
+#pragma unroll
+          for (int j = 0; j < F; ++j) frame(j, false);
+        } else {
+#pragma unroll
+          for (int j = 0; j < F; ++j)
+            if (j < nfr) frame(j, kb == 0 && j == 0);
+        }
+      }
+      tile_barrier(bar_id, bar_cnt);
+    }
+    if (b < B && status && !ok) status[b] = 1;
+    return;
+  }
+
+  // ---------------- mean chain + stores
+  T* f = filt + (g * Tn * SG) * kLanes + lane;
+  for (long k = 0; k < nb + 2; ++k) {
+    if (k >= 2) {
+      const long kb = k - 2;
+      const T* src = recb + (kb % 3) * (F * REC * kLanes) + lane;
+      const T* vsrc = vb + (kb & 1) * (F * VR * kLanes) + lane;
+      const long rem = Tn - kb * F;
+      const int nfr = (int)(rem < F ? rem : F);
+      auto frame = [&](int j, bool is_first) {
+        T nm[NS], V[NS];
+#pragma unroll
+        for (int r = 0; r < NS; ++r) nm[r] = vsrc[(j * VR + r) * kLanes];
+        const T r1 = vsrc[(j * VR + NS) * kLanes];
+        if (!(is_first && first == kPriorOnly)) {
+          T rec[REC];
+#pragma unroll
+          for (int r = 0; r < REC; ++r) rec[r] = src[(j * REC + r) * kLanes];
+          fwd_mean_scaled<T, N, P>(prm, rec, !(is_first && first == kPriorUpdate), nm, r1, m, V);
+        } else {
+#pragma unroll
+          for (int r = 0; r < NS; ++r) V[r] = nm[r] * r1;
+        }
+        T* o = f + j * (SG * kLanes);
+#pragma unroll
+        for (int i = 0; i < N; ++i) o[i * kLanes] = m[i];
+#pragma unroll
+        for (int i = 0; i < NS; ++i) o[(N + i) * kLanes] = V[i];
+      };
+      if (kb > 0 && nfr == F) {
+#pragma unroll
+        for (int j = 0; j < F; ++j) frame(j, false);
+      } else {
+#pragma unroll
+        for (int j = 0; j < F; ++j)
+          if (j < nfr) frame(j, kb == 0 && j == 0);
+      }
+      f += F * SG * kLanes;
+    }
+    tile_barrier(bar_id, bar_cnt);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // backward:  filt records -> smth records (+ ym, yv); walks u = T-1-t upward.
 // Batch k holds frames t_hi = T-1-kF down to t_lo = max(0, T-(k+1)F): one contiguous run in
 // HBM; local frame j (u = kF+j) sits at run offset nfr-1-j.

@@ -143,6 +143,65 @@ static int launch_fwd_cfg(const T* obs, const T* m0, const T* S0, const T* C, co
   return check_launch("kf_forward_pipe_kernel");
 }
 
+// Three-role forward (kf_forward_pipe3_kernel): covariance warp of tile t alone on scheduler t, the mean
+// warps and helpers round-robin on the other schedulers.  tpc <= 2 only.
+inline int make_roles3(int tpc, int H, RoleMap& rm) {
+  for (int w = 0; w < kMaxWarps; ++w) { rm.tile[w] = -1; rm.h[w] = 0; }
+  int len[4] = {0, 0, 0, 0};
+  auto put = [&](int s2, int tile, int h) {
+    const int w = 4 * len[s2] + s2;
+    rm.tile[w] = (signed char)tile;
+    rm.h[w] = (signed char)h;
+    ++len[s2];
+  };
+  for (int t = 0; t < tpc; ++t) put(t, t, kRoleCov);
+  int s2 = tpc;
+  auto next = [&]() { if (++s2 == 4) s2 = tpc; };
+  for (int t = 0; t < tpc; ++t) { put(s2, t, kRoleMean); next(); }
+  for (int h = 0; h < H; ++h)
+    for (int t = 0; t < tpc; ++t) { put(s2, t, h); next(); }
+  int mx = 1;
+  for (int i = 0; i < 4; ++i) mx = len[i] > mx ? len[i] : mx;
+  return 4 * mx;
+}
+
+template <int H_, int F_, int NST_> struct Pipe3Cfg {
+  static constexpr int H = H_, F = F_, NST = NST_;
+  static constexpr int THREADS = 4 * ((2 * (H + 1) + 1) / 2) * 32;   // two tiles: (H + 1) warps on each of 2 schedulers
+};
+template <typename T, int N, int P, int H> struct Auto3 {
+  template <int F, int NST> static constexpr size_t bytes() {
+    return Pipe3Smem<T, 2 * P, Rec<N>::FWD, Dim<N>::NS + 1, Pipe3Cfg<H, F, NST>>::kTile;
+  }
+  static constexpr size_t kTwo = (kCtaSmemBudget - 1024) / 2;
+  static constexpr bool a = bytes<8, 4>() <= kTwo, b = bytes<6, 4>() <= kTwo, c = bytes<6, 3>() <= kTwo,
+                        d = bytes<4, 3>() <= kTwo;
+  static constexpr int F = a ? 8 : (b || c) ? 6 : 4;
+  static constexpr int NST = (a || b) ? 4 : 3;
+  static constexpr bool ok = a || b || c || d;
+  using type = Pipe3Cfg<H, F, NST>;
+  static constexpr size_t kTileSmem = bytes<F, NST>();
+};
+
+#ifndef EKSB_FWD3_H
+#define EKSB_FWD3_H 2
+#endif
+
+template <typename T, int N, int P>
+static int launch_fwd_pipe3(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
+                            long B, long Tn, int first, T* filt, int* status, int tpc, cudaStream_t st) {
+  using Auto = Auto3<T, N, P, EKSB_FWD3_H>;
+  using Cfg = typename Auto::type;
+  auto kern = kf_forward_pipe3_kernel<T, N, P, Cfg>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(Auto::kTileSmem * 2));
+  const unsigned grid = (unsigned)((num_tiles(B) + tpc - 1) / tpc);
+  RoleMap rm;
+  const int warps = make_roles3(tpc, Cfg::H, rm);
+  kern<<<grid, warps * kLanes, Auto::kTileSmem * tpc, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt,
+                                                            status, tpc, rm);
+  return check_launch("kf_forward_pipe3_kernel");
+}
+
 // Two ring shapes, like the backward pass.  With few tiles per SM the bytes in flight per SM (stages x
 // frames x record) bound the read bandwidth (Little's law: 256 tiles x 24 KB = 6 MB in flight sustained
 // ~5.7 TB/s algorithmic in f64); the "deep" ring (8-frame batches, 4 stages: 4x the bytes in flight) lifts
@@ -152,6 +211,16 @@ static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, c
                            long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
   using Shallow = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, EKSB_FWD_F, EKSB_FWD_NST>;
   using Deep = AutoCfg<T, EKSB_FWD_DEEP_H, 2 * P, Rec<N>::FWD, 8, 4>;
+  if constexpr (OP == 0 && AM == 0 && N <= 3 && Auto3<T, N, P, EKSB_FWD3_H>::ok) {
+    const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
+    // Measured (f64, 100 000 frames, sustained): one tile per SM 16.2 -> 13.5 ms (the pass runs at the chain's
+    // pace); two tiles per SM 18.3 -> 20.8 ms (the FP64 pipes of the two helper schedulers saturate once they
+    // also carry the mean warps, and the two-role kernel is already HBM-bound there).  Hence: one tile per SM only.
+    static const int max_per_sm = getenv("EKSB_FWD3_MAX") ? atoi(getenv("EKSB_FWD3_MAX")) : 1;
+    if (per_sm <= max_per_sm && per_sm <= 2)
+      return launch_fwd_pipe3<T, N, P>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status,
+                                       (int)(per_sm < 1 ? 1 : per_sm), st);
+  }
   if constexpr (N <= 3 && Deep::ok) {
     const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
     static const bool shallow_only = getenv("EKSB_FWD_SHALLOW") != nullptr;
