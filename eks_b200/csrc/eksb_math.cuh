@@ -832,6 +832,37 @@ EKSB_HD void bwd_prep(const Params<T, N, P, AM>& prm, const T* m, const T* V, T*
   }
 }
 
+// The two halves of bwd_chain are independent recursions (the smoothed mean does not enter the smoothed
+// covariance and vice versa); the backward kernel runs them on two warps when an SM holds a single tile.
+template <typename T, int N>
+EKSB_HD void bwd_chain_mean(const T* rec, T* ms) {
+  constexpr int NS = Dim<N>::NS;
+  T ms1[N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) ms1[i] = ms[i];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    T s = rec[N * N + NS + i];
+    EKSB_UNROLL
+    for (int k = 0; k < N; ++k) s += rec[i * N + k] * ms1[k];
+    ms[i] = s;
+  }
+}
+template <typename T, int N>
+EKSB_HD void bwd_chain_cov(const T* rec, T* Vs) {
+  constexpr int NS = Dim<N>::NS;
+  T J[N][N], Vs1[NS], JVJ[NS];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) J[i][j] = rec[i * N + j];
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < NS; ++i) Vs1[i] = Vs[i];
+  sandwich<T, N>(J, Vs1, JVJ);
+  EKSB_UNROLL
+  for (int i = 0; i < NS; ++i) Vs[i] = rec[N * N + i] + JVJ[i];
+}
 template <typename T, int N>
 EKSB_HD void bwd_chain(const T* rec, T* ms, T* Vs) {
   constexpr int NS = Dim<N>::NS;

@@ -65,11 +65,21 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
 // (the launch picks the actual tiles per CTA, `tpc` <= TPC, so that tiles spread evenly over the SMs)
 template <int H_, int F_, int NST_, int TPC_> struct PipeCfg {
   static constexpr int H = H_, F = F_, NST = NST_, TPC = TPC_;
-  // upper bound on warps per CTA incl. filler warps (eksb_pipe_impl.cuh roles_warps): dedicated-scheduler
-  // placement for 1-2 tiles may need 4*H warps
-  static constexpr int WARPS_A = (TPC * (H + 1) + 3) / 4 * 4;
-  static constexpr int WARPS_B = 4 * H;
-  static constexpr int WARPS_C = (WARPS_A > WARPS_B ? WARPS_A : WARPS_B);
+  // upper bound on warps per CTA incl. filler warps: the largest value eksb_pipe_impl.cuh roles_warps returns
+  // for 1..TPC tiles per CTA (dedicated-scheduler placement for 1-2 tiles, packed placement for more)
+  static constexpr int warps_for(int tpc) {
+    if (tpc <= 2) {
+      const int per = (tpc * H + (4 - tpc) - 1) / (4 - tpc);
+      return 4 * (per < 1 ? 1 : per);
+    }
+    return 4 * ((tpc * (H + 1) + 3) / 4);
+  }
+  static constexpr int max_warps() {
+    int m = 4;
+    for (int t = 1; t <= TPC; ++t) m = warps_for(t) > m ? warps_for(t) : m;
+    return m;
+  }
+  static constexpr int WARPS_C = max_warps();
   static constexpr int THREADS = (WARPS_C > 32 ? 32 : WARPS_C) * kLanes;
 };
 
@@ -81,7 +91,9 @@ constexpr int kMaxWarps = 32;
 struct RoleMap {
   signed char tile[kMaxWarps];   // tile within the CTA, or -1: idle warp (exits at once)
   signed char h[kMaxWarps];      // -1: chain warp; 0..H-1: helper index
+  int chain_warps;               // backward kernel: 1, or 2 = covariance chain (h = -2) and mean chain (h = -3) apart
 };
+constexpr int kRoleBwdCov = -2, kRoleBwdMean = -3;
 
 template <typename T, int ROWS_IN, int REC, typename Cfg> struct PipeSmem {
   static constexpr size_t kRaw = (size_t)Cfg::NST * Cfg::F * ROWS_IN * kLanes * sizeof(T);
@@ -482,7 +494,7 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
   T* raw = reinterpret_cast<T*>(tile_smem);
   T* recb = reinterpret_cast<T*>(tile_smem + SM::kRaw);
   uint64_t* full = reinterpret_cast<uint64_t*>(tile_smem + SM::kRaw + SM::kRec);
-  const int bar_id = tile_in_cta + 1, bar_cnt = (H + 1) * kLanes;
+  const int bar_id = tile_in_cta + 1, bar_cnt = (H + roles.chain_warps) * kLanes;
   const long b = g * kLanes + lane;
   const long bp = b < B ? b : B - 1;
   Params<T, N, P, AM> prm;
@@ -612,6 +624,76 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
   tile_barrier(bar_id, bar_cnt);                           // (barrier init)
   tile_barrier(bar_id, bar_cnt);                           // batch 0 ready
   const long nfull = Tn / F;                               // batches with all F frames: no per-frame guards
+  const int role = roles.h[warp];
+  if (role == kRoleBwdCov) {                               // covariance recursion (+ yv) only
+    auto cframe = [&](const T* src, int j) {
+      T rec[N * N + NS];
+#pragma unroll
+      for (int r = 0; r < N * N + NS; ++r) rec[r] = src[(j * REC + r) * kLanes];
+      bwd_chain_cov<T, N>(rec, Vs);
+      T* o = so - (long)j * (SG * kLanes);
+#pragma unroll
+      for (int i = 0; i < NS; ++i) o[(N + i) * kLanes] = Vs[i];
+      if (kYv) {
+#pragma unroll
+        for (int jj = 0; jj < P; ++jj) {
+          T q = T(0);
+#pragma unroll
+          for (int i = 0; i < N; ++i) {
+            T a = T(0);
+#pragma unroll
+            for (int k2 = 0; k2 < N; ++k2) a += Vs[sym_idx<N>(i, k2)] * prm.C[jj][k2];
+            q += prm.C[jj][i] * a;
+          }
+          yvo[(jj - j * P) * kLanes] = q;
+        }
+      }
+    };
+    for (long k = 0; k < nb; ++k) {
+      const T* src = recb + (k & 1) * (F * REC * kLanes) + lane;
+      const int nfr = k < nfull ? F : (int)(Tn - k * F);
+#pragma unroll
+      for (int j = 0; j < F; ++j)
+        if (j < nfr) cframe(src, j);
+      so -= F * SG * kLanes;
+      if (kYv) yvo -= F * P * kLanes;
+      tile_barrier(bar_id, bar_cnt);
+    }
+    return;
+  }
+  if (role == kRoleBwdMean) {                              // mean recursion (+ ym) only
+    auto mframe = [&](const T* src, int j) {
+      T rec[REC];
+#pragma unroll
+      for (int r = 0; r < N * N; ++r) rec[r] = src[(j * REC + r) * kLanes];
+#pragma unroll
+      for (int r = 0; r < N; ++r) rec[N * N + NS + r] = src[(j * REC + N * N + NS + r) * kLanes];
+      bwd_chain_mean<T, N>(rec, ms);
+      T* o = so - (long)j * (SG * kLanes);
+#pragma unroll
+      for (int i = 0; i < N; ++i) o[i * kLanes] = ms[i];
+      if (kYm) {
+#pragma unroll
+        for (int jj = 0; jj < P; ++jj) {
+          T s2 = T(0);
+#pragma unroll
+          for (int i = 0; i < N; ++i) s2 += prm.C[jj][i] * ms[i];
+          ymo[(jj - j * P) * kLanes] = s2;
+        }
+      }
+    };
+    for (long k = 0; k < nb; ++k) {
+      const T* src = recb + (k & 1) * (F * REC * kLanes) + lane;
+      const int nfr = k < nfull ? F : (int)(Tn - k * F);
+#pragma unroll
+      for (int j = 0; j < F; ++j)
+        if (j < nfr) mframe(src, j);
+      so -= F * SG * kLanes;
+      if (kYm) ymo -= F * P * kLanes;
+      tile_barrier(bar_id, bar_cnt);
+    }
+    return;
+  }
   for (long k = 0; k < nb; ++k) {
     const T* src = recb + (k & 1) * (F * REC * kLanes) + lane;
     if (k < nfull) {

@@ -37,8 +37,9 @@ inline int roles_warps(int tpc, int H) {
   }
   return 4 * ((tpc * (H + 1) + 3) / 4);
 }
-inline int make_roles(int tpc, int H, float w_chain, float w_helper, RoleMap& rm) {
+inline int make_roles(int tpc, int H, float w_chain, float w_helper, RoleMap& rm, bool split_chain = false) {
   for (int w = 0; w < kMaxWarps; ++w) { rm.tile[w] = -1; rm.h[w] = -1; }
+  rm.chain_warps = 1;
   int len[4] = {0, 0, 0, 0};
   auto put = [&](int s2, int tile, int h) {
     const int w = 4 * len[s2] + s2;
@@ -46,6 +47,13 @@ inline int make_roles(int tpc, int H, float w_chain, float w_helper, RoleMap& rm
     rm.h[w] = (signed char)h;
     ++len[s2];
   };
+  if (tpc == 1 && split_chain) {                    // backward: covariance chain, mean chain, helpers on the rest
+    rm.chain_warps = 2;
+    put(0, 0, kRoleBwdCov);
+    put(1, 0, kRoleBwdMean);
+    for (int h = 0; h < H; ++h) put(2 + (h & 1), 0, h);
+    return 4 * ((H + 1) / 2 < 1 ? 1 : (H + 1) / 2);
+  }
   if (tpc <= 2) {
     for (int t = 0; t < tpc; ++t) put(t, t, -1);
     int s2 = tpc;
@@ -124,6 +132,15 @@ template <typename T, int H, int ROWS_IN, int REC, int FORCE_F = 0, int FORCE_NS
 #ifndef EKSB_BWD_WIDE_NST
 #define EKSB_BWD_WIDE_NST 3
 #endif
+#ifndef EKSB_BWD_WIDE_F
+#define EKSB_BWD_WIDE_F 6
+#endif
+#ifndef EKSB_BWD_SOLO_H
+#define EKSB_BWD_SOLO_H 4
+#endif
+#ifndef EKSB_BWD_SOLO_F
+#define EKSB_BWD_SOLO_F 8
+#endif
 constexpr int kFwdHelpers = EKSB_FWD_H, kBwdHelpers = EKSB_BWD_H;
 // instructions per frame (n=3, p=4, f64 SASS): forward chain / helper, backward chain / helpers
 constexpr float kFwdChainW = 118, kFwdHelperW = 125, kBwdChainW = 103, kBwdHelperW = 200;
@@ -147,6 +164,7 @@ static int launch_fwd_cfg(const T* obs, const T* m0, const T* S0, const T* C, co
 // warps and helpers round-robin on the other schedulers.  tpc <= 2 only.
 inline int make_roles3(int tpc, int H, RoleMap& rm) {
   for (int w = 0; w < kMaxWarps; ++w) { rm.tile[w] = -1; rm.h[w] = 0; }
+  rm.chain_warps = 2;
   int len[4] = {0, 0, 0, 0};
   auto put = [&](int s2, int tile, int h) {
     const int w = 4 * len[s2] + s2;
@@ -183,14 +201,20 @@ template <typename T, int N, int P, int H> struct Auto3 {
   static constexpr size_t kTileSmem = bytes<F, NST>();
 };
 
-#ifndef EKSB_FWD3_H
-#define EKSB_FWD3_H 2
+// helpers of the three-role forward kernel.  Measured at one tile per SM, 100 000 frames: f64 13.6 / 11.7 / 11.2 ms
+// with 2 / 3 / 4 helpers, f32 7.9 / 9.7 / 10.2 ms.
+#ifndef EKSB_FWD3_H64
+#define EKSB_FWD3_H64 4
 #endif
+#ifndef EKSB_FWD3_H32
+#define EKSB_FWD3_H32 2
+#endif
+template <typename T> struct Fwd3Helpers { static constexpr int value = sizeof(T) == 8 ? EKSB_FWD3_H64 : EKSB_FWD3_H32; };
 
 template <typename T, int N, int P>
 static int launch_fwd_pipe3(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                             long B, long Tn, int first, T* filt, int* status, int tpc, cudaStream_t st) {
-  using Auto = Auto3<T, N, P, EKSB_FWD3_H>;
+  using Auto = Auto3<T, N, P, Fwd3Helpers<T>::value>;
   using Cfg = typename Auto::type;
   auto kern = kf_forward_pipe3_kernel<T, N, P, Cfg>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(Auto::kTileSmem * 2));
@@ -211,7 +235,7 @@ static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, c
                            long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
   using Shallow = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, EKSB_FWD_F, EKSB_FWD_NST>;
   using Deep = AutoCfg<T, EKSB_FWD_DEEP_H, 2 * P, Rec<N>::FWD, 8, 4>;
-  if constexpr (OP == 0 && AM == 0 && N <= 3 && Auto3<T, N, P, EKSB_FWD3_H>::ok) {
+  if constexpr (OP == 0 && AM == 0 && N <= 3 && Auto3<T, N, P, Fwd3Helpers<T>::value>::ok) {
     const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
     // Measured (f64, 100 000 frames, sustained): one tile per SM 16.2 -> 13.5 ms (the pass runs at the chain's
     // pace); two tiles per SM 18.3 -> 20.8 ms (the FP64 pipes of the two helper schedulers saturate once they
@@ -241,7 +265,8 @@ static int launch_bwd_cfg(const T* filt, const T* C, const T* A, const T* Q, int
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(Auto::kTileSmem * Cfg::TPC));
   const unsigned grid = (unsigned)((num_tiles(B) + tpc - 1) / tpc);
   RoleMap rm;
-  const int warps = make_roles(tpc, Cfg::H, kBwdChainW, kBwdHelperW, rm);
+  static const bool no_split = getenv("EKSB_BWD_NO_SPLIT") != nullptr;
+  const int warps = make_roles(tpc, Cfg::H, kBwdChainW, kBwdHelperW, rm, !no_split);
   kern<<<grid, warps * kLanes, smem, st>>>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, tpc, rm);
   return check_launch("rts_backward_pipe_kernel");
 }
@@ -254,7 +279,15 @@ template <typename T, int N, int P, int AM, int OP, int OUT>
 static int launch_bwd_pipe_out(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
                                T* smth, T* ym, T* yv, int* status, cudaStream_t st) {
   using Narrow = AutoCfg<T, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_F, EKSB_BWD_NST>;
-  using Wide = AutoCfg<T, EKSB_BWD_WIDE_H, Dim<N>::SIGMA, Rec<N>::BWD, 6, EKSB_BWD_WIDE_NST>;
+  using Wide = AutoCfg<T, EKSB_BWD_WIDE_H, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_WIDE_F, EKSB_BWD_WIDE_NST>;
+  // "Solo": an SM holds one tile, so the whole shared memory and all four schedulers serve it -- 4 helpers on
+  // 8-frame batches, covariance and mean chains on two warps (f64 4736 tracks x 100 000 frames: 15.8 -> 13.0 ms).
+  using Solo = AutoCfg<T, EKSB_BWD_SOLO_H, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_SOLO_F, 3>;
+  if constexpr (N <= 3 && Solo::ok) {
+    static const bool no_solo = getenv("EKSB_BWD_NO_SOLO") != nullptr;
+    if (!no_solo && num_tiles(B) <= kSMs)
+      return launch_bwd_cfg<T, N, P, AM, OP, OUT, Solo>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+  }
   if constexpr (N <= 3 && Wide::ok) {
     const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
     static const bool narrow_only = getenv("EKSB_BWD_NARROW") != nullptr;
