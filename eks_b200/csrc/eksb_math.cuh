@@ -1225,4 +1225,142 @@ EKSB_HD void bwd_summary_step(const T* rec, T* acc) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// Chunk programs of the scan (one warp per (track tile, chunk) on the device, one call per chunk in
+// the host tests).  Both stop paying for the summary as soon as it has become irrelevant:
+// the filter forgets its start exponentially, so after K frames the sensitivity Phi of the chunk's
+// running state to the unknown start state is numerically zero (|Phi| < ScanCut, checked every 16
+// frames for the whole warp).  From there on (b, C) IS the filtered state, so the rest of the chunk
+// is run as the ordinary filter and its records are written out at once; only the first K frames of
+// the chunk have to be re-run after the fold.  The same holds for the smoother's E (product of the
+// RTS gains).  HBM traffic drops from (2 reads of the input + 1 write) to (1 + K/L reads + 1 write).
+// ---------------------------------------------------------------------------
+template <typename T> struct ScanCut;
+// state error after the cut <= ScanCut * |x_start|: below one ulp of the state for |x_start| up to ~1e6 (f64) / ~1e4 (f32)
+template <> struct ScanCut<double> { static constexpr double value = 1e-22; };
+template <> struct ScanCut<float> { static constexpr float value = 1e-11f; };
+
+#if defined(__CUDA_ARCH__)
+#define EKSB_WARP_ALL(pred) __all_sync(0xffffffffu, (pred))
+#else
+#define EKSB_WARP_ALL(pred) (pred)
+#endif
+
+// Forward summary of one chunk of `n` frames.  obs / filt point at the chunk's first frame.
+// sum (ScanRec<N>::FWD values, local) receives the element.  Returns the cut k: frames [k, n) of the
+// chunk have been written to filt (k == n: nothing written, the whole chunk must be re-run).
+template <typename T, int N, int P, int AM, int LS, int PF>
+EKSB_HD long scan_fwd_chunk(const Params<T, N, P, AM>& prm, const T* __restrict__ obs, T* __restrict__ filt, long n,
+                            bool early_out, T* sum, bool& ok) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
+  T Phi[N][N], bb[N], Cc[NS], eta[N], J[NS];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    bb[i] = eta[i] = T(0);
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) Phi[i][j] = (i == j) ? T(1) : T(0);
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < NS; ++i) Cc[i] = J[i] = T(0);
+  T nxt[R2];
+  EKSB_UNROLL
+  for (int r = 0; r < R2; ++r) nxt[r] = obs[r * LS];
+  long t = 0;
+  bool dead = false;
+  while (t < n) {
+    T cur[R2], rec[Rec<N>::FWD];
+    EKSB_UNROLL
+    for (int r = 0; r < R2; ++r) cur[r] = nxt[r];
+    const long f = (t + 1 < n) ? t + 1 : n - 1;
+    EKSB_UNROLL
+    for (int r = 0; r < R2; ++r) nxt[r] = obs[(f * R2 + r) * LS];
+    fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
+    fwd_summary_step<T, N, P, AM>(prm, rec, Phi, bb, Cc, eta, J, ok);
+    ++t;
+    if ((t & 15) == 0) {
+      T mx = T(0);
+      EKSB_UNROLL
+      for (int i = 0; i < N; ++i) {
+        EKSB_UNROLL
+        for (int j = 0; j < N; ++j) mx = fmax(mx, fabs(Phi[i][j]));
+      }
+      if (EKSB_WARP_ALL(mx < ScanCut<T>::value)) { dead = true; break; }
+    }
+  }
+  long cut = n;
+  if (dead) {
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) Phi[i][j] = T(0);
+    }
+    if (t < n) {
+      if (early_out) cut = t;
+      double acc = 0.0;
+      ok = kf_forward_range<T, N, P, AM, LS, PF, false>(prm, obs + t * R2 * LS, early_out ? filt + t * SG * LS : nullptr,
+                                                        n - t, kContinue, bb, Cc, acc) && ok;
+    }
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) sum[i * N + j] = Phi[i][j];
+    sum[N * N + i] = bb[i];
+    sum[N * N + N + NS + i] = eta[i];
+  }
+  EKSB_UNROLL
+  for (int i = 0; i < NS; ++i) {
+    sum[N * N + N + i] = Cc[i];
+    sum[N * N + N + NS + N + i] = J[i];
+  }
+  return cut;
+}
+
+// Backward (smoother) summary of one chunk of `n` frames, last frame first; filt / smth / ym point at
+// the chunk's first frame (smth may alias filt: a frame is read before it is overwritten, and frames
+// >= the returned cut are left untouched for the re-run).  acc (ScanRec<N>::BWD values, local) receives
+// (E, L, g).  Returns the cut k: frames [0, k) of the chunk have been smoothed and written (k == 0:
+// nothing written).
+template <typename T, int N, int P, int AM, int LS, int PF>
+EKSB_HD long scan_bwd_chunk(const Params<T, N, P, AM>& prm, const T* filt, T* smth, T* ym, long n, bool early_out,
+                            T* acc, bool& ok) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
+  EKSB_UNROLL
+  for (int i = 0; i < SR; ++i) acc[i] = T(0);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) acc[i * N + i] = T(1);
+  T nxt[SG];
+  EKSB_UNROLL
+  for (int r = 0; r < SG; ++r) nxt[r] = filt[((n - 1) * SG + r) * LS];
+  long t = n - 1, done = 0;
+  bool dead = false;
+  while (t >= 0) {
+    T cur[SG], rec[Rec<N>::BWD];
+    EKSB_UNROLL
+    for (int r = 0; r < SG; ++r) cur[r] = nxt[r];
+    const long f = (t - 1 >= 0) ? t - 1 : 0;
+    EKSB_UNROLL
+    for (int r = 0; r < SG; ++r) nxt[r] = filt[(f * SG + r) * LS];
+    bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
+    bwd_summary_step<T, N>(rec, acc);
+    --t;
+    ++done;
+    if (early_out && (done & 15) == 0) {
+      T mx = T(0);
+      EKSB_UNROLL
+      for (int i = 0; i < N * N; ++i) mx = fmax(mx, fabs(acc[i]));
+      if (EKSB_WARP_ALL(mx < ScanCut<T>::value)) { dead = true; break; }
+    }
+  }
+  long cut = 0;
+  if (dead && t >= 0) {
+    cut = t + 1;
+    EKSB_UNROLL
+    for (int i = 0; i < N * N; ++i) acc[i] = T(0);
+    ok = rts_backward_range<T, N, P, AM, LS, PF>(prm, filt, smth, ym, nullptr, nullptr, cut, false, acc + N * N + NS,
+                                                 acc + N * N) && ok;
+  }
+  return cut;
+}
+
 }  // namespace eksb

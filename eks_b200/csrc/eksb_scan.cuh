@@ -9,7 +9,11 @@
 //   3. re-run kernel  : every chunk runs the ordinary sequential recursion from its exact boundary
 //                       state and writes the per-frame records (kf_forward_range / rts_backward_range).
 // The result is the sequential result up to rounding (tests: chunked == sequential == oracle).
-// Extra HBM traffic vs the sequential kernels: one more read of the pass's input.
+// Early write-out (eksb_math.cuh scan_fwd_chunk / scan_bwd_chunk): once a chunk's summary has forgotten
+// the chunk's unknown boundary state (|Phi| resp. |E| numerically zero for the whole warp), the summary
+// kernel's running state is the exact state, so it writes the per-frame records itself for the rest of
+// the chunk and records the cut; the re-run kernel then only covers the K frames before the cut.
+// HBM traffic: (1 + K/L) reads of the pass's input + 1 write, against 2 reads + 1 write without it.
 #pragma once
 #include "eksb_common.cuh"
 
@@ -21,18 +25,16 @@ constexpr int kScanWarps = 4;   // warps (= chunks) per CTA
 // Work items [0, tiles): chunk 0 of each tile, run as the ordinary filter from the prior (it needs no
 // summary, only its end state, and would otherwise be a serial 1-warp-per-tile launch of its own).
 // Work items [tiles, tiles*nc): summary of chunk c >= 1.  Once the sensitivity Phi of a chunk's running
-// mean to its unknown start state has decayed below kPhiCut for all 32 tracks of the warp (the filter
+// mean to its unknown start state has decayed below ScanCut for all 32 tracks of the warp (the filter
 // forgets its start exponentially), J and eta have stopped changing and Phi is numerically zero, so the
-// rest of the chunk is the plain filter step (2.4x cheaper); the element is exact to ~kPhiCut * |x_start|.
-template <typename T> struct PhiCut;
-template <> struct PhiCut<double> { static constexpr double value = 1e-26; };
-template <> struct PhiCut<float> { static constexpr float value = 1e-13f; };
-
+// rest of the chunk is the plain filter (2.4x cheaper) whose records are final and written at once;
+// fcut[g*nc+c] = number of leading frames of the chunk that still need the re-run.
 template <typename T, int N, int P, int AM>
 __global__ void __launch_bounds__(kScanWarps* kLanes)
 scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                         const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
-                        long B, long Tn, long L, long nc, T* __restrict__ fsum, T* __restrict__ filt,
+                        long B, long Tn, long L, long nc, int early_out, T* __restrict__ fsum,
+                        long* __restrict__ fcut, int* __restrict__ alive, T* __restrict__ filt,
                         int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, SR = ScanRec<N>::FWD;
   const int lane = threadIdx.x & 31;
@@ -63,65 +65,31 @@ scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
   const long c = wi - g * (nc - 1) + 1;
   const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
-  T Phi[N][N], bb[N], Cc[NS], eta[N], J[NS];
-#pragma unroll
-  for (int i = 0; i < N; ++i) {
-    bb[i] = eta[i] = T(0);
-#pragma unroll
-    for (int j = 0; j < N; ++j) Phi[i][j] = (i == j) ? T(1) : T(0);
-  }
-#pragma unroll
-  for (int i = 0; i < NS; ++i) Cc[i] = J[i] = T(0);
   bool ok = true;
-  const long t1 = (c + 1) * L < Tn ? (c + 1) * L : Tn;
-  const T* o = obs + (g * Tn * R2) * kLanes + lane;
-  long t = c * L;
-  for (; t < t1; ++t) {
-    T cur[R2], rec[Rec<N>::FWD];
-#pragma unroll
-    for (int r = 0; r < R2; ++r) cur[r] = o[(t * R2 + r) * kLanes];
-    fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
-    fwd_summary_step<T, N, P, AM>(prm, rec, Phi, bb, Cc, eta, J, ok);
-    if (((t - c * L) & 15) == 15) {                        // every 16 frames: has Phi died out for the whole warp?
-      T mx = T(0);
-#pragma unroll
-      for (int i = 0; i < N; ++i)
-#pragma unroll
-        for (int j = 0; j < N; ++j) mx = fmax(mx, fabs(Phi[i][j]));
-      if (__all_sync(0xffffffffu, mx < PhiCut<T>::value)) { ++t; break; }
-    }
-  }
-  if (t < t1) {                                            // tail: plain filter on (bb, Cc), Phi == 0
-#pragma unroll
-    for (int i = 0; i < N; ++i)
-#pragma unroll
-      for (int j = 0; j < N; ++j) Phi[i][j] = T(0);
-    for (; t < t1; ++t) {
-      T cur[R2], rec[Rec<N>::FWD];
-#pragma unroll
-      for (int r = 0; r < R2; ++r) cur[r] = o[(t * R2 + r) * kLanes];
-      fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
-      fwd_chain<T, N, P, AM>(prm, rec, true, bb, Cc, ok);
-    }
+  const long t0 = c * L, t1 = (c + 1) * L < Tn ? (c + 1) * L : Tn;
+  T sum[SR];
+  const long cut = scan_fwd_chunk<T, N, P, AM, kLanes, 2>(prm, obs + ((g * Tn + t0) * R2) * kLanes + lane,
+                                                          filt + ((g * Tn + t0) * SG) * kLanes + lane, t1 - t0,
+                                                          early_out != 0, sum, ok);
+  if (lane == 0) {
+    fcut[g * nc + c] = cut;
+    if (cut >= t1 - t0) atomicOr(alive, 1);                // its last frame is not final: the fold has to run
   }
   T* out = fsum + ((g * nc + c) * SR) * kLanes + lane;
 #pragma unroll
-  for (int i = 0; i < N; ++i)
-#pragma unroll
-    for (int j = 0; j < N; ++j) out[(i * N + j) * kLanes] = Phi[i][j];
-#pragma unroll
-  for (int i = 0; i < N; ++i) { out[(N * N + i) * kLanes] = bb[i]; out[(N * N + N + NS + i) * kLanes] = eta[i]; }
-#pragma unroll
-  for (int i = 0; i < NS; ++i) { out[(N * N + N + i) * kLanes] = Cc[i]; out[(N * N + N + NS + N + i) * kLanes] = J[i]; }
+  for (int r = 0; r < SR; ++r) out[r * kLanes] = sum[r];
   if (b < B && status && !ok) status[b] = 1;
 }
 
 // ---- 2a. forward fold: exact filtered state at the frame before every chunk ---------------------
+// Only needed when some chunk did not forget its start (alive != 0); a chunk that did has already written
+// its exact last frame, which is the next chunk's start state.
 template <typename T, int N>
 __global__ void __launch_bounds__(kLanes)
 scan_fwd_fold_kernel(const T* __restrict__ filt, const T* __restrict__ fsum, long B, long Tn, long L, long nc,
-                     T* __restrict__ finit, int* __restrict__ status) {
+                     const int* __restrict__ alive, T* __restrict__ finit, int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::FWD;
+  if (*alive == 0) return;       // every chunk wrote its own last frame: the re-run reads its start states from filt
   const int lane = threadIdx.x;
   const long g = blockIdx.x;
   const long b = g * kLanes + lane;
@@ -162,8 +130,8 @@ template <typename T, int N, int P, int AM>
 __global__ void __launch_bounds__(kScanWarps* kLanes)
 scan_fwd_rerun_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                       const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask, long B,
-                      long Tn, long L, long nc, long c_lo, long c_hi, const T* __restrict__ finit, T* __restrict__ filt,
-                      int* __restrict__ status) {
+                      long Tn, long L, long nc, long c_lo, long c_hi, const T* __restrict__ finit,
+                      const long* __restrict__ fcut, T* filt, int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
   const int lane = threadIdx.x & 31;
   const long span = c_hi - c_lo;
@@ -184,13 +152,19 @@ scan_fwd_rerun_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const
     load_sym<T, N>(V, ps);
     first = kPriorUpdate;
   } else {
-    const T* s = finit + ((g * nc + c) * SG) * kLanes + lane;
+    // start state: the last frame of chunk c-1 if that chunk wrote it itself (chunk 0 always did), else the fold's
+    const bool prev_final = (c == 1) || (fcut && fcut[g * nc + c - 1] < L);
+    const T* s = prev_final ? filt + ((g * Tn + c * L - 1) * SG) * kLanes + lane
+                            : finit + ((g * nc + c) * SG) * kLanes + lane;
 #pragma unroll
     for (int i = 0; i < N; ++i) m[i] = s[i * kLanes];
 #pragma unroll
     for (int i = 0; i < NS; ++i) V[i] = s[(N + i) * kLanes];
   }
-  const long t0 = c * L, t1 = (c + 1) * L < Tn ? (c + 1) * L : Tn;
+  const long t0 = c * L;
+  long t1 = (c + 1) * L < Tn ? (c + 1) * L : Tn;
+  if (fcut && c > 0) t1 = t0 + fcut[g * nc + c];           // the summary kernel wrote the frames from the cut on
+  if (t1 <= t0) return;
   double acc = 0.0;
   bool ok = kf_forward_range<T, N, P, AM, kLanes, 2, false>(prm, obs + ((g * Tn + t0) * R2) * kLanes + lane,
                                                             filt + ((g * Tn + t0) * SG) * kLanes + lane, t1 - t0, first,
@@ -201,12 +175,15 @@ scan_fwd_rerun_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const
 // ---- 1b. backward chunk summaries, chunks [0, nc-1), plus the sequential run of the last chunk --------
 // Work items [0, tiles): the terminal chunk of each tile, smoothed directly (ms = mf at T-1); it only
 // touches its own frames, so it can ride in the launch that summarises the other chunks (smth may alias
-// filt).  Work items [tiles, tiles*nc): (E, g, L) summary of chunk c < nc-1.
+// filt).  Work items [tiles, tiles*nc): (E, g, L) summary of chunk c < nc-1; once E has died out the
+// chunk's remaining (earlier) frames are smoothed and written here, bcut[g*nc+c] = first frame offset
+// of the chunk that still needs the re-run.
 template <typename T, int N, int P, int AM>
 __global__ void __launch_bounds__(kScanWarps* kLanes)
 scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A,
-                        const T* __restrict__ Q, int shared_mask, long B, long Tn, long L, long nc,
-                        T* __restrict__ bsum, T* smth, T* __restrict__ ym, int* __restrict__ status) {
+                        const T* __restrict__ Q, int shared_mask, long B, long Tn, long L, long nc, int early_out,
+                        T* __restrict__ bsum, long* __restrict__ bcut, int* __restrict__ alive, T* smth, T* ym,
+                        int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
   const int lane = threadIdx.x & 31;
   const long tiles = num_tiles_dev(B);
@@ -232,18 +209,13 @@ scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restr
   const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
   T acc[SR];
-#pragma unroll
-  for (int i = 0; i < SR; ++i) acc[i] = T(0);
-#pragma unroll
-  for (int i = 0; i < N; ++i) acc[i * N + i] = T(1);
   bool ok = true;
-  const T* f = filt + (g * Tn * SG) * kLanes + lane;
-  for (long t = (c + 1) * L - 1; t >= c * L; --t) {
-    T cur[SG], rec[Rec<N>::BWD];
-#pragma unroll
-    for (int r = 0; r < SG; ++r) cur[r] = f[(t * SG + r) * kLanes];
-    bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
-    bwd_summary_step<T, N>(rec, acc);
+  const long base = (g * Tn + c * L) * kLanes;
+  const long cut = scan_bwd_chunk<T, N, P, AM, kLanes, 2>(prm, filt + base * SG + lane, smth + base * SG + lane,
+                                                          ym ? ym + base * P + lane : nullptr, L, early_out != 0, acc, ok);
+  if (lane == 0) {
+    bcut[g * nc + c] = cut;
+    if (cut <= 0) atomicOr(alive, 1);                      // its first frame is not final: the fold has to run
   }
   T* out = bsum + ((g * nc + c) * SR) * kLanes + lane;
 #pragma unroll
@@ -255,8 +227,9 @@ scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restr
 template <typename T, int N>
 __global__ void __launch_bounds__(kLanes)
 scan_bwd_fold_kernel(const T* __restrict__ smth, const T* __restrict__ bsum, long B, long Tn, long L, long nc,
-                     T* __restrict__ binit) {
+                     const int* __restrict__ alive, T* __restrict__ binit) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
+  if (*alive == 0) return;       // every chunk smoothed its own first frame: the re-run reads it from smth
   const int lane = threadIdx.x;
   const long g = blockIdx.x;
   T ms[N], Vs[NS];
@@ -284,7 +257,8 @@ template <typename T, int N, int P, int AM>
 __global__ void __launch_bounds__(kScanWarps* kLanes)
 scan_bwd_rerun_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
                       int shared_mask, long B, long Tn, long L, long nc, long c_lo, long c_hi,
-                      const T* __restrict__ binit, T* smth, T* __restrict__ ym, int* __restrict__ status) {
+                      const T* __restrict__ binit, const long* __restrict__ bcut, T* smth, T* ym,
+                      int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
   const int lane = threadIdx.x & 31;
   const long span = c_hi - c_lo;
@@ -298,13 +272,19 @@ scan_bwd_rerun_kernel(const T* filt, const T* __restrict__ C, const T* __restric
   T ms[N], Vs[NS];
   const bool terminal = (c == nc - 1);
   if (!terminal) {
-    const T* s = binit + ((g * nc + c) * SG) * kLanes + lane;
+    // smoothed state of the frame after this chunk: chunk c+1's first frame if its summary pass (or the
+    // terminal run) already wrote it -- the re-run of chunk c+1 only touches frames from its cut on
+    const bool next_final = (c + 1 == nc - 1) || (bcut && bcut[g * nc + c + 1] > 0);
+    const T* s = next_final ? smth + ((g * Tn + (c + 1) * L) * SG) * kLanes + lane
+                            : binit + ((g * nc + c) * SG) * kLanes + lane;
 #pragma unroll
     for (int i = 0; i < N; ++i) ms[i] = s[i * kLanes];
 #pragma unroll
     for (int i = 0; i < NS; ++i) Vs[i] = s[(N + i) * kLanes];
   }
-  const long t0 = c * L, t1 = (c + 1) * L < Tn ? (c + 1) * L : Tn;
+  long t0 = c * L;
+  const long t1 = (c + 1) * L < Tn ? (c + 1) * L : Tn;
+  if (bcut && !terminal) t0 += bcut[g * nc + c];           // the summary kernel smoothed the frames below the cut
   const long base = (g * Tn + t0) * kLanes;
   bool ok = rts_backward_range<T, N, P, AM, kLanes, 2>(prm, filt + base * SG + lane, smth + base * SG + lane,
                                                       ym ? ym + base * P + lane : nullptr, nullptr, nullptr, t1 - t0,

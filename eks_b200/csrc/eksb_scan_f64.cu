@@ -10,6 +10,6 @@ extern "C" int eksb_kf_rts_scan_f64(const double* obs, const double* m0, const d
 
 extern "C" size_t eksb_scan_workspace_bytes(long B, long T, int n, long chunk, int elem_size) {
   if (B <= 0 || T <= 0 || n <= 0) return 0;
-  return scan_workspace_elems(B, T, n, chunk > 0 ? chunk : scan_auto_chunk(B, T)) * (size_t)elem_size;
+  return scan_workspace_elems(B, T, n, chunk > 0 ? chunk : scan_auto_chunk(B, T, n, elem_size)) * (size_t)elem_size;
 }
-extern "C" long eksb_scan_chunk_len(long B, long T, long chunk) { return chunk > 0 ? chunk : scan_auto_chunk(B, T); }
+extern "C" long eksb_scan_chunk_len(long B, long T, int n, long chunk, int elem_size) { return chunk > 0 ? chunk : scan_auto_chunk(B, T, n, elem_size); }

@@ -4,17 +4,27 @@
 
 namespace eksb {
 
+inline long scan_env_long(const char* name, long dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atol(v) : dflt;
+}
+
 inline size_t scan_workspace_elems(long B, long Tn, int n, long L) {
   const long nc = (Tn + L - 1) / L;
   const long per = (n * n + n + 2 * (n * (n + 1) / 2) + n)      /* forward summary  */
                    + (n * n + n * (n + 1) / 2 + n)             /* backward summary */
-                   + 2 * (n + n * (n + 1) / 2);                /* boundary states, both passes */
+                   + 2 * (n + n * (n + 1) / 2)                 /* boundary states, both passes */
+                   + 1;                                        /* the two cut positions (2 x int64 per warp) */
   return (size_t)num_tiles(B) * nc * per * kLanes;
 }
 
-inline long scan_auto_chunk(long B, long Tn) {
-  // aim at ~32 resident warps per SM: warps = tiles * chunks
-  const long want_chunks = (148L * 32 + num_tiles(B) - 1) / num_tiles(B);
+inline long scan_auto_chunk(long B, long Tn, int n, int elem_size) {
+  // warps = tiles * chunks.  The kernels are register-bound at 12 (f64, n <= 3), 8 (f64, n = 4) and 20 (f32)
+  // resident warps per SM; aim at ONE full wave (f32: 16 measured best).  Longer chunks amortise the K warm-up
+  // frames every chunk pays before its summary has forgotten the boundary state (eksb_math.cuh scan_fwd_chunk):
+  // measured on 64 tracks x 10 M frames f64, 12 / 24 / 36 / 48 warps per SM -> 36.5 / 37.4 / 43.7 / 46.7 ms.
+  const long per_sm = scan_env_long("EKSB_SCAN_WARPS_PER_SM", elem_size == 8 ? (n >= 4 ? 8 : 12) : 16);
+  const long want_chunks = (148L * per_sm + num_tiles(B) - 1) / num_tiles(B);
   long L = (Tn + want_chunks - 1) / want_chunks;
   if (L < 64) L = 64;
   return L;
@@ -29,27 +39,32 @@ static int scan_run(const T* obs, const T* m0, const T* S0, const T* C, const T*
   T* bsum = fsum + (size_t)tiles * nc * ScanRec<N>::FWD * kLanes;
   T* finit = bsum + (size_t)tiles * nc * ScanRec<N>::BWD * kLanes;
   T* binit = finit + (size_t)tiles * nc * SG * kLanes;
+  long* fcut = reinterpret_cast<long*>(binit + (size_t)tiles * nc * SG * kLanes);   // 32 T's (>= 16 B) per (tile, chunk)
+  long* bcut = fcut + tiles * nc;
+  int* alive = reinterpret_cast<int*>(bcut + tiles * nc);   // [0] forward, [1] backward: "the fold must run"
+  if (nc > 1 && cudaMemsetAsync(alive, 0, 2 * sizeof(int), st) != cudaSuccess) return check_launch("scan flags");
+  const int early = scan_env_long("EKSB_SCAN_NO_EARLY", 0) ? 0 : 1;                 // A/B switch: old 2-read behaviour
   auto blocks = [&](long items) { return (unsigned)((items + kScanWarps - 1) / kScanWarps); };
   const int thr = kScanWarps * kLanes;
   // forward pass
   if (nc == 1) {
-    scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 0, 1, finit, filt, status);
+    scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 0, 1, finit, nullptr, filt, status);
   } else {
     // chunk 0 (sequential from the prior) rides in the same launch as the summaries of chunks >= 1
-    scan_fwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, fsum, filt, status);
-    scan_fwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(filt, fsum, B, Tn, L, nc, finit, status);
-    scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 1, nc, finit, filt, status);
+    scan_fwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, early, fsum, fcut, alive, filt, status);
+    scan_fwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(filt, fsum, B, Tn, L, nc, alive, finit, status);
+    scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 1, nc, finit, fcut, filt, status);
   }
   int rc = check_launch("scan forward kernels");
   if (rc != EKSB_OK || !smth) return rc;
   // backward pass (smth may alias filt: a chunk only reads and writes its own frames)
   if (nc == 1) {
-    scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, nc - 1, nc, binit, smth, ym, status);
+    scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, nc - 1, nc, binit, nullptr, smth, ym, status);
   } else {
     // the terminal chunk (sequential from the end of the track) rides in the summary launch
-    scan_bwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, bsum, smth, ym, status);
-    scan_bwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(smth, bsum, B, Tn, L, nc, binit);
-    scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, 0, nc - 1, binit, smth, ym, status);
+    scan_bwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, early, bsum, bcut, alive + 1, smth, ym, status);
+    scan_bwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(smth, bsum, B, Tn, L, nc, alive + 1, binit);
+    scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, 0, nc - 1, binit, bcut, smth, ym, status);
   }
   return check_launch("scan backward kernels");
 }
@@ -60,7 +75,7 @@ static int scan_api(const T* obs, const T* m0, const T* S0, const T* C, const T*
                     void* stream) {
   if (!obs || !m0 || !S0 || !C || !A || !Q || !filt || !ws || B <= 0 || Tn <= 0) { set_error("kf_rts_scan: null pointer or empty batch"); return EKSB_EARG; }
   if (a_mode != EKSB_A_DIAG && a_mode != EKSB_A_DENSE) { set_error("kf_rts_scan: bad a_mode %d", a_mode); return EKSB_EARG; }
-  const long L = chunk > 0 ? chunk : scan_auto_chunk(B, Tn);
+  const long L = chunk > 0 ? chunk : scan_auto_chunk(B, Tn, n, (int)sizeof(T));
   if (scan_workspace_elems(B, Tn, n, L) * sizeof(T) > ws_bytes) { set_error("kf_rts_scan: workspace too small (%zu bytes needed)", scan_workspace_elems(B, Tn, n, L) * sizeof(T)); return EKSB_EARG; }
 #define X(N_, P_)                                                                                                   \
   if (n == N_ && p == P_)                                                                                           \

@@ -288,11 +288,21 @@ def rts_backward(filt, prm: TrackParams, B, T, inplace=False, want_ym=True, want
 
 
 # ------------------------------------------------------------------ A7 block-tridiagonal solve
-def btd_solve(obs, prm: TrackParams, B, T, want_ym=False, inplace=True, status=None):
+def btd_solve(obs, prm: TrackParams, B, T, want_ym=False, inplace=True, status=None, scan=None):
     """Block-tridiagonal Newton step.  prm.C is the observation matrix B, prm.Q the process noise E.
-    Returns dict(sol [x | diag blocks of H^-1, state-record layout], ym, status)."""
+    Returns dict(sol [x | diag blocks of H^-1, state-record layout], ym, status).
+
+    scan: None = parallel-in-time for a handful of long tracks (fewer track tiles than SMs, T >= 4096:
+    config 5), False = block-Thomas elimination (eksb_btd_solve), True = force the scan.  The scan route uses
+    the identity the solver is pinned by (x == RTS mean, diagonal blocks of H^-1 == Vs):
+    the same system is solved by the chunked filter + smoother elements of eksb_kf_rts_scan."""
     _need_cuda(obs, "obs")
     dev, dt = obs.device, obs.dtype
+    if scan is None:
+        scan = num_tiles(B) < 148 and T >= 4096 and prm.n <= 4
+    if scan:
+        out = kf_rts_scan(obs, prm, B, T, smooth=True, inplace=True, want_ym=want_ym, status=status)
+        return dict(sol=out["smth"], ym=out["ym"], status=out["status"])
     work = alloc_records(B, T, sigma(prm.n), dt, dev)
     sol = work if inplace else torch.empty_like(work)
     ym = alloc_records(B, T, prm.p, dt, dev) if want_ym else None
@@ -332,4 +342,4 @@ def kf_rts_scan(obs, prm: TrackParams, B, T, chunk=0, smooth=True, inplace=True,
     check(fn(_ptr(obs), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), prm.shared_mask, B, T, prm.n,
              prm.p, prm.a_mode, chunk, _ptr(ws), nbytes, _ptr(filt), _ptr(smth), _ptr(ym), _ptr(status), _stream(dev)),
           "eksb_kf_rts_scan")
-    return dict(filt=filt, smth=smth, ym=ym, status=status, chunk=int(lib().eksb_scan_chunk_len(B, T, chunk)))
+    return dict(filt=filt, smth=smth, ym=ym, status=status, chunk=int(lib().eksb_scan_chunk_len(B, T, prm.n, chunk, es)))

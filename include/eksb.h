@@ -208,11 +208,13 @@ EKSB_API int eksb_reduce_rows_f64(const double* in, int rows, long B, double* ou
  * Same inputs and outputs as eksb_kf_forward (first = PRIOR_UPDATE) followed by eksb_rts_backward,
  * computed with an exact chunked scan over time (Sarkka & Garcia-Fernandez elements accumulated per
  * chunk of `chunk` frames, folded per track, every chunk re-run from its exact boundary state), so a
- * handful of very long tracks (config 5: 64 x 10 M frames) still fills the GPU.  chunk <= 0 picks
+ * handful of very long tracks (config 5: 64 x 10 M frames) still fills the GPU.  A chunk whose summary has
+ * forgotten the chunk's boundary state (sensitivity < 1e-22 f64 / 1e-11 f32) writes its remaining records
+ * during the summary pass, so the input is read ~once, not twice (EKSB_SCAN_NO_EARLY=1 switches that off).  chunk <= 0 picks
  * the chunk length (eksb_scan_chunk_len).  workspace: eksb_scan_workspace_bytes(...) bytes.
  * smth may be NULL (filter only) or alias filt (in-place).  State dim n <= 4. */
 EKSB_API size_t eksb_scan_workspace_bytes(long B, long T, int n, long chunk, int elem_size);
-EKSB_API long eksb_scan_chunk_len(long B, long T, long chunk);
+EKSB_API long eksb_scan_chunk_len(long B, long T, int n, long chunk, int elem_size);
 EKSB_API int eksb_kf_rts_scan_f64(const double* obs, const double* m0, const double* S0, const double* C, const double* A,
                          const double* Q, int shared_mask, long B, long T, int n, int p, int a_mode, long chunk,
                          double* workspace, size_t workspace_bytes, double* filt, double* smth, double* ym,

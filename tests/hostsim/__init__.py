@@ -112,8 +112,10 @@ def btd(y, ev, m0, S0, C, A, Q, dtype=np.float64):
     return dict(rc=rc, x=sol[:, :n], Sig=sym_unpack(sol[:, n:], n))
 
 
-def scan(y, ev, m0, S0, C, A, Q, chunk, dtype=np.float64):
-    """Host run of the chunked parallel-in-time phases (summaries, fold, re-run) on one track."""
+def scan(y, ev, m0, S0, C, A, Q, chunk, dtype=np.float64, early=True):
+    """Host run of the chunked parallel-in-time phases (summaries, fold, re-run) on one track.
+    early: the summary pass writes the records itself once it has forgotten the chunk's boundary state
+    (the device default); fcut / bcut in the result are the per-chunk cut positions."""
     T, p = y.shape
     n = m0.shape[0]
     c = lambda a: np.ascontiguousarray(a, dtype=dtype)
@@ -124,8 +126,10 @@ def scan(y, ev, m0, S0, C, A, Q, chunk, dtype=np.float64):
     smth = np.zeros((T, sg), dtype=dtype)
     fn = lib().hs_scan_f64 if dtype == np.float64 else lib().hs_scan_f32
     P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
-    rc = fn(ctypes.c_int(n), ctypes.c_int(p), ctypes.c_int(am), ctypes.c_long(T), ctypes.c_long(chunk), P(y), P(ev),
-            P(m0), P(S0), P(C), P(A), P(Q), P(filt), P(smth))
+    nc = (T + chunk - 1) // chunk
+    cuts = np.zeros(2 * nc, dtype=np.int64)
+    rc = fn(ctypes.c_int(n), ctypes.c_int(p), ctypes.c_int(am), ctypes.c_long(T), ctypes.c_long(chunk),
+            ctypes.c_int(1 if early else 0), P(y), P(ev), P(m0), P(S0), P(C), P(A), P(Q), P(filt), P(smth), P(cuts))
     if rc < 0:
         raise ValueError(f"unsupported dims n={n} p={p}")
-    return dict(rc=rc, mf=filt[:, :n], Vf=sym_unpack(filt[:, n:], n), ms=smth[:, :n], Vs=sym_unpack(smth[:, n:], n))
+    return dict(rc=rc, fcut=cuts[:nc], bcut=cuts[nc:], mf=filt[:, :n], Vf=sym_unpack(filt[:, n:], n), ms=smth[:, :n], Vs=sym_unpack(smth[:, n:], n))

@@ -188,117 +188,104 @@ extern "C" int hs_btd_f32(int n, int p, int am, long Tn, const float* y, const f
 }
 
 // ---- chunked parallel-in-time scan, phases run one after another on the host ----
+// Same chunk programs as the device kernels (scan_fwd_chunk / scan_bwd_chunk, lane stride 1), same
+// hand-over through the cut positions; `early` = 0 switches the early write-out off (full re-run).
+// cuts (optional, 2*nc longs) receives the forward and backward cut of every chunk.
 template <typename T, int N, int P, int AM>
-static int run_scan(long Tn, long L, const T* y, const T* ev, const T* m0, const T* S0, const T* C, const T* A,
-                    const T* Q, T* filt, T* smth) {
-  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
+static int run_scan(long Tn, long L, int early, const T* y, const T* ev, const T* m0, const T* S0, const T* C,
+                    const T* A, const T* Q, T* filt, T* smth, long* cuts) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
   Params<T, N, P, AM> prm;
   load_params<T, N, P, AM>(prm, C, A, Q);
   bool ok = true;
   const long nc = (Tn + L - 1) / L;
+  std::vector<T> obs(Tn * R2);
+  for (long t = 0; t < Tn; ++t)
+    for (int j = 0; j < P; ++j) { obs[t * R2 + j] = y[t * P + j]; obs[t * R2 + P + j] = ev[t * P + j]; }
   std::vector<T> fsum(nc * ScanRec<N>::FWD), finit(nc * SG), bsum(nc * ScanRec<N>::BWD), binit(nc * SG);
-  // F1: forward summaries of chunks 1..nc-1
-  for (long c = 1; c < nc; ++c) {
-    T Phi[N][N], b[N], Cc[NS], eta[N], J[NS];
-    for (int i = 0; i < N; ++i) { b[i] = eta[i] = T(0); for (int j = 0; j < N; ++j) Phi[i][j] = (i == j) ? T(1) : T(0); }
-    for (int i = 0; i < NS; ++i) Cc[i] = J[i] = T(0);
-    for (long t = c * L; t < Tn && t < (c + 1) * L; ++t) {
-      T rec[Rec<N>::FWD];
-      fwd_prep<T, N, P, AM>(prm, y + t * P, ev + t * P, rec);
-      fwd_summary_step<T, N, P, AM>(prm, rec, Phi, b, Cc, eta, J, ok);
-    }
-    T* o = &fsum[c * ScanRec<N>::FWD];
-    for (int i = 0; i < N; ++i) for (int j = 0; j < N; ++j) *o++ = Phi[i][j];
-    for (int i = 0; i < N; ++i) *o++ = b[i];
-    for (int i = 0; i < NS; ++i) *o++ = Cc[i];
-    for (int i = 0; i < N; ++i) *o++ = eta[i];
-    for (int i = 0; i < NS; ++i) *o++ = J[i];
-  }
-  // F3 for chunk 0 (plain filter from the prior), then F2 prefix, then F3 for the rest
-  auto run_fwd = [&](long c, T* m, T* V, bool from_prior) {
-    for (long t = c * L; t < Tn && t < (c + 1) * L; ++t) {
-      T rec[Rec<N>::FWD];
-      fwd_prep<T, N, P, AM>(prm, y + t * P, ev + t * P, rec);
-      fwd_chain<T, N, P, AM>(prm, rec, !(from_prior && t == 0), m, V, ok);
-      for (int i = 0; i < N; ++i) filt[t * SG + i] = m[i];
-      for (int i = 0; i < NS; ++i) filt[t * SG + N + i] = V[i];
-    }
-  };
+  std::vector<long> fcut(nc, 0), bcut(nc, 0);
+  auto len = [&](long c) { return ((c + 1) * L < Tn ? (c + 1) * L : Tn) - c * L; };
+  double nll = 0.0;
+  // F1: chunk 0 from the prior; summaries (+ early write-out) of chunks 1..nc-1
   T m[N], V[NS];
   for (int i = 0; i < N; ++i) m[i] = m0[i];
   load_sym<T, N>(V, S0);
-  run_fwd(0, m, V, true);
+  ok = kf_forward_range<T, N, P, AM, 1, 2, false>(prm, obs.data(), filt, len(0), kPriorUpdate, m, V, nll) && ok;
+  for (long c = 1; c < nc; ++c)
+    fcut[c] = scan_fwd_chunk<T, N, P, AM, 1, 2>(prm, obs.data() + c * L * R2, filt + c * L * SG, len(c), early != 0,
+                                                &fsum[c * ScanRec<N>::FWD], ok);
+  // F2: fold -- skipped (as on the device) when every chunk wrote its own last frame
+  bool f_alive = false;
+  for (long c = 1; c < nc; ++c) f_alive = f_alive || fcut[c] >= len(c);
+  if (f_alive)
+    for (long c = 1; c < nc; ++c) {
+      for (int i = 0; i < N; ++i) finit[c * SG + i] = m[i];
+      for (int i = 0; i < NS; ++i) finit[c * SG + N + i] = V[i];
+      fwd_apply_summary<T, N>(&fsum[c * ScanRec<N>::FWD], m, V, ok);
+    }
+  // F3: re-run of the frames before each chunk's cut, from the last frame of the previous chunk if that
+  // chunk wrote it itself, else from the fold's boundary state
   for (long c = 1; c < nc; ++c) {
-    for (int i = 0; i < N; ++i) finit[c * SG + i] = m[i];
-    for (int i = 0; i < NS; ++i) finit[c * SG + N + i] = V[i];
-    fwd_apply_summary<T, N>(&fsum[c * ScanRec<N>::FWD], m, V, ok);
-  }
-  for (long c = 1; c < nc; ++c) {
+    if (fcut[c] <= 0) continue;
+    const bool prev_final = (c == 1) || fcut[c - 1] < L;
+    const T* src = prev_final ? filt + (c * L - 1) * SG : &finit[c * SG];
     T mm[N], VV[NS];
-    for (int i = 0; i < N; ++i) mm[i] = finit[c * SG + i];
-    for (int i = 0; i < NS; ++i) VV[i] = finit[c * SG + N + i];
-    run_fwd(c, mm, VV, false);
+    for (int i = 0; i < N; ++i) mm[i] = src[i];
+    for (int i = 0; i < NS; ++i) VV[i] = src[N + i];
+    ok = kf_forward_range<T, N, P, AM, 1, 2, false>(prm, obs.data() + c * L * R2, filt + c * L * SG, fcut[c], kContinue,
+                                                    mm, VV, nll) && ok;
   }
-  // B1: backward summaries of chunks 0..nc-2
-  for (long c = 0; c + 1 < nc; ++c) {
-    T acc[ScanRec<N>::BWD];
-    for (int i = 0; i < ScanRec<N>::BWD; ++i) acc[i] = T(0);
-    for (int i = 0; i < N; ++i) acc[i * N + i] = T(1);
-    for (long t = (c + 1) * L - 1; t >= c * L; --t) {
-      T rec[Rec<N>::BWD];
-      bwd_prep<T, N, P, AM>(prm, filt + t * SG, filt + t * SG + N, rec, ok);
-      bwd_summary_step<T, N>(rec, acc);
-    }
-    for (int i = 0; i < ScanRec<N>::BWD; ++i) bsum[c * ScanRec<N>::BWD + i] = acc[i];
-  }
-  auto run_bwd = [&](long c, T* ms, T* Vs, bool terminal) {
-    long hi = (c + 1) * L < Tn ? (c + 1) * L : Tn;
-    for (long t = hi - 1; t >= c * L; --t) {
-      if (terminal && t == Tn - 1) {
-        for (int i = 0; i < N; ++i) ms[i] = filt[t * SG + i];
-        for (int i = 0; i < NS; ++i) Vs[i] = filt[t * SG + N + i];
-      } else {
-        T rec[Rec<N>::BWD];
-        bwd_prep<T, N, P, AM>(prm, filt + t * SG, filt + t * SG + N, rec, ok);
-        bwd_chain<T, N>(rec, ms, Vs);
-      }
-      for (int i = 0; i < N; ++i) smth[t * SG + i] = ms[i];
-      for (int i = 0; i < NS; ++i) smth[t * SG + N + i] = Vs[i];
-    }
-  };
+  // B1: terminal chunk directly; summaries (+ early write-out) of chunks 0..nc-2.  Out of place here
+  // (smth != filt); the in-place aliasing is covered by the GPU tests.
   T ms[N], Vs[NS];
-  run_bwd(nc - 1, ms, Vs, true);
+  ok = rts_backward_range<T, N, P, AM, 1, 2>(prm, filt + (nc - 1) * L * SG, smth + (nc - 1) * L * SG, nullptr, nullptr,
+                                             nullptr, len(nc - 1), true, ms, Vs) && ok;
+  for (long c = 0; c + 1 < nc; ++c)
+    bcut[c] = scan_bwd_chunk<T, N, P, AM, 1, 2>(prm, filt + c * L * SG, smth + c * L * SG, nullptr, L, early != 0,
+                                                &bsum[c * ScanRec<N>::BWD], ok);
+  // B2: fold -- skipped when every chunk smoothed its own first frame
+  bool b_alive = false;
+  for (long c = 0; c + 1 < nc; ++c) b_alive = b_alive || bcut[c] <= 0;
+  if (b_alive)
+    for (long c = nc - 2; c >= 0; --c) {
+      for (int i = 0; i < N; ++i) binit[c * SG + i] = ms[i];
+      for (int i = 0; i < NS; ++i) binit[c * SG + N + i] = Vs[i];
+      bwd_chain<T, N>(&bsum[c * ScanRec<N>::BWD], ms, Vs);
+    }
+  // B3: re-run of the frames from each chunk's cut on
   for (long c = nc - 2; c >= 0; --c) {
-    for (int i = 0; i < N; ++i) binit[c * SG + i] = ms[i];
-    for (int i = 0; i < NS; ++i) binit[c * SG + N + i] = Vs[i];
-    bwd_chain<T, N>(&bsum[c * ScanRec<N>::BWD], ms, Vs);
-  }
-  for (long c = nc - 2; c >= 0; --c) {
+    const bool next_final = (c + 1 == nc - 1) || bcut[c + 1] > 0;
+    const T* src = next_final ? smth + (c + 1) * L * SG : &binit[c * SG];
     T a[N], Bv[NS];
-    for (int i = 0; i < N; ++i) a[i] = binit[c * SG + i];
-    for (int i = 0; i < NS; ++i) Bv[i] = binit[c * SG + N + i];
-    run_bwd(c, a, Bv, false);
+    for (int i = 0; i < N; ++i) a[i] = src[i];
+    for (int i = 0; i < NS; ++i) Bv[i] = src[N + i];
+    const long t0 = c * L + bcut[c];
+    ok = rts_backward_range<T, N, P, AM, 1, 2>(prm, filt + t0 * SG, smth + t0 * SG, nullptr, nullptr, nullptr,
+                                               L - bcut[c], false, a, Bv) && ok;
   }
+  if (cuts)
+    for (long c = 0; c < nc; ++c) { cuts[c] = fcut[c]; cuts[nc + c] = bcut[c]; }
   return ok ? 0 : 1;
 }
 
 template <typename T>
-static int dispatch_scan(int n, int p, int am, long Tn, long L, const T* y, const T* ev, const T* m0, const T* S0,
-                         const T* C, const T* A, const T* Q, T* filt, T* smth) {
+static int dispatch_scan(int n, int p, int am, long Tn, long L, int early, const T* y, const T* ev, const T* m0,
+                         const T* S0, const T* C, const T* A, const T* Q, T* filt, T* smth, long* cuts) {
 #define X(N_, P_)                                                                       \
   if (n == N_ && p == P_)                                                               \
-    return am ? run_scan<T, N_, P_, 1>(Tn, L, y, ev, m0, S0, C, A, Q, filt, smth)       \
-              : run_scan<T, N_, P_, 0>(Tn, L, y, ev, m0, S0, C, A, Q, filt, smth);
+    return am ? run_scan<T, N_, P_, 1>(Tn, L, early, y, ev, m0, S0, C, A, Q, filt, smth, cuts)       \
+              : run_scan<T, N_, P_, 0>(Tn, L, early, y, ev, m0, S0, C, A, Q, filt, smth, cuts);
   EKSB_FOR_EACH_DIM(X)
 #undef X
   return -1;
 }
-extern "C" int hs_scan_f64(int n, int p, int am, long Tn, long L, const double* y, const double* ev, const double* m0,
-                           const double* S0, const double* C, const double* A, const double* Q, double* filt,
-                           double* smth) {
-  return dispatch_scan<double>(n, p, am, Tn, L, y, ev, m0, S0, C, A, Q, filt, smth);
+extern "C" int hs_scan_f64(int n, int p, int am, long Tn, long L, int early, const double* y, const double* ev,
+                           const double* m0, const double* S0, const double* C, const double* A, const double* Q,
+                           double* filt, double* smth, long* cuts) {
+  return dispatch_scan<double>(n, p, am, Tn, L, early, y, ev, m0, S0, C, A, Q, filt, smth, cuts);
 }
-extern "C" int hs_scan_f32(int n, int p, int am, long Tn, long L, const float* y, const float* ev, const float* m0,
-                           const float* S0, const float* C, const float* A, const float* Q, float* filt, float* smth) {
-  return dispatch_scan<float>(n, p, am, Tn, L, y, ev, m0, S0, C, A, Q, filt, smth);
+extern "C" int hs_scan_f32(int n, int p, int am, long Tn, long L, int early, const float* y, const float* ev,
+                           const float* m0, const float* S0, const float* C, const float* A, const float* Q, float* filt,
+                           float* smth, long* cuts) {
+  return dispatch_scan<float>(n, p, am, Tn, L, early, y, ev, m0, S0, C, A, Q, filt, smth, cuts);
 }

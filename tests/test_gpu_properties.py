@@ -56,12 +56,26 @@ def test_block_tridiagonal_solve_equals_filter_plus_rts_at_scale():
     B, T = 2048, 20000
     obs, prm = _batch(B, T, seed=3)
     sm, _ = _smooth(obs, prm, B, T)
-    sol = dev.btd_solve(obs.reshape(-1), prm, B, T)
+    sol = dev.btd_solve(obs.reshape(-1), prm, B, T, scan=False)               # the block-Thomas kernels
     assert int(sol["status"].sum()) == 0
     x = sol["sol"].reshape(-1, T, 9, 32)
     scale = float(sm[:, :, :3].abs().max())
     assert float((x[:, :, :3] - sm[:, :, :3]).abs().max()) < 1e-8 * scale
     assert float((x[:, :, 3:] - sm[:, :, 3:]).abs().max()) < 1e-8 * float(sm[:, :, 3:].abs().max())
+
+
+def test_block_tridiagonal_solve_of_few_long_tracks_goes_parallel_in_time():
+    """Config 5 shape: a handful of long tracks.  btd_solve routes them through the chunked scan; solution and
+    diagonal blocks of H^-1 equal the block-Thomas kernels' (and, by the test above, filter + RTS)."""
+    from eks_b200 import device as dev
+    B, T = 64, 300_000
+    obs, prm = _batch(B, T, seed=8)
+    thomas = dev.btd_solve(obs.reshape(-1), prm, B, T, scan=False)
+    auto = dev.btd_solve(obs.reshape(-1), prm, B, T)
+    assert int(thomas["status"].sum()) == 0 and int(auto["status"].sum()) == 0
+    a, b = auto["sol"].reshape(-1, T, 9, 32), thomas["sol"].reshape(-1, T, 9, 32)
+    for lo, hi in ((0, 3), (3, 9)):
+        assert float((a[:, :, lo:hi] - b[:, :, lo:hi]).abs().max()) < 1e-8 * float(b[:, :, lo:hi].abs().max())
 
 
 def test_scan_equals_sequential_on_long_tracks():
@@ -74,6 +88,47 @@ def test_scan_equals_sequential_on_long_tracks():
     scale = float(sm[:, :, :3].abs().max())
     assert float((sc["smth"].reshape(-1, T, 9, 32)[:, :, :3] - sm[:, :, :3]).abs().max()) < 1e-8 * scale
     assert float((sc["ym"].reshape(-1, T, 4, 32) - ym).abs().max()) < 1e-8 * scale
+
+
+@pytest.mark.parametrize("early", ["1", "0"])
+@pytest.mark.parametrize("dtname,tol", [("float64", 1e-8), ("float32", 2e-3)])
+def test_scan_early_writeout_in_place_equals_sequential(dtname, tol, early, monkeypatch):
+    """Chunks much longer than the filter's memory: the summary kernels write most records themselves
+    (early write-out, smoothing in place over the filtered records) and the re-run kernels only the
+    frames before each cut.  Same records as the sequential kernels, with the switch on and off."""
+    import torch
+    from eks_b200 import device as dev
+    if early == "0":
+        monkeypatch.setenv("EKSB_SCAN_NO_EARLY", "1")
+    B, T = 96, 200_000
+    obs, prm = _batch(B, T, seed=6, dt=getattr(torch, dtname))
+    sm, ym = _smooth(obs, prm, B, T)
+    sc = dev.kf_rts_scan(obs.reshape(-1), prm, B, T, chunk=10_000)
+    assert int(sc["status"].sum()) == 0 and sc["smth"].data_ptr() == sc["filt"].data_ptr()
+    got = sc["smth"].reshape(-1, T, 9, 32)
+    for lo, hi in ((0, 3), (3, 9)):
+        scale = float(sm[:, :, lo:hi].abs().max())
+        assert float((got[:, :, lo:hi] - sm[:, :, lo:hi]).abs().max()) < tol * scale
+    assert float((sc["ym"].reshape(-1, T, 4, 32) - ym).abs().max()) < tol * float(ym.abs().max())
+
+
+def test_scan_mixed_chunks_in_place_equals_sequential():
+    """Some (tile, chunk) pairs never forget their start (a blind stretch of huge ensemble variance in one tile
+    only), so the folds run and those chunks are re-run in full, while their neighbours take their start state
+    from the records the summary kernels wrote.  Same records as the sequential kernels."""
+    from eks_b200 import device as dev
+    B, T, L = 96, 120_000, 10_000
+    obs, prm = _batch(B, T, seed=7)
+    obs[1, 39_000:71_000, 4:] *= 1e12                                  # tile 1: chunks 4..6 are blind
+    sm, ym = _smooth(obs, prm, B, T)
+    sc = dev.kf_rts_scan(obs.reshape(-1), prm, B, T, chunk=L)
+    assert int(sc["status"].sum()) == 0
+    got = sc["smth"].reshape(-1, T, 9, 32)
+    for lo, hi in ((0, 3), (3, 9)):
+        for g in range(3):                                             # per tile: the blind tile has a far larger scale
+            scale = float(sm[g, :, lo:hi].abs().max())
+            assert float((got[g, :, lo:hi] - sm[g, :, lo:hi]).abs().max()) < 1e-8 * scale
+    assert float((sc["ym"].reshape(-1, T, 4, 32) - ym).abs().max()) < 1e-8 * float(ym.abs().max())
 
 
 def test_shard_of_a_large_batch_is_bitwise_identical():

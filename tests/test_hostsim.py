@@ -107,3 +107,60 @@ def test_chunked_scan_equals_sequential(name, chunk, dtype, tol):
     assert r["rc"] == 0
     for k in ("mf", "Vf", "ms", "Vs"):
         assert rel(r[k], c[k]) < tol, k
+
+
+def _long_track(T, q, seed=0, p=4, n=3):
+    rng = np.random.default_rng(seed)
+    C = np.linalg.qr(rng.normal(size=(p, n)))[0]
+    x = np.cumsum(rng.normal(size=(T, n)) * np.sqrt(q), axis=0) + 300.0        # far from 0: the cut must not care
+    ev = np.exp(rng.normal(size=(T, p)) * 0.8 - 1.5)
+    y = x @ C.T + np.sqrt(5 * ev) * rng.normal(size=(T, p))
+    return y, ev, np.zeros(n), np.eye(n), C, np.eye(n), q * np.eye(n)
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-10), (np.float32, 2e-3)])
+def test_scan_early_writeout_equals_sequential(dtype, tol):
+    """K4 early write-out: once a chunk's summary has forgotten the boundary state the summary pass
+    writes the records itself; the result still equals the sequential recursion (and the scan without
+    early write-out), and the cuts show that most of every chunk was written early."""
+    T, L = 12000, 3000
+    args = _long_track(T, 1e-2)
+    seq = hostsim.kf_rts(*args, dtype=dtype, want_cv=False)
+    r1 = hostsim.scan(*args, L, dtype=dtype, early=True)
+    r0 = hostsim.scan(*args, L, dtype=dtype, early=False)
+    assert r1["rc"] == 0 and r0["rc"] == 0
+    for k in ("mf", "Vf", "ms", "Vs"):
+        assert rel(r1[k], seq[k]) < tol, k
+        assert rel(r1[k], r0[k]) < tol, k
+    assert (r0["fcut"][1:] == L).all() and (r0["bcut"] == 0).all()            # nothing written early
+    assert (r1["fcut"][1:] < L // 4).all() and (r1["fcut"][1:] > 0).all()     # re-run covers the warm-up only
+    assert (r1["bcut"][:-1] > 3 * L // 4).all()
+
+
+def test_scan_early_writeout_never_cuts_a_slowly_forgetting_filter():
+    """With a tiny process noise the filter does not forget its start inside a chunk: no early write-out,
+    full re-run, same result as the sequential recursion."""
+    T, L = 6000, 1500
+    args = _long_track(T, 1e-7, seed=1)
+    seq = hostsim.kf_rts(*args, want_cv=False)
+    r = hostsim.scan(*args, L, early=True)
+    assert (r["fcut"][1:] == L).all() and (r["bcut"] == 0).all()
+    for k in ("mf", "Vf", "ms", "Vs"):
+        assert rel(r[k], seq[k]) < 1e-9, k
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 2e-3)])
+def test_scan_mixed_chunks_some_forget_some_do_not(dtype, tol):
+    """A stretch of uninformative frames (huge ensemble variance) keeps some chunks from forgetting their
+    start: those go through the fold and a full re-run, their neighbours start from the records the summary
+    pass wrote.  Still the sequential result."""
+    T, L = 15000, 3000
+    y, ev, m0, S0, C, A, Q = _long_track(T, 1e-2, seed=2)
+    ev = ev.copy(); ev[5900:9100] *= 1e12
+    seq = hostsim.kf_rts(y, ev, m0, S0, C, A, Q, dtype=dtype, want_cv=False)
+    r = hostsim.scan(y, ev, m0, S0, C, A, Q, L, dtype=dtype, early=True)
+    assert r["rc"] == 0
+    assert r["fcut"][2] == L and r["bcut"][2] == 0                       # chunk 2 lies inside the blind stretch
+    assert r["fcut"][4] < L and r["bcut"][0] > 0                         # far from it the early write-out works
+    for k in ("mf", "Vf", "ms", "Vs"):
+        assert rel(r[k], seq[k]) < tol, k

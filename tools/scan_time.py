@@ -31,10 +31,22 @@ def run(dt, B, T, chunk=0, reps=2):
                   f"{tf*(3*p+3*dev.sigma(n))*obs.element_size()/ms*1e-6:7.1f} GB/s algorithmic", flush=True)
         assert int(out["status"].sum()) == 0
         del out
+    if T >= 10_000_000:
+        for r in range(2):
+            e0.record()
+            out = dev.btd_solve(obs, prm, B, T)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            if r:
+                print(f"{str(dt):14s} B={B} T={T} btd_solve (parallel-in-time route) {ms:8.2f} ms -> {B*T/ms*1e-6:7.2f} G tf/s", flush=True)
+            del out
     torch.cuda.empty_cache()
 
 if __name__ == "__main__":
+    big_only = os.environ.get("SCAN_TIME_BIG_ONLY") == "1"
     for dt in (torch.float32, torch.float64):
-        run(dt, 64, 2_000_000)
-        run(dt, 64, 2_000_000, chunk=1024)
+        if not big_only:
+            run(dt, 64, 2_000_000)
+            run(dt, 64, 2_000_000, chunk=1024)
         run(dt, 64, 10_000_000)
