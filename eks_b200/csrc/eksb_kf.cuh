@@ -85,8 +85,17 @@ template <typename T, int N, int P>
 static int launch_forward(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                           long B, long Tn, int a_mode, int first, const T* q_scale, int n_scale, T* filt, double* nll,
                           int* status, cudaStream_t st) {
-  if (filt && !nll && !q_scale && use_pipe(B)) {           // latency-bound regime: warp-specialised kernel
-    int rc = kf_forward_pipe<T>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, N, P, a_mode, first, filt, status, st);
+  if (filt && !nll && !q_scale && use_pipe(B)) {           // warp-specialised kernel, in groups of tiles it handles best
+    const long tiles = num_tiles(B), ng = pipe_groups(tiles, (int)sizeof(T)), per = (tiles + ng - 1) / ng;
+    int rc = EKSB_OK;
+    for (long g0 = 0; g0 < tiles && rc == EKSB_OK; g0 += per) {
+      const long b0 = g0 * kLanes, Bs = (B - b0 < per * kLanes) ? B - b0 : per * kLanes;
+      auto off = [&](const T* ptr, int flag, long stride) { return ptr + ((shared_mask & flag) ? 0 : b0 * stride); };
+      rc = kf_forward_pipe<T>(obs + g0 * Tn * (2 * P) * kLanes, off(m0, EKSB_SHARED_M0, N), off(S0, EKSB_SHARED_S0, N * N),
+                              off(C, EKSB_SHARED_C, P * N), off(A, EKSB_SHARED_A, N * N), off(Q, EKSB_SHARED_Q, N * N),
+                              shared_mask, Bs, Tn, N, P, a_mode, first, filt + g0 * Tn * Dim<N>::SIGMA * kLanes,
+                              status ? status + b0 : nullptr, st);
+    }
     if (rc != EKSB_EDIM) return rc;
   }
   dim3 grid((unsigned)num_tiles(B), (unsigned)(q_scale ? n_scale : 1));
@@ -103,7 +112,17 @@ template <typename T, int N, int P>
 static int launch_backward(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
                            int a_mode, T* smth, T* ym, T* yv, T* cv, int* status, cudaStream_t st) {
   if (!cv && use_pipe(B)) {
-    int rc = rts_backward_pipe<T>(filt, C, A, Q, shared_mask, B, Tn, N, P, a_mode, smth, ym, yv, status, st);
+    const long tiles = num_tiles(B), ng = pipe_groups(tiles, (int)sizeof(T)), per = (tiles + ng - 1) / ng;
+    int rc = EKSB_OK;
+    for (long g0 = 0; g0 < tiles && rc == EKSB_OK; g0 += per) {
+      const long b0 = g0 * kLanes, Bs = (B - b0 < per * kLanes) ? B - b0 : per * kLanes;
+      auto off = [&](const T* ptr, int flag, long stride) { return ptr + ((shared_mask & flag) ? 0 : b0 * stride); };
+      const long rec0 = g0 * Tn * kLanes;
+      rc = rts_backward_pipe<T>(filt + rec0 * Dim<N>::SIGMA, off(C, EKSB_SHARED_C, P * N), off(A, EKSB_SHARED_A, N * N),
+                                off(Q, EKSB_SHARED_Q, N * N), shared_mask, Bs, Tn, N, P, a_mode,
+                                smth + rec0 * Dim<N>::SIGMA, ym ? ym + rec0 * P : nullptr, yv ? yv + rec0 * P : nullptr,
+                                status ? status + b0 : nullptr, st);
+    }
     if (rc != EKSB_EDIM) return rc;
   }
   unsigned grid = (unsigned)num_tiles(B);

@@ -16,15 +16,21 @@ void set_error(const char* fmt, ...) {
 }
 
 bool use_pipe(long B) {
-  static int enabled = -1;
-  static long max_tiles = 0;
-  if (enabled < 0) {
-    const char* e = getenv("EKSB_PIPE");
-    const char* m = getenv("EKSB_PIPE_MAX_TILES");
-    max_tiles = m ? atol(m) : 1536;      // ~10 tiles per SM; beyond that plain occupancy hides latency
-    enabled = (e && e[0] == '0') ? 0 : 1;
-  }
-  return enabled && num_tiles(B) <= max_tiles;
+  const char* e = getenv("EKSB_PIPE");                    // read per call: tests switch kernel families in-process
+  return !(e && e[0] == '0') && B > 0;
+}
+
+long pipe_groups(long tiles, int elem_size) {
+  const char* m = getenv("EKSB_PIPE_MAX_TILES");
+  const char* g = getenv("EKSB_PIPE_GROUP_TILES");
+  // Measured (tools/gpu_groups.sh, 8 000 frames): f64 65 536 tracks 5.78 / 6.30 / 5.90 / 6.27 / 6.41 TB/s algorithmic in
+  // groups of 148 / 256 / 293 / 410 / 512 tiles (plain kernels: 4.72); f32 131 072 tracks 5.72 / 6.21 / 5.85 / 5.56 in
+  // groups of 293 / 512 / 586 / 820 (plain: 4.15).  512 tiles = 128 CTAs of 4 tiles, in both types.
+  (void)elem_size;
+  const long max_single = m ? atol(m) : 592;              // up to 4 tiles on every SM: one launch
+  long group = g ? atol(g) : 512;
+  if (group < 1) group = 1;
+  return tiles <= max_single ? 1 : (tiles + group - 1) / group;
 }
 
 constexpr int kFT = 16;   // frames per transpose tile

@@ -362,6 +362,24 @@ int btd_solve_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* 
   set_error("btd_solve: (n=%d,p=%d) not instantiated (state dim <= 4)", n, p);
   return EKSB_EDIM;
 }
+
+// large batches: groups of tiles, like launch_forward / launch_backward (eksb_kf.cuh)
+template <typename T>
+int btd_solve_grouped(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B,
+                      long Tn, int n, int p, int a_mode, T* work, T* sol, T* ym, int* status, cudaStream_t st) {
+  const long tiles = num_tiles(B), ng = pipe_groups(tiles, (int)sizeof(T)), per = (tiles + ng - 1) / ng;
+  const long sg = n + n * (n + 1) / 2;
+  int rc = EKSB_OK;
+  for (long g0 = 0; g0 < tiles && rc == EKSB_OK; g0 += per) {
+    const long b0 = g0 * kLanes, Bs = (B - b0 < per * kLanes) ? B - b0 : per * kLanes, rec0 = g0 * Tn * kLanes;
+    auto off = [&](const T* ptr, int flag, long stride) { return ptr + ((shared_mask & flag) ? 0 : b0 * stride); };
+    rc = btd_solve_pipe<T>(obs + rec0 * 2 * p, off(m0, EKSB_SHARED_M0, n), off(S0, EKSB_SHARED_S0, n * n),
+                           off(C, EKSB_SHARED_C, p * n), off(A, EKSB_SHARED_A, n * n), off(Q, EKSB_SHARED_Q, n * n),
+                           shared_mask, Bs, Tn, n, p, a_mode, work + rec0 * sg, sol + rec0 * sg,
+                           ym ? ym + rec0 * p : nullptr, status ? status + b0 : nullptr, st);
+  }
+  return rc;
+}
 #endif
 
 }  // namespace eksb

@@ -141,6 +141,48 @@ def test_batched_pipe_and_plain_kernels_vs_oracle(n, p, dtname, tol, a_diag, mon
             assert rel(r["yv"][b], np.einsum("jk,tkl,jl->tj", c["C"][b], Vs, c["C"][b])) < tol, (label, b)
 
 
+@pytest.mark.parametrize("dtname,tol", [("float64", 1e-11), ("float32", 1e-4)])
+def test_large_batches_go_out_as_groups_of_tiles(dtname, tol, monkeypatch):
+    """A batch with more tiles than the pipelined kernels handle at their best is launched as several
+    groups of tiles (eksb_kf.cuh launch_forward / launch_backward).  Forced here on 7 ragged tiles with
+    per-track C: same records as one launch and as the plain kernels, status lands on the right track."""
+    import torch
+    from eks_b200 import device as dev
+    dt = getattr(torch, dtname)
+    B, T, p, n = 200, 150, 4, 3
+    c = _random_batch(B, T, p, n, dt, seed=77)
+
+    def run():
+        filt, _, st = dev.kf_forward(c["obs"], c["prm"], B, T)
+        out = dev.rts_backward(filt, c["prm"], B, T, want_ym=True, want_yv=True)
+        btd = dev.btd_solve(c["obs"], c["prm"], B, T, want_ym=True, scan=False)
+        assert int(btd["status"].sum()) == 0
+        return filt.clone(), out["smth"], out["ym"], out["yv"], st, out["status"], btd["sol"], btd["ym"]
+
+    one = run()
+    monkeypatch.setenv("EKSB_PIPE_MAX_TILES", "2")
+    monkeypatch.setenv("EKSB_PIPE_GROUP_TILES", "3")                   # 7 tiles -> groups of 3, 3, 1
+    grouped = run()
+    monkeypatch.setenv("EKSB_PIPE", "0")
+    plain = run()
+    tol_plain = 1e-9 if dtname == "float64" else 2e-3                  # different arithmetic order (north_star bars 1e-5 / 1e-3)
+    for a, b, e in zip(one[:4], grouped[:4], plain[:4]):
+        scale = float(a.abs().max())
+        assert float((a - b).abs().max()) <= tol * scale
+        assert float((b - e).abs().max()) <= tol_plain * scale
+    for a, b in zip(one[6:], grouped[6:]):                             # block-tridiagonal solve, same grouping
+        assert float((a - b).abs().max()) <= tol * float(a.abs().max())
+    assert float((grouped[6] - grouped[1]).abs().max()) <= tol_plain * float(grouped[1].abs().max())   # == filter + RTS
+    assert int(grouped[4].sum()) == 0 and int(grouped[5].sum()) == 0
+    # a track with a non-positive ensemble variance in the last group reports through its own status slot
+    monkeypatch.setenv("EKSB_PIPE", "1")
+    bad = 197
+    obs = c["obs"].clone().reshape(-1, T, 2 * p, 32)
+    obs[bad // 32, 10, p:, bad % 32] = -1e-6           # det(Id + Lam S) < 0 at that frame
+    _, _, st = dev.kf_forward(obs.reshape(-1), c["prm"], B, T)
+    assert int(st[bad]) == 1 and int(st.sum()) == 1                    # status offset of the last group
+
+
 def test_inplace_smoothing_equals_out_of_place():
     import torch
     from eks_b200 import device as dev
