@@ -15,6 +15,7 @@
 // numpy's linear interpolation formula, evaluated without FMA contraction so the threshold (and
 // with it the mask) is bit-identical to numpy's.
 // Accumulation and the eigen-solve are double precision for both storage types.
+#include <stdlib.h>
 #include "eksb_common.cuh"
 
 namespace eksb {
@@ -38,8 +39,9 @@ inline int moment_slices(long tiles, long Tn) {      // one warp per (tile, slic
   return (int)(s < 1 ? 1 : s);
 }
 template <int P> constexpr int mom_rows() { return 2 + 4 * P + P * (P + 1); }
+constexpr int kCandCap = 1024;    // candidate slots per track after the full-length select passes
 struct SetupWs {                  // workspace layout in 8-byte words
-  size_t thr, state, ghist, part, mx, total;
+  size_t thr, state, ghist, part, cand, flag, mx, total;
 };
 inline SetupWs setup_layout(long B, long Tn, int p, int elem_size) {
   const size_t tiles = (size_t)num_tiles(B);
@@ -47,9 +49,11 @@ inline SetupWs setup_layout(long B, long Tn, int p, int elem_size) {
   SetupWs w;
   w.thr = 0;
   w.state = w.thr + tiles * kLanes;
-  w.ghist = w.state + tiles * 4 * kLanes;
+  w.ghist = w.state + tiles * 6 * kLanes;
   w.part = w.ghist + (size_t)npass * tiles * 256 * kLanes / 2;
-  w.mx = w.part + tiles * (size_t)moment_slices((long)tiles, Tn) * (2 + 4 * p + p * (p + 1)) * kLanes;
+  w.cand = w.part + tiles * (size_t)moment_slices((long)tiles, Tn) * (2 + 4 * p + p * (p + 1)) * kLanes;
+  w.flag = w.cand + (tiles * (size_t)kCandCap * kLanes * elem_size + 7) / 8;
+  w.mx = w.flag + 1;
   w.total = w.mx + (tiles * (size_t)Tn * kLanes * elem_size + 7) / 8;
   return w;
 }
@@ -96,10 +100,18 @@ __host__ __device__ inline void percentile_position(long T, double q, long& lo, 
 //   8 (4) passes : 8-bit digit histogram of the keys that match the prefix selected so far; per-CTA
 //                  shared-memory histogram [256][32 lanes], flushed with one global atomic per non-empty bin
 //   pick kernel  : one warp per tile walks its 256 bins to the digit holding rank k (between passes)
+//   collect      : after 3 (f64) / 2 (f32) passes only a handful of keys per track still match the prefix; they
+//                  are copied to a compact [tile][kCandCap][32] buffer (plus the smallest key above the prefix) and
+//                  the remaining passes and the tail run on that buffer instead of the T-long one -- 5 reads of
+//                  max_vars per track-frame instead of 9.  A track with more than kCandCap matching keys (massive
+//                  ties) raises the overflow flag and every later kernel goes back to the full buffer.
 //   tail kernel  : count(key <= v_lo) and min(key > v_lo)  ->  sorted[lo+1]
 //   thr kernel   : numpy's interpolation
 struct SelState {            // per track, [tile][field][32 lanes] as 64-bit words
-  static constexpr int PREFIX = 0, RANK = 1, CNT_LE = 2, NEXT = 3, WORDS = 4;
+  static constexpr int PREFIX = 0, RANK = 1, CNT_LE = 2, NEXT = 3, NCAND = 4, RANK_C = 5, WORDS = 6;
+  // NEXT: min(key > v_lo); the collect kernel seeds it with the smallest key above the candidates' prefix, the
+  // tail kernel lowers it to the smallest candidate above v_lo if there is one.  NCAND: candidates appended.
+  // RANK_C: rank of the wanted key among the candidates at the time they were collected.
 };
 
 template <typename T, int P>
@@ -113,7 +125,8 @@ setup_mx_kernel(const T* __restrict__ obs, long tiles, long Tn, T* __restrict__ 
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-setup_hist_kernel(const T* __restrict__ mx, long Tn, int slices, int shift, const unsigned long long* __restrict__ state,
+setup_hist_kernel(const T* __restrict__ mx, long Tn, const T* __restrict__ cand, const int* __restrict__ overflow,
+                  int slices, int shift, const unsigned long long* __restrict__ state,
                   unsigned int* __restrict__ ghist /* [tile][256][32], this pass */) {
   using K = KeyOf<T>;
   using Key = typename K::type;
@@ -121,15 +134,19 @@ setup_hist_kernel(const T* __restrict__ mx, long Tn, int slices, int shift, cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long g = blockIdx.x / slices;
   const int sl = (int)(blockIdx.x - g * slices);
+  const bool use_c = cand && *overflow == 0;               // candidates collected: the short buffer holds every match
+  const long n = use_c ? kCandCap : Tn;
+  const long len = (n + slices - 1) / slices;
+  const long t0 = sl * len, t1 = (t0 + len < n) ? t0 + len : n;
+  if (t0 >= t1) return;
   for (int i = threadIdx.x; i < 256 * kLanes; i += blockDim.x) (&hist[0][0])[i] = 0;
   __syncthreads();
   const Key prefix = (Key)state[(g * SelState::WORDS + SelState::PREFIX) * kLanes + lane];
   const bool top = (shift == K::kBits - 8);
-  const long len = (Tn + slices - 1) / slices;
-  const long t0 = sl * len, t1 = (t0 + len < Tn) ? t0 + len : Tn;
-  const T* base = mx + g * Tn * kLanes + lane;
+  const T* base = (use_c ? cand + g * kCandCap * kLanes : mx + g * Tn * kLanes) + lane;
   for (long t = t0 + warp; t < t1; t += 8) {
     const Key key = K::of(base[t * kLanes]);
+    if (use_c && key == (Key) ~(Key)0) continue;          // empty candidate slot
     if (top || (key >> ((shift + 8) & (K::kBits - 1))) == (prefix >> ((shift + 8) & (K::kBits - 1))))
       atomicAdd(&hist[(unsigned)(key >> shift) & 255u][lane], 1u);
   }
@@ -162,7 +179,8 @@ setup_pick_kernel(const unsigned int* __restrict__ ghist, int shift, unsigned lo
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-setup_tail_kernel(const T* __restrict__ mx, long Tn, int slices, unsigned long long* __restrict__ state) {
+setup_tail_kernel(const T* __restrict__ mx, long Tn, const T* __restrict__ cand, const int* __restrict__ overflow,
+                  int slices, unsigned long long* __restrict__ state) {
   using K = KeyOf<T>;
   using Key = typename K::type;
   __shared__ unsigned int s_cnt[kLanes];
@@ -170,17 +188,21 @@ setup_tail_kernel(const T* __restrict__ mx, long Tn, int slices, unsigned long l
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long g = blockIdx.x / slices;
   const int sl = (int)(blockIdx.x - g * slices);
+  const bool use_c = cand && *overflow == 0;
+  const long n = use_c ? kCandCap : Tn;
+  const long len = (n + slices - 1) / slices;
+  const long t0 = sl * len, t1 = (t0 + len < n) ? t0 + len : n;
+  if (t0 >= t1) return;
   if (warp == 0) { s_cnt[lane] = 0; s_next[lane] = ~0ull; }
   __syncthreads();
   unsigned long long* st = state + g * SelState::WORDS * kLanes + lane;
   const Key klo = (Key)st[SelState::PREFIX * kLanes];
-  const long len = (Tn + slices - 1) / slices;
-  const long t0 = sl * len, t1 = (t0 + len < Tn) ? t0 + len : Tn;
-  const T* base = mx + g * Tn * kLanes + lane;
+  const T* base = (use_c ? cand + g * kCandCap * kLanes : mx + g * Tn * kLanes) + lane;
   unsigned cnt = 0;
   unsigned long long nxt = ~0ull;
   for (long t = t0 + warp; t < t1; t += 8) {
     const Key key = K::of(base[t * kLanes]);
+    if (use_c && key == (Key) ~(Key)0) continue;          // empty candidate slot
     if (key <= klo) ++cnt;
     else if ((unsigned long long)key < nxt) nxt = key;
   }
@@ -193,6 +215,45 @@ setup_tail_kernel(const T* __restrict__ mx, long Tn, int slices, unsigned long l
   }
 }
 
+// Copy the keys that still match the selected prefix (bits >= low_bit) to the compact candidate buffer and
+// find the smallest key above that prefix (it is sorted[lo+1] when the rank-lo key is the largest candidate).
+template <typename T>
+__global__ void __launch_bounds__(256)
+setup_collect_kernel(const T* __restrict__ mx, long Tn, int slices, int low_bit, unsigned long long* __restrict__ state,
+                     T* __restrict__ cand, int* __restrict__ overflow) {
+  using K = KeyOf<T>;
+  using Key = typename K::type;
+  __shared__ unsigned long long s_above[kLanes];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long g = blockIdx.x / slices;
+  const int sl = (int)(blockIdx.x - g * slices);
+  if (warp == 0) s_above[lane] = ~0ull;
+  __syncthreads();
+  unsigned long long* st = state + g * SelState::WORDS * kLanes + lane;
+  const Key pp = (Key)st[SelState::PREFIX * kLanes] >> low_bit;
+  if (sl == 0 && warp == 0) st[SelState::RANK_C * kLanes] = st[SelState::RANK * kLanes];
+  const long len = (Tn + slices - 1) / slices;
+  const long t0 = sl * len, t1 = (t0 + len < Tn) ? t0 + len : Tn;
+  const T* base = mx + g * Tn * kLanes + lane;
+  T* out = cand + g * kCandCap * kLanes + lane;
+  unsigned long long above = ~0ull;
+  for (long t = t0 + warp; t < t1; t += 8) {
+    const T v = base[t * kLanes];
+    const Key key = K::of(v);
+    const Key kp = key >> low_bit;
+    if (kp == pp) {
+      const unsigned long long idx = atomicAdd(&st[SelState::NCAND * kLanes], 1ull);
+      if (idx < (unsigned long long)kCandCap) out[idx * kLanes] = v;
+      else atomicExch(overflow, 1);
+    } else if (kp > pp && (unsigned long long)key < above) {
+      above = key;
+    }
+  }
+  if (above != ~0ull) atomicMin(&s_above[lane], above);
+  __syncthreads();
+  if (warp == 0 && s_above[lane] != ~0ull) atomicMin(&st[SelState::NEXT * kLanes], s_above[lane]);
+}
+
 __global__ void setup_init_state_kernel(unsigned long long* __restrict__ state, long lo) {
   unsigned long long* st = state + (long)blockIdx.x * SelState::WORDS * kLanes + threadIdx.x;
   st[SelState::RANK * kLanes] = (unsigned long long)lo;
@@ -200,8 +261,8 @@ __global__ void setup_init_state_kernel(unsigned long long* __restrict__ state, 
 }
 
 template <typename T>
-__global__ void setup_thr_kernel(const unsigned long long* __restrict__ state, long B, long Tn, double q,
-                                 double* __restrict__ thr) {
+__global__ void setup_thr_kernel(const unsigned long long* __restrict__ state, const int* __restrict__ overflow,
+                                 int collected, long B, long Tn, double q, double* __restrict__ thr) {
   using K = KeyOf<T>;
   using Key = typename K::type;
   const long b = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -213,7 +274,9 @@ __global__ void setup_thr_kernel(const unsigned long long* __restrict__ state, l
   double gamma;
   percentile_position(Tn, q, lo, gamma);
   const double a = (double)K::back((Key)st[SelState::PREFIX * kLanes]);
-  const bool same = (long)st[SelState::CNT_LE * kLanes] >= lo + 2 || lo + 1 >= Tn || st[SelState::NEXT * kLanes] == ~0ull;
+  // with candidates, CNT_LE counts inside the candidate buffer and the rank to compare with is the rank among them
+  const long need = (collected && *overflow == 0) ? (long)st[SelState::RANK_C * kLanes] + 2 : lo + 2;
+  const bool same = (long)st[SelState::CNT_LE * kLanes] >= need || lo + 1 >= Tn || st[SelState::NEXT * kLanes] == ~0ull;
   const double b2 = same ? a : (double)K::back((Key)st[SelState::NEXT * kLanes]);
   const double diff = __dsub_rn(b2, a);
   double v = __dadd_rn(a, __dmul_rn(diff, gamma));
@@ -233,8 +296,8 @@ template <int P> struct MomRows {
 
 template <typename T, int P>
 __global__ void __launch_bounds__(kMomWarpsPerCta* kLanes)
-setup_moments_kernel(const T* __restrict__ obs, long B, long Tn, int slices, const double* __restrict__ thr,
-                     double* __restrict__ part) {
+setup_moments_kernel(const T* __restrict__ obs, const T* __restrict__ mx, long B, long Tn, int slices,
+                     const double* __restrict__ thr, double* __restrict__ part) {
   using MR = MomRows<P>;
   constexpr int PS = MR::PS;
   const int lane = threadIdx.x & 31;
@@ -245,6 +308,7 @@ setup_moments_kernel(const T* __restrict__ obs, long B, long Tn, int slices, con
   const long b = g * kLanes + lane;
   const double th = thr[b < B ? b : B - 1];
   const T* base = obs + (g * Tn * (2 * P)) * kLanes + lane;
+  const T* mxb = mx + g * Tn * kLanes + lane;          // max_vars from the select passes: 1 row instead of the P variance rows
   const long len = (Tn + slices - 1) / slices;
   const long t0 = sl * len, t1 = (t0 + len < Tn) ? t0 + len : Tn;
   double sh[P], sy[P], syy[PS], sd[P], sdd[PS], first[P], last[P];
@@ -254,23 +318,21 @@ setup_moments_kernel(const T* __restrict__ obs, long B, long Tn, int slices, con
 #pragma unroll
   for (int j = 0; j < PS; ++j) syy[j] = sdd[j] = 0;
   bool have = false;
-  constexpr int kUn = 4;                       // frames whose records are loaded before any is processed
+  constexpr int kUn = P <= 4 ? 8 : 4;          // frames whose records are loaded before any is processed (registers)
   for (long tb = t0; tb < t1; tb += kUn) {
-    T raw[kUn][2 * P];
+    T raw[kUn][P], mxv[kUn];
 #pragma unroll
     for (int f = 0; f < kUn; ++f)
       if (tb + f < t1) {
         const T* r = base + (tb + f) * (2 * P) * kLanes;
+        mxv[f] = mxb[(tb + f) * kLanes];
 #pragma unroll
-        for (int j = 0; j < 2 * P; ++j) raw[f][j] = r[j * kLanes];
+        for (int j = 0; j < P; ++j) raw[f][j] = r[j * kLanes];
       }
 #pragma unroll
     for (int f = 0; f < kUn; ++f) {
       if (tb + f >= t1) break;
-      T mxv = raw[f][P];
-#pragma unroll
-      for (int j = 1; j < P; ++j) mxv = raw[f][P + j] > mxv ? raw[f][P + j] : mxv;
-      if ((double)(mxv + T(0)) <= th) {
+      if ((double)mxv[f] <= th) {
         double y[P];
 #pragma unroll
         for (int j = 0; j < P; ++j) y[j] = (double)raw[f][j];
@@ -505,26 +567,37 @@ static int setup_run(T* obs, long B, long Tn, int n, double q, double s, int cen
   unsigned int* ghist = reinterpret_cast<unsigned int*>(ws + L.ghist);
   double* part = ws + L.part;
   T* mx = reinterpret_cast<T*>(ws + L.mx);
+  T* cand = reinterpret_cast<T*>(ws + L.cand);
+  int* overflow = reinterpret_cast<int*>(ws + L.flag);
   const int npass = (int)sizeof(Key), ssl = select_slices(tiles, Tn), msl = moment_slices(tiles, Tn);
+  // full-length passes before the candidates are collected (EKSB_SETUP_NO_COLLECT=1: never, every pass full length)
+  const char* nc = getenv("EKSB_SETUP_NO_COLLECT");
+  const int collect_after = (nc && nc[0] == '1') ? npass : (sizeof(T) == 8 ? 3 : 2);
   // state: prefix 0, rank = lo, cnt_le 0, next = ~0 ; histograms 0
   long lo;
   double gamma;
   percentile_position(Tn, q, lo, gamma);
   cudaMemsetAsync(ghist, 0, (size_t)npass * tiles * 256 * kLanes * sizeof(unsigned int), st);
   cudaMemsetAsync(state, 0, (size_t)tiles * SelState::WORDS * kLanes * 8, st);
+  cudaMemsetAsync(overflow, 0, 8, st);
+  const bool collect = collect_after < npass;
+  if (collect) cudaMemsetAsync(cand, 0xFF, (size_t)tiles * kCandCap * kLanes * sizeof(T), st);   // all-ones key = empty slot
   setup_init_state_kernel<<<(unsigned)tiles, kLanes, 0, st>>>(state, lo);
   setup_mx_kernel<T, P><<<(unsigned)((tiles * Tn + 7) / 8), 256, 0, st>>>(obs, tiles, Tn, mx);
   for (int pass = 0; pass < npass; ++pass) {
     const int shift = 8 * (npass - 1 - pass);
     unsigned int* gh = ghist + (size_t)pass * tiles * 256 * kLanes;
-    setup_hist_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, ssl, shift, state, gh);
+    if (pass == collect_after)
+      setup_collect_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, ssl, shift + 8, state, cand, overflow);
+    setup_hist_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, pass >= collect_after ? cand : nullptr, overflow,
+                                                                  ssl, shift, state, gh);
     setup_pick_kernel<T><<<(unsigned)tiles, kLanes, 0, st>>>(gh, shift, state);
   }
-  setup_tail_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, ssl, state);
-  setup_thr_kernel<T><<<(unsigned)((B + 127) / 128), 128, 0, st>>>(state, B, Tn, q, thr);
+  setup_tail_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, collect ? cand : nullptr, overflow, ssl, state);
+  setup_thr_kernel<T><<<(unsigned)((B + 127) / 128), 128, 0, st>>>(state, overflow, collect ? 1 : 0, B, Tn, q, thr);
   const long warps = tiles * msl;
   setup_moments_kernel<T, P><<<(unsigned)((warps + kMomWarpsPerCta - 1) / kMomWarpsPerCta), kMomWarpsPerCta * kLanes, 0, st>>>(
-      obs, B, Tn, msl, thr, part);
+      obs, mx, B, Tn, msl, thr, part);
   setup_finalize_kernel<T, P, 3><<<(unsigned)((B + 63) / 64), 64, 0, st>>>(obs, part, B, Tn, msl, s, means, C, S0, Q, status);
   if (center) {
     const long warps_c = tiles * ((Tn + kCenterFrames - 1) / kCenterFrames);

@@ -111,6 +111,43 @@ def test_device_parameter_setup_matches_oracle(B, T, p, q):
         np.testing.assert_allclose(prm.Q[b].cpu().numpy(), Qw, rtol=1e-7, atol=1e-9 * np.abs(Qw).max())
 
 
+@pytest.mark.parametrize("dtname,rtol", [("float64", 1e-10), ("float32", 2e-5)])
+@pytest.mark.parametrize("ties", [False, True])
+def test_percentile_select_candidate_buffer_and_overflow_fallback(dtname, rtol, ties, monkeypatch):
+    """The exact percentile is a radix select; after the first full-length passes the few keys still matching the
+    prefix are collected into a short buffer and the remaining passes run on it.  Same parameters, bit for bit,
+    as with every pass at full length (EKSB_SETUP_NO_COLLECT=1), also when thousands of tied keys overflow the
+    buffer and the kernels fall back to the full-length passes; good-frame means equal the numpy percentile mask."""
+    import torch
+    from eks_b200 import device as dev
+    from oracle import restated_smoothers as osm
+    dt = getattr(torch, dtname)
+    B, T, p = 40, 6000, 4
+    rng = np.random.default_rng(11 + ties)
+    y = np.cumsum(rng.normal(size=(B, T, p)) * 0.3, axis=1) + rng.uniform(50, 400, size=(B, 1, p))
+    ev = np.exp(rng.normal(np.log(0.05), 1.6, size=(B, T, p)))
+    if ties:                                                          # 3 distinct max_vars, ~2000 copies of each
+        ev = np.array([0.01, 0.1, 1.0])[rng.integers(0, 3, size=(B, T, 1))] * np.ones(p)
+    d = torch.device("cuda", 0)
+    yt, evt = torch.as_tensor(y, dtype=dt), torch.as_tensor(ev, dtype=dt)
+    obs = dev.pack_obs(yt.to(d), evt.to(d))
+    for q in (25, 60):
+        res = {}
+        for mode in ("collect", "full"):
+            if mode == "full":
+                monkeypatch.setenv("EKSB_SETUP_NO_COLLECT", "1")
+            else:
+                monkeypatch.delenv("EKSB_SETUP_NO_COLLECT", raising=False)
+            prm, means, status = dev.pca_setup(obs.clone(), B, T, p, q, 0.01, center=False)
+            assert int(status.sum()) == 0
+            res[mode] = (means, prm.C, prm.S0, prm.Q)
+        for a, b in zip(res["collect"], res["full"]):
+            assert torch.equal(a, b)
+        for b in (0, 17, B - 1):
+            good = osm.good_frame_mask(evt[b].double().numpy(), q)
+            np.testing.assert_allclose(res["collect"][0][b].cpu().double().numpy(), yt[b].double().numpy()[good].mean(axis=0), rtol=rtol)
+
+
 def test_session_entry_equals_per_keypoint_calls():
     """All mirror-mouse keypoints in one batched session call == the per-keypoint drop-in == shipped CSVs."""
     from eks_b200.multiview_pca_smoother import smooth_session_multi_cam, session_dfs
