@@ -1249,9 +1249,24 @@ template <> struct ScanCut<float> { static constexpr float value = 1e-11f; };
 // Forward summary of one chunk of `n` frames.  obs / filt point at the chunk's first frame.
 // sum (ScanRec<N>::FWD values, local) receives the element.  Returns the cut k: frames [k, n) of the
 // chunk have been written to filt (k == n: nothing written, the whole chunk must be re-run).
-template <typename T, int N, int P, int AM, int LS, int PF>
+// Tail = the ordinary filter over the rest of the chunk: bool tail(prm, obs, filt_or_null, n, m, V).  The default
+// is kf_forward_range with a register prefetch (host tests, re-run kernels); the summary kernels pass a variant that
+// stages the frames through shared memory (eksb_scan.cuh FwdTailRing) -- same arithmetic.
+template <typename T, int N, int P, int AM, int LS, int PF> struct FwdTailPlain {
+  EKSB_HD bool operator()(const Params<T, N, P, AM>& prm, const T* obs, T* filt, long n, T* m, T* V) const {
+    double acc = 0.0;
+    return kf_forward_range<T, N, P, AM, LS, PF, false>(prm, obs, filt, n, kContinue, m, V, acc);
+  }
+};
+template <typename T, int N, int P, int AM, int LS, int PF> struct BwdTailPlain {
+  EKSB_HD bool operator()(const Params<T, N, P, AM>& prm, const T* filt, T* smth, T* ym, long n, T* ms, T* Vs) const {
+    return rts_backward_range<T, N, P, AM, LS, PF>(prm, filt, smth, ym, nullptr, nullptr, n, false, ms, Vs);
+  }
+};
+
+template <typename T, int N, int P, int AM, int LS, typename Tail>
 EKSB_HD long scan_fwd_chunk(const Params<T, N, P, AM>& prm, const T* __restrict__ obs, T* __restrict__ filt, long n,
-                            bool early_out, T* sum, bool& ok) {
+                            bool early_out, T* sum, bool& ok, const Tail& tail) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
   T Phi[N][N], bb[N], Cc[NS], eta[N], J[NS];
   EKSB_UNROLL
@@ -1296,9 +1311,7 @@ EKSB_HD long scan_fwd_chunk(const Params<T, N, P, AM>& prm, const T* __restrict_
     }
     if (t < n) {
       if (early_out) cut = t;
-      double acc = 0.0;
-      ok = kf_forward_range<T, N, P, AM, LS, PF, false>(prm, obs + t * R2 * LS, early_out ? filt + t * SG * LS : nullptr,
-                                                        n - t, kContinue, bb, Cc, acc) && ok;
+      ok = tail(prm, obs + t * R2 * LS, early_out ? filt + t * SG * LS : nullptr, n - t, bb, Cc) && ok;
     }
   }
   EKSB_UNROLL
@@ -1321,9 +1334,9 @@ EKSB_HD long scan_fwd_chunk(const Params<T, N, P, AM>& prm, const T* __restrict_
 // >= the returned cut are left untouched for the re-run).  acc (ScanRec<N>::BWD values, local) receives
 // (E, L, g).  Returns the cut k: frames [0, k) of the chunk have been smoothed and written (k == 0:
 // nothing written).
-template <typename T, int N, int P, int AM, int LS, int PF>
+template <typename T, int N, int P, int AM, int LS, typename Tail>
 EKSB_HD long scan_bwd_chunk(const Params<T, N, P, AM>& prm, const T* filt, T* smth, T* ym, long n, bool early_out,
-                            T* acc, bool& ok) {
+                            T* acc, bool& ok, const Tail& tail) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
   EKSB_UNROLL
   for (int i = 0; i < SR; ++i) acc[i] = T(0);
@@ -1357,8 +1370,7 @@ EKSB_HD long scan_bwd_chunk(const Params<T, N, P, AM>& prm, const T* filt, T* sm
     cut = t + 1;
     EKSB_UNROLL
     for (int i = 0; i < N * N; ++i) acc[i] = T(0);
-    ok = rts_backward_range<T, N, P, AM, LS, PF>(prm, filt, smth, ym, nullptr, nullptr, cut, false, acc + N * N + NS,
-                                                 acc + N * N) && ok;
+    ok = tail(prm, filt, smth, ym, cut, acc + N * N + NS, acc + N * N) && ok;
   }
   return cut;
 }

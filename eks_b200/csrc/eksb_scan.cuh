@@ -21,6 +21,142 @@ namespace eksb {
 
 constexpr int kScanWarps = 4;   // warps (= chunks) per CTA
 
+// ---- per-lane shared-memory frame ring (device only) ----------------------------------------------
+// A register prefetch ring cannot keep more than ~2 frames of loads in flight per warp (scoreboard
+// slots, see eksb_pipe.cuh), and with 12 resident warps per SM that is too few bytes in flight to
+// saturate HBM.  Here every lane copies ITS OWN column of the next kRingDepth frames global -> shared
+// with cp.async (LDGSTS: no register, no scoreboard), and reads it back after cp.async.wait_group:
+// a lane only ever consumes what it copied itself, so no barrier of any kind is needed.
+// Ring layout per warp: [slot][row][32 lanes]; `ring` points at this lane's column.
+constexpr int kRingDepth = 6;
+
+template <typename T> __device__ __forceinline__ void cp_async_elem(T* dst_smem, const T* src) {
+  static_assert(sizeof(T) == 4 || sizeof(T) == 8, "element size");
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+  if (sizeof(T) == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(src) : "memory");
+  else                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int NPENDING> __device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(NPENDING) : "memory");
+}
+template <typename T, int ROWS> __device__ __forceinline__ void ring_issue(T* ring, int slot, const T* frame) {
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) cp_async_elem(ring + (slot * ROWS + r) * kLanes, frame + r * kLanes);
+}
+template <typename T, int ROWS> __host__ __device__ constexpr size_t ring_bytes_per_warp() { return (size_t)kRingDepth * ROWS * kLanes * sizeof(T); }
+
+// kf_forward_range (eksb_math.cuh) with the obs frames staged through the ring; same arithmetic.
+template <typename T, int N, int P, int AM>
+__device__ bool kf_forward_range_ring(const Params<T, N, P, AM>& prm, const T* __restrict__ obs, T* __restrict__ filt,
+                                      long n, int first, T* m, T* V, T* ring) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, D = kRingDepth;
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    if (k < n) ring_issue<T, R2>(ring, k, obs + (long)k * R2 * kLanes);
+    cp_async_commit();
+  }
+  int slot = 0;
+  for (long t = 0; t < n; ++t) {
+    cp_async_wait<D - 1>();
+    T cur[R2];
+#pragma unroll
+    for (int r = 0; r < R2; ++r) cur[r] = ring[(slot * R2 + r) * kLanes];
+    if (t + D < n) ring_issue<T, R2>(ring, slot, obs + (t + D) * R2 * kLanes);
+    cp_async_commit();
+    slot = (slot + 1 == D) ? 0 : slot + 1;
+    const bool is_first = (t == 0);
+    if (!(is_first && first == kPriorOnly)) {
+      T mp[N], S[NS];
+      if (is_first && first == kPriorUpdate) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) mp[i] = m[i];
+#pragma unroll
+        for (int i = 0; i < NS; ++i) S[i] = V[i];
+      } else {
+        predict<T, N, P, AM>(prm, m, V, mp, S);
+      }
+      update<T, N, P, AM, false>(prm, cur, cur + P, mp, S, m, V, ok);
+    }
+    if (filt) {
+      T* o = filt + t * SG * kLanes;
+#pragma unroll
+      for (int i = 0; i < N; ++i) o[i * kLanes] = m[i];
+#pragma unroll
+      for (int i = 0; i < NS; ++i) o[(N + i) * kLanes] = V[i];
+    }
+  }
+  cp_async_wait<0>();
+  return ok;
+}
+
+// rts_backward_range (eksb_math.cuh; no yv / cv outputs) with the filtered records staged through the ring.
+// smth may alias filt: frame t is copied to shared memory before the loop reaches (and overwrites) it.
+template <typename T, int N, int P, int AM>
+__device__ bool rts_backward_range_ring(const Params<T, N, P, AM>& prm, const T* filt, T* smth, T* ym, long n,
+                                        bool terminal, T* ms, T* Vs, T* ring) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, D = kRingDepth;
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    if (n - 1 - k >= 0) ring_issue<T, SG>(ring, k, filt + (n - 1 - k) * SG * kLanes);
+    cp_async_commit();
+  }
+  int slot = 0;
+  for (long t = n - 1; t >= 0; --t) {
+    cp_async_wait<D - 1>();
+    T cur[SG];
+#pragma unroll
+    for (int r = 0; r < SG; ++r) cur[r] = ring[(slot * SG + r) * kLanes];
+    if (t - D >= 0) ring_issue<T, SG>(ring, slot, filt + (t - D) * SG * kLanes);
+    cp_async_commit();
+    slot = (slot + 1 == D) ? 0 : slot + 1;
+    if (terminal && t == n - 1) {
+#pragma unroll
+      for (int i = 0; i < N; ++i) ms[i] = cur[i];
+#pragma unroll
+      for (int i = 0; i < NS; ++i) Vs[i] = cur[N + i];
+    } else {
+      T ms1[N], Vs1[NS];
+#pragma unroll
+      for (int i = 0; i < N; ++i) ms1[i] = ms[i];
+#pragma unroll
+      for (int i = 0; i < NS; ++i) Vs1[i] = Vs[i];
+      rts_step<T, N, P, AM>(prm, cur, cur + N, ms1, Vs1, ms, Vs, nullptr, ok);
+    }
+    T* o = smth + t * SG * kLanes;
+#pragma unroll
+    for (int i = 0; i < N; ++i) o[i * kLanes] = ms[i];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) o[(N + i) * kLanes] = Vs[i];
+    if (ym) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) {
+        T sacc = T(0);
+#pragma unroll
+        for (int i = 0; i < N; ++i) sacc += prm.C[j][i] * ms[i];
+        ym[(t * P + j) * kLanes] = sacc;
+      }
+    }
+  }
+  cp_async_wait<0>();
+  return ok;
+}
+
+template <typename T, int N, int P, int AM> struct FwdTailRing {
+  T* ring;
+  __device__ bool operator()(const Params<T, N, P, AM>& prm, const T* obs, T* filt, long n, T* m, T* V) const {
+    return kf_forward_range_ring<T, N, P, AM>(prm, obs, filt, n, kContinue, m, V, ring);
+  }
+};
+template <typename T, int N, int P, int AM> struct BwdTailRing {
+  T* ring;
+  __device__ bool operator()(const Params<T, N, P, AM>& prm, const T* filt, T* smth, T* ym, long n, T* ms, T* Vs) const {
+    return rts_backward_range_ring<T, N, P, AM>(prm, filt, smth, ym, n, false, ms, Vs, ring);
+  }
+};
+
 // ---- 1a. forward chunk summaries, chunks [1, nc), plus the sequential run of chunk 0 -----------------
 // Work items [0, tiles): chunk 0 of each tile, run as the ordinary filter from the prior (it needs no
 // summary, only its end state, and would otherwise be a serial 1-warp-per-tile launch of its own).
@@ -29,15 +165,18 @@ constexpr int kScanWarps = 4;   // warps (= chunks) per CTA
 // forgets its start exponentially), J and eta have stopped changing and Phi is numerically zero, so the
 // rest of the chunk is the plain filter (2.4x cheaper) whose records are final and written at once;
 // fcut[g*nc+c] = number of leading frames of the chunk that still need the re-run.
+// three CTAs (12 warps) per SM for state dim <= 3, as the chunk policy assumes (eksb_scan_impl.cuh scan_auto_chunk)
 template <typename T, int N, int P, int AM>
-__global__ void __launch_bounds__(kScanWarps* kLanes)
+__global__ void __launch_bounds__(kScanWarps* kLanes, N <= 3 ? 3 : 1)
 scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                         const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
                         long B, long Tn, long L, long nc, int early_out, T* __restrict__ fsum,
                         long* __restrict__ fcut, int* __restrict__ alive, T* __restrict__ filt,
                         int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, SR = ScanRec<N>::FWD;
+  extern __shared__ __align__(16) unsigned char scan_smem[];
   const int lane = threadIdx.x & 31;
+  T* ring = reinterpret_cast<T*>(scan_smem + (threadIdx.x >> 5) * ring_bytes_per_warp<T, R2>()) + lane;
   const long tiles = num_tiles_dev(B);
   const long w = (long)blockIdx.x * kScanWarps + (threadIdx.x >> 5);
   if (w >= tiles * nc) return;
@@ -53,10 +192,8 @@ scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
     for (int i = 0; i < N; ++i) m[i] = pm[i];
     load_sym<T, N>(V, ps);
     const long t1 = L < Tn ? L : Tn;
-    double acc = 0.0;
-    const bool ok0 = kf_forward_range<T, N, P, AM, kLanes, 2, false>(prm, obs + (g * Tn * R2) * kLanes + lane,
-                                                                    filt + (g * Tn * SG) * kLanes + lane, t1,
-                                                                    kPriorUpdate, m, V, acc);
+    const bool ok0 = kf_forward_range_ring<T, N, P, AM>(prm, obs + (g * Tn * R2) * kLanes + lane,
+                                                        filt + (g * Tn * SG) * kLanes + lane, t1, kPriorUpdate, m, V, ring);
     if (b < B && status && !ok0) status[b] = 1;
     return;
   }
@@ -68,9 +205,9 @@ scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
   bool ok = true;
   const long t0 = c * L, t1 = (c + 1) * L < Tn ? (c + 1) * L : Tn;
   T sum[SR];
-  const long cut = scan_fwd_chunk<T, N, P, AM, kLanes, 2>(prm, obs + ((g * Tn + t0) * R2) * kLanes + lane,
-                                                          filt + ((g * Tn + t0) * SG) * kLanes + lane, t1 - t0,
-                                                          early_out != 0, sum, ok);
+  const long cut = scan_fwd_chunk<T, N, P, AM, kLanes>(prm, obs + ((g * Tn + t0) * R2) * kLanes + lane,
+                                                       filt + ((g * Tn + t0) * SG) * kLanes + lane, t1 - t0,
+                                                       early_out != 0, sum, ok, FwdTailRing<T, N, P, AM>{ring});
   if (lane == 0) {
     fcut[g * nc + c] = cut;
     if (cut >= t1 - t0) atomicOr(alive, 1);                // its last frame is not final: the fold has to run
@@ -179,13 +316,15 @@ scan_fwd_rerun_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const
 // chunk's remaining (earlier) frames are smoothed and written here, bcut[g*nc+c] = first frame offset
 // of the chunk that still needs the re-run.
 template <typename T, int N, int P, int AM>
-__global__ void __launch_bounds__(kScanWarps* kLanes)
+__global__ void __launch_bounds__(kScanWarps* kLanes, N <= 3 ? 3 : 1)
 scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A,
                         const T* __restrict__ Q, int shared_mask, long B, long Tn, long L, long nc, int early_out,
                         T* __restrict__ bsum, long* __restrict__ bcut, int* __restrict__ alive, T* smth, T* ym,
                         int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
+  extern __shared__ __align__(16) unsigned char scan_smem[];
   const int lane = threadIdx.x & 31;
+  T* ring = reinterpret_cast<T*>(scan_smem + (threadIdx.x >> 5) * ring_bytes_per_warp<T, SG>()) + lane;
   const long tiles = num_tiles_dev(B);
   const long w = (long)blockIdx.x * kScanWarps + (threadIdx.x >> 5);
   if (w >= tiles * nc) return;
@@ -197,9 +336,8 @@ scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restr
     T ms[N], Vs[NS];
     const long t0 = (nc - 1) * L;
     const long base = (g * Tn + t0) * kLanes;
-    const bool ok0 = rts_backward_range<T, N, P, AM, kLanes, 2>(prm, filt + base * SG + lane, smth + base * SG + lane,
-                                                               ym ? ym + base * P + lane : nullptr, nullptr, nullptr,
-                                                               Tn - t0, true, ms, Vs);
+    const bool ok0 = rts_backward_range_ring<T, N, P, AM>(prm, filt + base * SG + lane, smth + base * SG + lane,
+                                                          ym ? ym + base * P + lane : nullptr, Tn - t0, true, ms, Vs, ring);
     if (b < B && status && !ok0) status[b] = 1;
     return;
   }
@@ -211,8 +349,9 @@ scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restr
   T acc[SR];
   bool ok = true;
   const long base = (g * Tn + c * L) * kLanes;
-  const long cut = scan_bwd_chunk<T, N, P, AM, kLanes, 2>(prm, filt + base * SG + lane, smth + base * SG + lane,
-                                                          ym ? ym + base * P + lane : nullptr, L, early_out != 0, acc, ok);
+  const long cut = scan_bwd_chunk<T, N, P, AM, kLanes>(prm, filt + base * SG + lane, smth + base * SG + lane,
+                                                       ym ? ym + base * P + lane : nullptr, L, early_out != 0, acc, ok,
+                                                       BwdTailRing<T, N, P, AM>{ring});
   if (lane == 0) {
     bcut[g * nc + c] = cut;
     if (cut <= 0) atomicOr(alive, 1);                      // its first frame is not final: the fold has to run

@@ -19,11 +19,13 @@ inline size_t scan_workspace_elems(long B, long Tn, int n, long L) {
 }
 
 inline long scan_auto_chunk(long B, long Tn, int n, int elem_size) {
-  // warps = tiles * chunks.  The kernels are register-bound at 12 (f64, n <= 3), 8 (f64, n = 4) and 20 (f32)
-  // resident warps per SM; aim at ONE full wave (f32: 16 measured best).  Longer chunks amortise the K warm-up
-  // frames every chunk pays before its summary has forgotten the boundary state (eksb_math.cuh scan_fwd_chunk):
-  // measured on 64 tracks x 10 M frames f64, 12 / 24 / 36 / 48 warps per SM -> 36.5 / 37.4 / 43.7 / 46.7 ms.
-  const long per_sm = scan_env_long("EKSB_SCAN_WARPS_PER_SM", elem_size == 8 ? (n >= 4 ? 8 : 12) : 16);
+  // warps = tiles * chunks.  The summary kernels keep 12 (f64) / 16 (f32) warps resident per SM (register-bound,
+  // n <= 3) and stage their frames through per-lane cp.async rings, so bytes in flight do not hinge on occupancy:
+  // fewer, longer chunks win because every chunk pays K warm-up frames before its summary has forgotten the
+  // boundary state (eksb_math.cuh scan_fwd_chunk).  Measured, 64 tracks x 10 M frames, 8 / 12 / 16 / 24 warps per
+  // SM: f64 34.8 / 35.1 / 35.5 / 36.4 ms, f32 17.8 / - / 18.2 / 20.1 ms.
+  (void)n;
+  const long per_sm = scan_env_long("EKSB_SCAN_WARPS_PER_SM", 8);
   const long want_chunks = (148L * per_sm + num_tiles(B) - 1) / num_tiles(B);
   long L = (Tn + want_chunks - 1) / want_chunks;
   if (L < 64) L = 64;
@@ -46,12 +48,16 @@ static int scan_run(const T* obs, const T* m0, const T* S0, const T* C, const T*
   const int early = scan_env_long("EKSB_SCAN_NO_EARLY", 0) ? 0 : 1;                 // A/B switch: old 2-read behaviour
   auto blocks = [&](long items) { return (unsigned)((items + kScanWarps - 1) / kScanWarps); };
   const int thr = kScanWarps * kLanes;
+  // per-lane frame rings of the summary kernels (eksb_scan.cuh), one per warp
+  const size_t smem_f = kScanWarps * ring_bytes_per_warp<T, 2 * P>(), smem_b = kScanWarps * ring_bytes_per_warp<T, SG>();
+  cudaFuncSetAttribute(scan_fwd_summary_kernel<T, N, P, AM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f);
+  cudaFuncSetAttribute(scan_bwd_summary_kernel<T, N, P, AM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b);
   // forward pass
   if (nc == 1) {
     scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 0, 1, finit, nullptr, filt, status);
   } else {
     // chunk 0 (sequential from the prior) rides in the same launch as the summaries of chunks >= 1
-    scan_fwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, early, fsum, fcut, alive, filt, status);
+    scan_fwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, smem_f, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, early, fsum, fcut, alive, filt, status);
     scan_fwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(filt, fsum, B, Tn, L, nc, alive, finit, status);
     scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 1, nc, finit, fcut, filt, status);
   }
@@ -62,7 +68,7 @@ static int scan_run(const T* obs, const T* m0, const T* S0, const T* C, const T*
     scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, nc - 1, nc, binit, nullptr, smth, ym, status);
   } else {
     // the terminal chunk (sequential from the end of the track) rides in the summary launch
-    scan_bwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, early, bsum, bcut, alive + 1, smth, ym, status);
+    scan_bwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, smem_b, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, early, bsum, bcut, alive + 1, smth, ym, status);
     scan_bwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(smth, bsum, B, Tn, L, nc, alive + 1, binit);
     scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, 0, nc - 1, binit, bcut, smth, ym, status);
   }

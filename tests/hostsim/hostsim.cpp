@@ -212,8 +212,8 @@ static int run_scan(long Tn, long L, int early, const T* y, const T* ev, const T
   load_sym<T, N>(V, S0);
   ok = kf_forward_range<T, N, P, AM, 1, 2, false>(prm, obs.data(), filt, len(0), kPriorUpdate, m, V, nll) && ok;
   for (long c = 1; c < nc; ++c)
-    fcut[c] = scan_fwd_chunk<T, N, P, AM, 1, 2>(prm, obs.data() + c * L * R2, filt + c * L * SG, len(c), early != 0,
-                                                &fsum[c * ScanRec<N>::FWD], ok);
+    fcut[c] = scan_fwd_chunk<T, N, P, AM, 1>(prm, obs.data() + c * L * R2, filt + c * L * SG, len(c), early != 0,
+                                             &fsum[c * ScanRec<N>::FWD], ok, FwdTailPlain<T, N, P, AM, 1, 2>());
   // F2: fold -- skipped (as on the device) when every chunk wrote its own last frame
   bool f_alive = false;
   for (long c = 1; c < nc; ++c) f_alive = f_alive || fcut[c] >= len(c);
@@ -241,8 +241,8 @@ static int run_scan(long Tn, long L, int early, const T* y, const T* ev, const T
   ok = rts_backward_range<T, N, P, AM, 1, 2>(prm, filt + (nc - 1) * L * SG, smth + (nc - 1) * L * SG, nullptr, nullptr,
                                              nullptr, len(nc - 1), true, ms, Vs) && ok;
   for (long c = 0; c + 1 < nc; ++c)
-    bcut[c] = scan_bwd_chunk<T, N, P, AM, 1, 2>(prm, filt + c * L * SG, smth + c * L * SG, nullptr, L, early != 0,
-                                                &bsum[c * ScanRec<N>::BWD], ok);
+    bcut[c] = scan_bwd_chunk<T, N, P, AM, 1>(prm, filt + c * L * SG, smth + c * L * SG, nullptr, L, early != 0,
+                                             &bsum[c * ScanRec<N>::BWD], ok, BwdTailPlain<T, N, P, AM, 1, 2>());
   // B2: fold -- skipped when every chunk smoothed its own first frame
   bool b_alive = false;
   for (long c = 0; c + 1 < nc; ++c) b_alive = b_alive || bcut[c] <= 0;
