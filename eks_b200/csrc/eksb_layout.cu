@@ -259,10 +259,77 @@ __global__ void zscore_kernel(const T* __restrict__ obs, const T* __restrict__ s
   }
 }
 
+// Compile-time (n, p): C and the frame records live in registers, one warp handles kZF consecutive frames of a
+// tile with all their loads issued before the first use (the runtime-dimension kernel above keeps m, V in local
+// memory and re-reads C for every frame: 2.1 TB/s on the bench shape).
+template <int N, int P> struct ZFrames {   // frames per warp: bounded by the registers their records take
+  static constexpr int value = (N + N * (N + 1) / 2 + 2 * P) > 20 ? ((N + N * (N + 1) / 2 + 2 * P) > 30 ? 1 : 2) : 4;
+};
+template <typename T, int N, int P>
+__global__ void __launch_bounds__(256)
+zscore_dim_kernel(const T* __restrict__ obs, const T* __restrict__ smth, const T* __restrict__ C, int shared_mask, long B,
+                  long Tn, int add_ev, T* __restrict__ z) {
+  constexpr int NS = N * (N + 1) / 2, SG = N + NS, kZF = ZFrames<N, P>::value;
+  const int lane = threadIdx.x & 31;
+  const long nblk = (Tn + kZF - 1) / kZF;
+  const long w = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (w >= num_tiles_dev(B) * nblk) return;
+  const long g = w / nblk;
+  const long t0 = (w - g * nblk) * kZF;
+  const long b = g * kLanes + lane;
+  const long bp = b < B ? b : B - 1;
+  const T* cp = C + ((shared_mask & EKSB_SHARED_C) ? 0 : bp * P * N);
+  T c[P][N];
+#pragma unroll
+  for (int j = 0; j < P; ++j)
+#pragma unroll
+    for (int i = 0; i < N; ++i) c[j][i] = cp[j * N + i];
+  const int nf = (int)(Tn - t0 < kZF ? Tn - t0 : kZF);
+  T st[kZF][SG], ob[kZF][2 * P];
+#pragma unroll
+  for (int f = 0; f < kZF; ++f)
+    if (f < nf) {
+      const T* rec = smth + ((g * Tn + t0 + f) * SG) * kLanes + lane;
+      const T* o = obs + ((g * Tn + t0 + f) * 2 * P) * kLanes + lane;
+#pragma unroll
+      for (int r = 0; r < SG; ++r) st[f][r] = rec[r * kLanes];
+#pragma unroll
+      for (int r = 0; r < 2 * P; ++r) ob[f][r] = o[r * kLanes];
+    }
+#pragma unroll
+  for (int f = 0; f < kZF; ++f)
+    if (f < nf) {
+      T* out = z + ((g * Tn + t0 + f) * P) * kLanes + lane;
+#pragma unroll
+      for (int j = 0; j < P; ++j) {
+        T mu = T(0), var = T(0);
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+          mu += c[j][i] * st[f][i];
+          T a = T(0);
+#pragma unroll
+          for (int l = 0; l < N; ++l) a += st[f][N + sym_idx<N>(i, l)] * c[j][l];
+          var += c[j][i] * a;
+        }
+        if (add_ev) var += ob[f][P + j];
+        out[j * kLanes] = (ob[f][j] - mu) * rsqrt(var);          // MUFU seed + Newton: ~1 ulp, a third of div + sqrt in f64
+      }
+    }
+}
+
 template <typename T>
 static int zscore_api(const T* obs, const T* smth, const T* C, int shared_mask, long B, long Tn, int n, int p, int add_ev,
                       T* z, void* stream) {
   if (!obs || !smth || !C || !z || B <= 0 || Tn <= 0 || n < 1 || n > 8 || p < 1 || p > 16) { set_error("zscore: bad argument"); return EKSB_EARG; }
+#define X(N_, P_)                                                                                                      \
+  if (n == N_ && p == P_) {                                                                                            \
+    const long warps = num_tiles(B) * ((Tn + ZFrames<N_, P_>::value - 1) / ZFrames<N_, P_>::value);                    \
+    zscore_dim_kernel<T, N_, P_><<<(unsigned)((warps + 7) / 8), 256, 0, (cudaStream_t)stream>>>(obs, smth, C, shared_mask, B, \
+                                                                                               Tn, add_ev, z);       \
+    return check_launch("zscore_dim_kernel");                                                                          \
+  }
+  EKSB_FOR_EACH_DIM(X)
+#undef X
   unsigned grid = (unsigned)(((Tn + 7) / 8) * num_tiles(B));
   zscore_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(obs, smth, C, shared_mask, B, Tn, n, p, add_ev, z);
   return check_launch("zscore_kernel");
