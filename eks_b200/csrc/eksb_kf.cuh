@@ -3,10 +3,13 @@
 // Mapping: one track per thread, one track-tile (32 tracks) per warp, one warp per CTA.
 // Every global access of a warp is one contiguous 128 B (f32) / 256 B (f64) line of the
 // track-tile layout (eksb_math.cuh), so the kernels stream HBM at full sector efficiency
-// with no shared-memory staging; latency is covered by a PF-frame register prefetch ring.
+// The forward kernel stages its obs frames through a per-lane cp.async ring in shared memory
+// (eksb_ring.cuh: no barrier, no register or scoreboard tied up by the prefetch); the backward kernel
+// (CV / yv outputs, single-track API calls) keeps a PF-frame register prefetch ring.
 // All matrices live in registers (see -Xptxas -v: no local memory).
 #pragma once
 #include "eksb_common.cuh"
+#include "eksb_ring.cuh"
 
 namespace eksb {
 
@@ -24,6 +27,7 @@ kf_forward_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* 
                   long B, long Tn, int first, const T* __restrict__ q_scale, T* __restrict__ filt,
                   double* __restrict__ nll, int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
+  extern __shared__ __align__(16) unsigned char kf_smem[];
   const long g = blockIdx.x;
   const int lane = threadIdx.x;
   const long b = g * kLanes + lane;
@@ -53,7 +57,7 @@ kf_forward_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* 
   const T* o = obs + (g * Tn * (2 * P)) * kLanes + lane;
   T* f = filt ? filt + (g * Tn * SG) * kLanes + lane : nullptr;
   double acc = 0.0;
-  ok = kf_forward_range<T, N, P, AM, kLanes, Prefetch<T, 2 * P>::value, NLL>(prm, o, f, Tn, first, m, V, acc) && ok;
+  ok = kf_forward_range_ring<T, N, P, AM, NLL>(prm, o, f, Tn, first, m, V, reinterpret_cast<T*>(kf_smem) + lane, &acc) && ok;
   if (b < B) {
     if (NLL) nll[(long)blockIdx.y * B + b] = 0.5 * (acc + (double)Tn * P * 1.8378770664093453 /* log 2pi */);
     if (status && !ok) status[b] = 1;
@@ -100,7 +104,7 @@ static int launch_forward(const T* obs, const T* m0, const T* S0, const T* C, co
   }
   dim3 grid((unsigned)num_tiles(B), (unsigned)(q_scale ? n_scale : 1));
 #define EKSB_GO(AM_, NLL_)                                                                                      \
-  kf_forward_kernel<T, N, P, AM_, NLL_><<<grid, kLanes, 0, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, \
+  kf_forward_kernel<T, N, P, AM_, NLL_><<<grid, kLanes, ring_bytes_per_warp<T, 2 * P>(), st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, \
                                                                  q_scale, filt, nll, status)
   if (a_mode == EKSB_A_DIAG) { if (nll) EKSB_GO(0, true); else EKSB_GO(0, false); }
   else                       { if (nll) EKSB_GO(1, true); else EKSB_GO(1, false); }
