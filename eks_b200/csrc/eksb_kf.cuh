@@ -8,6 +8,7 @@
 // (CV / yv outputs, single-track API calls) keeps a PF-frame register prefetch ring.
 // All matrices live in registers (see -Xptxas -v: no local memory).
 #pragma once
+#include <stdlib.h>
 #include "eksb_common.cuh"
 #include "eksb_ring.cuh"
 

@@ -322,14 +322,41 @@ EKSB_HD void predict(const Params<T, N, P, AM>& prm, const T* m, const T* V, T* 
 // Algebraically identical to eks/ensemble_kalman.py:104-105,110-117 (Woodbury) and to
 // the update at eks/newton_eks.py:137-138.  When NLL is set, returns this frame's
 //   log det(R + C S C^T) + nu^T (R + C S C^T)^-1 nu      (determinant lemma).
+// The update is split in two so that a sweep over several process-noise scales (SURVEY A8 grid search) can
+// share the state-independent half between the scales:
+//   update_shared: w = 1/r, cw = C^T R^-1 (per observation), Lam0 = C^T R^-1 C, detR = prod r
+//   update_state : everything that depends on the predicted state (mp, S)
 template <typename T, int N, int P, int AM, bool NLL>
-EKSB_HD double update(const Params<T, N, P, AM>& prm, const T* y, const T* r, const T* mp, const T* S,
-                      T* m, T* V, bool& ok) {
+EKSB_HD void update_shared(const Params<T, N, P, AM>& prm, const T* r, T* w, T (*cw)[N], T* Lam0, double& detR) {
   constexpr int NS = Dim<N>::NS;
-  T w[P], nu[P];
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) w[j] = rcp(r[j]);
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) Lam0[k] = T(0);   // C^T R^-1 C is accumulated apart from S^-1 (state-independent)
   EKSB_UNROLL
   for (int j = 0; j < P; ++j) {
-    w[j] = rcp(r[j]);
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) cw[j][i] = prm.C[j][i] * w[j];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int k = i; k < N; ++k) Lam0[sym_idx<N>(i, k)] += cw[j][i] * prm.C[j][k];
+    }
+  }
+  detR = 1.0;
+  if (NLL) {
+    EKSB_UNROLL
+    for (int j = 0; j < P; ++j) detR *= (double)r[j];
+  }
+}
+
+template <typename T, int N, int P, int AM, bool NLL>
+EKSB_HD double update_state(const Params<T, N, P, AM>& prm, const T* y, const T* w, const T (*cw)[N], const T* Lam0,
+                            double detR, const T* mp, const T* S, T* m, T* V, bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T nu[P];
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) {
     T s = y[j];
     EKSB_UNROLL
     for (int i = 0; i < N; ++i) s -= prm.C[j][i] * mp[i];
@@ -337,39 +364,39 @@ EKSB_HD double update(const Params<T, N, P, AM>& prm, const T* y, const T* r, co
   }
   T Sinv[NS], Lam[NS];
   T detS = sym_inv<T, N>(S, Sinv, ok);
-  EKSB_UNROLL
-  for (int k = 0; k < NS; ++k) Lam[k] = T(0);   // C^T R^-1 C is accumulated apart from S^-1 (state-independent)
   T u[N];
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) u[i] = T(0);
   EKSB_UNROLL
   for (int j = 0; j < P; ++j) {
-    T cw[N];
     EKSB_UNROLL
-    for (int i = 0; i < N; ++i) cw[i] = prm.C[j][i] * w[j];
-    EKSB_UNROLL
-    for (int i = 0; i < N; ++i) {
-      u[i] += cw[i] * nu[j];
-      EKSB_UNROLL
-      for (int k = i; k < N; ++k) Lam[sym_idx<N>(i, k)] += cw[i] * prm.C[j][k];
-    }
+    for (int i = 0; i < N; ++i) u[i] += cw[j][i] * nu[j];
   }
   EKSB_UNROLL
-  for (int k = 0; k < NS; ++k) Lam[k] += Sinv[k];
+  for (int k = 0; k < NS; ++k) Lam[k] = Lam0[k] + Sinv[k];
   T detL = sym_inv<T, N>(Lam, V, ok);
   T Vu[N];
   sym_matvec<T, N>(V, u, Vu);
   EKSB_UNROLL
   for (int i = 0; i < N; ++i) m[i] = mp[i] + Vu[i];
   if (NLL) {
-    double quad = 0.0, detR = 1.0, uVu = 0.0;
+    double quad = 0.0, uVu = 0.0;
     EKSB_UNROLL
-    for (int j = 0; j < P; ++j) { quad += (double)nu[j] * (double)nu[j] * (double)w[j]; detR *= (double)r[j]; }
+    for (int j = 0; j < P; ++j) quad += (double)nu[j] * (double)nu[j] * (double)w[j];
     EKSB_UNROLL
     for (int i = 0; i < N; ++i) uVu += (double)u[i] * (double)Vu[i];
     return log(detR * (double)detS * (double)detL) + (quad - uVu);
   }
   return 0.0;
+}
+
+template <typename T, int N, int P, int AM, bool NLL>
+EKSB_HD double update(const Params<T, N, P, AM>& prm, const T* y, const T* r, const T* mp, const T* S,
+                      T* m, T* V, bool& ok) {
+  T w[P], cw[P][N], Lam0[Dim<N>::NS];
+  double detR;
+  update_shared<T, N, P, AM, NLL>(prm, r, w, cw, Lam0, detR);
+  return update_state<T, N, P, AM, NLL>(prm, y, w, cw, Lam0, detR, mp, S, m, V, ok);
 }
 
 // ---------------------------------------------------------------------------
