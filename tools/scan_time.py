@@ -45,7 +45,8 @@ def run(dt, B, T, chunk=0, reps=2):
 
 if __name__ == "__main__":
     big_only = os.environ.get("SCAN_TIME_BIG_ONLY") == "1"
-    for dt in (torch.float32, torch.float64):
+    dts = (torch.float64,) if os.environ.get("SCAN_TIME_F64_ONLY") == "1" else (torch.float32, torch.float64)
+    for dt in dts:
         if not big_only:
             run(dt, 64, 2_000_000)
             run(dt, 64, 2_000_000, chunk=1024)
