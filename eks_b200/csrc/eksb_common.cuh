@@ -26,7 +26,7 @@ __device__ __forceinline__ long num_tiles_dev(long B) { return (B + kLanes - 1) 
 // (n,p) pair has no pipelined instantiation (the caller then uses the plain kernel).
 template <typename T>
 int kf_forward_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B,
-                    long Tn, int n, int p, int a_mode, int first, T* filt, int* status, cudaStream_t st);
+                    long Tn, int n, int p, int a_mode, int first, T* filt, int* status, const T* yoff, cudaStream_t st);
 template <typename T>
 int rts_backward_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, int n, int p,
                       int a_mode, T* smth, T* ym, T* yv, int* status, cudaStream_t st);

@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(kLanes)
 kf_forward_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                   const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
                   long B, long Tn, int first, const T* __restrict__ q_scale, T* __restrict__ filt,
-                  double* __restrict__ nll, int* __restrict__ status) {
+                  double* __restrict__ nll, int* __restrict__ status, const T* __restrict__ yoff) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
   extern __shared__ __align__(16) unsigned char kf_smem[];
   const long g = blockIdx.x;
@@ -58,7 +58,11 @@ kf_forward_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* 
   const T* o = obs + (g * Tn * (2 * P)) * kLanes + lane;
   T* f = filt ? filt + (g * Tn * SG) * kLanes + lane : nullptr;
   double acc = 0.0;
-  ok = kf_forward_range_ring<T, N, P, AM, NLL>(prm, o, f, Tn, first, m, V, reinterpret_cast<T*>(kf_smem) + lane, &acc) && ok;
+  T mu[P];                                 // optional per-track observation offset (camera means): y - mu, like the pipelined kernels
+#pragma unroll
+  for (int j = 0; j < P; ++j) mu[j] = yoff ? yoff[bp * P + j] : T(0);
+  ok = kf_forward_range_ring<T, N, P, AM, NLL>(prm, o, f, Tn, first, m, V, reinterpret_cast<T*>(kf_smem) + lane, &acc,
+                                               yoff ? mu : nullptr) && ok;
   if (b < B) {
     if (NLL) nll[(long)blockIdx.y * B + b] = 0.5 * (acc + (double)Tn * P * 1.8378770664093453 /* log 2pi */);
     if (status && !ok) status[b] = 1;
@@ -89,7 +93,7 @@ rts_backward_kernel(const T* filt, const T* __restrict__ C, const T* __restrict_
 template <typename T, int N, int P>
 static int launch_forward(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                           long B, long Tn, int a_mode, int first, const T* q_scale, int n_scale, T* filt, double* nll,
-                          int* status, cudaStream_t st) {
+                          int* status, const T* yoff, cudaStream_t st) {
   if (filt && !nll && !q_scale && use_pipe(B)) {           // warp-specialised kernel, in groups of tiles it handles best
     const long tiles = num_tiles(B), ng = pipe_groups(tiles, (int)sizeof(T)), per = (tiles + ng - 1) / ng;
     int rc = EKSB_OK;
@@ -99,14 +103,14 @@ static int launch_forward(const T* obs, const T* m0, const T* S0, const T* C, co
       rc = kf_forward_pipe<T>(obs + g0 * Tn * (2 * P) * kLanes, off(m0, EKSB_SHARED_M0, N), off(S0, EKSB_SHARED_S0, N * N),
                               off(C, EKSB_SHARED_C, P * N), off(A, EKSB_SHARED_A, N * N), off(Q, EKSB_SHARED_Q, N * N),
                               shared_mask, Bs, Tn, N, P, a_mode, first, filt + g0 * Tn * Dim<N>::SIGMA * kLanes,
-                              status ? status + b0 : nullptr, st);
+                              status ? status + b0 : nullptr, yoff ? yoff + b0 * P : nullptr, st);
     }
     if (rc != EKSB_EDIM) return rc;
   }
   dim3 grid((unsigned)num_tiles(B), (unsigned)(q_scale ? n_scale : 1));
 #define EKSB_GO(AM_, NLL_)                                                                                      \
   kf_forward_kernel<T, N, P, AM_, NLL_><<<grid, kLanes, ring_bytes_per_warp<T, 2 * P>(), st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, \
-                                                                 q_scale, filt, nll, status)
+                                                                 q_scale, filt, nll, status, yoff)
   if (a_mode == EKSB_A_DIAG) { if (nll) EKSB_GO(0, true); else EKSB_GO(0, false); }
   else                       { if (nll) EKSB_GO(1, true); else EKSB_GO(1, false); }
 #undef EKSB_GO
@@ -141,7 +145,7 @@ static int launch_backward(const T* filt, const T* C, const T* A, const T* Q, in
 template <typename T>
 static int kf_forward_api(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                           long B, long Tn, int n, int p, int a_mode, int first, const T* q_scale, int n_scale, T* filt,
-                          double* nll, int* status, void* stream) {
+                          double* nll, int* status, void* stream, const T* yoff = nullptr) {
   if (!obs || !m0 || !S0 || !C || !A || !Q || B <= 0 || Tn <= 0) { set_error("kf_forward: null pointer or empty batch"); return EKSB_EARG; }
   if (first != kPriorUpdate && first != kPriorOnly) { set_error("kf_forward: bad first-frame mode %d", first); return EKSB_EARG; }
   if (a_mode != EKSB_A_DIAG && a_mode != EKSB_A_DENSE) { set_error("kf_forward: bad a_mode %d", a_mode); return EKSB_EARG; }
@@ -150,7 +154,7 @@ static int kf_forward_api(const T* obs, const T* m0, const T* S0, const T* C, co
 #define X(N_, P_)                                                                                                 \
   if (n == N_ && p == P_)                                                                                         \
     return launch_forward<T, N_, P_>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, a_mode, first, q_scale, n_scale,   \
-                                     filt, nll, status, (cudaStream_t)stream);
+                                     filt, nll, status, yoff, (cudaStream_t)stream);
   EKSB_FOR_EACH_DIM(X)
 #undef X
   set_error("kf_forward: (n=%d,p=%d) not instantiated", n, p);

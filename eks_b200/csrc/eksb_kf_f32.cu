@@ -9,3 +9,9 @@ extern "C" int eksb_kf_forward_f32(const float* obs, const float* m0, const floa
                                    void* stream) {
   return kf_forward_api<float>(obs, m0, S0, C, A, Q, shared_mask, B, T, n, p, a_mode, first, q_scale, n_scale, filt, nll, status, stream);
 }
+
+extern "C" int eksb_kf_forward_offset_f32(const float* obs, const float* y_offset, const float* m0, const float* S0, const float* C,
+                                          const float* A, const float* Q, int shared_mask, long B, long T, int n, int p,
+                                          int a_mode, int first, float* filt, double* nll, int* status, void* stream) {
+  return kf_forward_api<float>(obs, m0, S0, C, A, Q, shared_mask, B, T, n, p, a_mode, first, nullptr, 0, filt, nll, status, stream, y_offset);
+}

@@ -112,8 +112,8 @@ template <typename T, int N, int P, int AM, int OP, typename Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS)
 kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                        const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
-                       long B, long Tn, int first, T* __restrict__ filt, int* __restrict__ status, int tpc,
-                       const __grid_constant__ RoleMap roles) {
+                       long B, long Tn, int first, T* __restrict__ filt, int* __restrict__ status,
+                       const T* __restrict__ yoff, int tpc, const __grid_constant__ RoleMap roles) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, REC = Rec<N>::FWD;
   constexpr int H = Cfg::H, F = Cfg::F, NST = Cfg::NST;
   const int TPC = tpc;
@@ -144,6 +144,11 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
     constexpr bool kOuter = (P * NS <= 36);                // outer products C_j C_j^T kept in registers
     T CC[kOuter ? P : 1][NS];
     if (kOuter) make_outer<T, N, kOuter ? P : 1>(prm.C, CC);
+    // optional per-track observation offset (camera means, multiview_pca_smoother.py:702-705): y - mu is formed here,
+    // with the same rounding as a separate centring pass over the records, which this replaces
+    T mu[P];
+#pragma unroll
+    for (int j = 0; j < P; ++j) mu[j] = yoff ? yoff[bp * P + j] : T(0);
     if (issuer) {
       for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
       mbar_fence_init();
@@ -174,6 +179,10 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
             T cur[R2], rec[REC];
 #pragma unroll
             for (int r = 0; r < R2; ++r) cur[r] = src[(j * R2 + r) * kLanes];
+            if (yoff) {
+#pragma unroll
+              for (int q = 0; q < P; ++q) cur[q] -= mu[q];
+            }
             if constexpr (kOuter) fwd_prep_outer<T, N, P>(prm.C, CC, cur, cur + P, rec);
             else fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
 #pragma unroll
@@ -290,8 +299,8 @@ template <typename T, int N, int P, typename Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS)
 kf_forward_pipe3_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                         const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
-                        long B, long Tn, int first, T* __restrict__ filt, int* __restrict__ status, int tpc,
-                        const __grid_constant__ RoleMap roles) {
+                        long B, long Tn, int first, T* __restrict__ filt, int* __restrict__ status,
+                        const T* __restrict__ yoff, int tpc, const __grid_constant__ RoleMap roles) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, REC = Rec<N>::FWD, VR = NS + 1;
   constexpr int H = Cfg::H, F = Cfg::F, NST = Cfg::NST;
   using SM = Pipe3Smem<T, R2, REC, VR, Cfg>;
@@ -322,6 +331,9 @@ kf_forward_pipe3_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
     constexpr bool kOuter = (P * NS <= 36);
     T CC[kOuter ? P : 1][NS];
     if constexpr (kOuter) make_outer<T, N, P>(prm.C, CC);
+    T mu[P];                                               // optional per-track observation offset, as in the two-role kernel
+#pragma unroll
+    for (int j = 0; j < P; ++j) mu[j] = yoff ? yoff[bp * P + j] : T(0);
     if (issuer) {
       for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
       mbar_fence_init();
@@ -351,6 +363,10 @@ kf_forward_pipe3_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
             T cur[R2], rec[REC];
 #pragma unroll
             for (int r = 0; r < R2; ++r) cur[r] = src[(j * R2 + r) * kLanes];
+            if (yoff) {
+#pragma unroll
+              for (int q = 0; q < P; ++q) cur[q] -= mu[q];
+            }
             if constexpr (kOuter) fwd_prep_outer<T, N, P>(prm.C, CC, cur, cur + P, rec);
             else fwd_prep<T, N, P, 0>(prm, cur, cur + P, rec);
 #pragma unroll

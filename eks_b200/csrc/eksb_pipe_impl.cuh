@@ -147,7 +147,7 @@ constexpr float kFwdChainW = 118, kFwdHelperW = 125, kBwdChainW = 103, kBwdHelpe
 
 template <typename T, int N, int P, int AM, int OP, typename Auto>
 static int launch_fwd_cfg(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
-                          long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
+                          long B, long Tn, int first, T* filt, int* status, const T* yoff, cudaStream_t st) {
   using Cfg = typename Auto::type;
   auto kern = kf_forward_pipe_kernel<T, N, P, AM, OP, Cfg>;
   const int tpc = pick_tpc(num_tiles(B), Cfg::TPC, Auto::kTileSmem);
@@ -156,7 +156,7 @@ static int launch_fwd_cfg(const T* obs, const T* m0, const T* S0, const T* C, co
   const unsigned grid = (unsigned)((num_tiles(B) + tpc - 1) / tpc);
   RoleMap rm;
   const int warps = make_roles(tpc, Cfg::H, kFwdChainW, kFwdHelperW, rm);
-  kern<<<grid, warps * kLanes, smem, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, tpc, rm);
+  kern<<<grid, warps * kLanes, smem, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, tpc, rm);
   return check_launch("kf_forward_pipe_kernel");
 }
 
@@ -213,7 +213,7 @@ template <typename T> struct Fwd3Helpers { static constexpr int value = sizeof(T
 
 template <typename T, int N, int P>
 static int launch_fwd_pipe3(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
-                            long B, long Tn, int first, T* filt, int* status, int tpc, cudaStream_t st) {
+                            long B, long Tn, int first, T* filt, int* status, const T* yoff, int tpc, cudaStream_t st) {
   using Auto = Auto3<T, N, P, Fwd3Helpers<T>::value>;
   using Cfg = typename Auto::type;
   auto kern = kf_forward_pipe3_kernel<T, N, P, Cfg>;
@@ -222,7 +222,7 @@ static int launch_fwd_pipe3(const T* obs, const T* m0, const T* S0, const T* C, 
   RoleMap rm;
   const int warps = make_roles3(tpc, Cfg::H, rm);
   kern<<<grid, warps * kLanes, Auto::kTileSmem * tpc, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt,
-                                                            status, tpc, rm);
+                                                            status, yoff, tpc, rm);
   return check_launch("kf_forward_pipe3_kernel");
 }
 
@@ -232,7 +232,7 @@ static int launch_fwd_pipe3(const T* obs, const T* m0, const T* S0, const T* C, 
 // that to ~6.4 TB/s.  It needs ~100 KB per f64 tile, so it is used when the tiles of an SM fit.
 template <typename T, int N, int P, int AM, int OP = 0>
 static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
-                           long B, long Tn, int first, T* filt, int* status, cudaStream_t st) {
+                           long B, long Tn, int first, T* filt, int* status, const T* yoff, cudaStream_t st) {
   using Shallow = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, EKSB_FWD_F, EKSB_FWD_NST>;
   using Deep = AutoCfg<T, EKSB_FWD_DEEP_H, 2 * P, Rec<N>::FWD, 8, 4>;
   if constexpr (OP == 0 && AM == 0 && N <= 3 && Auto3<T, N, P, Fwd3Helpers<T>::value>::ok) {
@@ -242,17 +242,17 @@ static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, c
     // also carry the mean warps, and the two-role kernel is already HBM-bound there).  Hence: one tile per SM only.
     static const int max_per_sm = getenv("EKSB_FWD3_MAX") ? atoi(getenv("EKSB_FWD3_MAX")) : 1;
     if (per_sm <= max_per_sm && per_sm <= 2)
-      return launch_fwd_pipe3<T, N, P>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status,
+      return launch_fwd_pipe3<T, N, P>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff,
                                        (int)(per_sm < 1 ? 1 : per_sm), st);
   }
   if constexpr (N <= 3 && Deep::ok) {
     const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
     static const bool shallow_only = getenv("EKSB_FWD_SHALLOW") != nullptr;
     if (!shallow_only && per_sm <= Deep::TPC && per_sm * Deep::kTileSmem + 1024 <= kCtaSmemBudget)
-      return launch_fwd_cfg<T, N, P, AM, OP, Deep>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, st);
+      return launch_fwd_cfg<T, N, P, AM, OP, Deep>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st);
   }
   if (!Shallow::ok) return EKSB_EDIM;
-  return launch_fwd_cfg<T, N, P, AM, OP, Shallow>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, st);
+  return launch_fwd_cfg<T, N, P, AM, OP, Shallow>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st);
 }
 
 template <typename T, int N, int P, int AM, int OP, int OUT, typename Auto>
@@ -315,12 +315,12 @@ static int launch_bwd_pipe(const T* filt, const T* C, const T* A, const T* Q, in
 #ifdef EKSB_PIPE_FWD
 template <typename T>
 int kf_forward_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B,
-                    long Tn, int n, int p, int a_mode, int first, T* filt, int* status, cudaStream_t st) {
+                    long Tn, int n, int p, int a_mode, int first, T* filt, int* status, const T* yoff, cudaStream_t st) {
 #define X(N_, P_)                                                                                                      \
   if (n == N_ && p == P_)                                                                                              \
     return a_mode == EKSB_A_DIAG                                                                                       \
-               ? launch_fwd_pipe<T, N_, P_, 0>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, st)      \
-               : launch_fwd_pipe<T, N_, P_, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, st);
+               ? launch_fwd_pipe<T, N_, P_, 0>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st) \
+               : launch_fwd_pipe<T, N_, P_, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st);
   EKSB_FOR_EACH_PIPE_DIM(X)
 #undef X
   return EKSB_EDIM;
@@ -350,8 +350,8 @@ int btd_solve_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* 
 #define X(N_, P_)                                                                                                       \
   if (n == N_ && p == P_) {                                                                                             \
     int rc = a_mode == EKSB_A_DIAG                                                                                      \
-                 ? launch_fwd_pipe<T, N_, P_, 0, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, kPriorUpdate, work, status, st) \
-                 : launch_fwd_pipe<T, N_, P_, 1, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, kPriorUpdate, work, status, st); \
+                 ? launch_fwd_pipe<T, N_, P_, 0, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, kPriorUpdate, work, status, (const T*)nullptr, st) \
+                 : launch_fwd_pipe<T, N_, P_, 1, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, kPriorUpdate, work, status, (const T*)nullptr, st); \
     if (rc != EKSB_OK) return rc;                                                                                       \
     return a_mode == EKSB_A_DIAG                                                                                        \
                ? launch_bwd_pipe<T, N_, P_, 0, 1>(work, C, A, Q, shared_mask, B, Tn, sol, ym, nullptr, status, st)      \

@@ -32,7 +32,8 @@ template <typename T, int ROWS> __host__ __device__ constexpr size_t ring_bytes_
 // kf_forward_range (eksb_math.cuh) with the obs frames staged through the ring; same arithmetic.
 template <typename T, int N, int P, int AM, bool NLL = false>
 __device__ bool kf_forward_range_ring(const Params<T, N, P, AM>& prm, const T* __restrict__ obs, T* __restrict__ filt,
-                                      long n, int first, T* m, T* V, T* ring, double* nll = nullptr) {
+                                      long n, int first, T* m, T* V, T* ring, double* nll = nullptr,
+                                      const T* mu = nullptr /* P per-track observation offsets in registers, or null */) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, D = kRingDepth;
   bool ok = true;
 #pragma unroll
@@ -49,6 +50,10 @@ __device__ bool kf_forward_range_ring(const Params<T, N, P, AM>& prm, const T* _
     if (t + D < n) ring_issue<T, R2>(ring, slot, obs + (t + D) * R2 * kLanes);
     cp_async_commit();
     slot = (slot + 1 == D) ? 0 : slot + 1;
+    if (mu) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) cur[j] -= mu[j];
+    }
     const bool is_first = (t == 0);
     if (!(is_first && first == kPriorOnly)) {
       T mp[N], S[NS];

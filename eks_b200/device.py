@@ -228,8 +228,10 @@ def pca_setup(obs, B, T, p, quantile, smooth_param, n=3, center=True, status=Non
 
 # ------------------------------------------------------------------ A2 / A6 forward
 def kf_forward(obs, prm: TrackParams, B, T, first=_lib.FIRST_PRIOR_UPDATE, q_scale=None, want_filt=True,
-               want_nll=False, filt=None, status=None):
-    """Forward filter.  Returns (filt or None, nll (n_scale,B) float64 or None, status (B,) int32)."""
+               want_nll=False, filt=None, status=None, y_offset=None):
+    """Forward filter.  Returns (filt or None, nll (n_scale,B) float64 or None, status (B,) int32).
+    y_offset: (B,p) per-track offsets subtracted from y as the frames are read (the camera means of
+    multiview_pca_smoother.py:698-705 without a centring pass over the records); not with q_scale."""
     _need_cuda(obs, "obs")
     dev, dt = obs.device, obs.dtype
     if prm.dtype != dt:
@@ -242,6 +244,16 @@ def kf_forward(obs, prm: TrackParams, B, T, first=_lib.FIRST_PRIOR_UPDATE, q_sca
     nll = torch.empty((max(n_scale, 1), B), dtype=torch.float64, device=dev) if want_nll else None
     if status is None:
         status = torch.zeros(B, dtype=torch.int32, device=dev)
+    if y_offset is not None:
+        if q_scale is not None:
+            raise ValueError("y_offset and q_scale cannot be combined")
+        if y_offset.dtype != dt or tuple(y_offset.shape) != (B, prm.p) or not y_offset.is_contiguous():
+            raise ValueError("y_offset must be a contiguous (B,p) tensor of the obs dtype")
+        fn = getattr(lib(), f"eksb_kf_forward_offset_{_sfx(dt)}")
+        check(fn(_ptr(obs), _ptr(y_offset), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q),
+                 prm.shared_mask, B, T, prm.n, prm.p, prm.a_mode, first, _ptr(filt), _ptr(nll), _ptr(status),
+                 _stream(dev)), "eksb_kf_forward_offset")
+        return filt, nll, status
     fn = getattr(lib(), f"eksb_kf_forward_{_sfx(dt)}")
     check(fn(_ptr(obs), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), prm.shared_mask, B, T,
              prm.n, prm.p, prm.a_mode, first, _ptr(q_scale), n_scale, _ptr(filt), _ptr(nll), _ptr(status),

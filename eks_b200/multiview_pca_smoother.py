@@ -113,8 +113,9 @@ def smooth_session_multi_cam(stack, smooth_param, quantile_keep_pca, newton=Fals
     stack: (M, T, B, p) host array or CUDA tensor -- M ensemble members, T frames, B keypoints (tracks),
     p = 2 * n_cameras columns ordered [cam0_x, cam0_y, cam1_x, ...] (the restack of :645-659).
     Pipeline, every stage a libeksb kernel: ensemble median + variance fused with the restack
-    (eksb_ensemble_tiled, :675-682) -> per-track good-frame selection, camera means, PCA(3), S0, Q, C and
-    centring (eksb_pca_setup, :684-731) -> filter + RTS + back-projection (or the Newton-recursive filter).
+    (eksb_ensemble_tiled, :675-682) -> per-track good-frame selection, camera means, PCA(3), S0, Q, C
+    (eksb_pca_setup, :684-731; the centring of :702-705 is fused into the forward filter as a per-track
+    observation offset) -> filter + RTS + back-projection (or the Newton-recursive filter).
     Returns dict(y=(B,T,p) smoothed observations with the camera means added back (:745,:761-762),
     latent=(B,T,3), means=(B,p)) as host float64 arrays."""
     d = _cuda()
@@ -122,14 +123,14 @@ def smooth_session_multi_cam(stack, smooth_param, quantile_keep_pca, newton=Fals
     M, T, B, p = t.shape
     preds = t.to(device=d, dtype=dtype).reshape(M, T, B * p).contiguous()
     obs = dev.ensemble_tiled(preds, B, p, "median")
-    prm, means, status = dev.pca_setup(obs, B, T, p, quantile_keep_pca, smooth_param, n=3, center=True)
+    prm, means, status = dev.pca_setup(obs, B, T, p, quantile_keep_pca, smooth_param, n=3, center=False)
     sg = dev.sigma(3)
     if newton:
-        filt, _, st2 = dev.kf_forward(obs, prm, B, T, first=_lib.FIRST_PRIOR_ONLY, status=status)
+        filt, _, st2 = dev.kf_forward(obs, prm, B, T, first=_lib.FIRST_PRIOR_ONLY, status=status, y_offset=means)
         lat = dev.unpack_rows(filt, sg, 0, B, T, 3)
         ym = dev.unpack_rows(dev.project(filt, prm, B, T), p, 0, B, T, p)
     else:
-        filt, _, _ = dev.kf_forward(obs, prm, B, T, status=status)
+        filt, _, _ = dev.kf_forward(obs, prm, B, T, status=status, y_offset=means)
         out = dev.rts_backward(filt, prm, B, T, inplace=True, want_ym=True, status=status)
         lat = dev.unpack_rows(out["smth"], sg, 0, B, T, 3)
         ym = dev.unpack_rows(out["ym"], p, 0, B, T, p)

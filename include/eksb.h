@@ -134,6 +134,17 @@ EKSB_API int eksb_kf_forward_f32(const float* obs, const float* m0, const float*
                         const float* Q, int shared_mask, long B, long T, int n, int p, int a_mode, int first,
                         const float* q_scale, int n_scale, float* filt, double* nll, int* status, void* stream);
 
+/* The same filter on UNCENTRED observations: y_offset (B,p), one row per track, is subtracted from y as the frames
+ * are read (y - offset, the rounding of a separate centring pass), so the camera means of
+ * multiview_pca_smoother.py:698-705 need no pass of their own over the records (eksb_pca_setup with center = 0).
+ * y_offset may be NULL (plain eksb_kf_forward). */
+EKSB_API int eksb_kf_forward_offset_f64(const double* obs, const double* y_offset, const double* m0, const double* S0,
+                        const double* C, const double* A, const double* Q, int shared_mask, long B, long T, int n, int p,
+                        int a_mode, int first, double* filt, double* nll, int* status, void* stream);
+EKSB_API int eksb_kf_forward_offset_f32(const float* obs, const float* y_offset, const float* m0, const float* S0,
+                        const float* C, const float* A, const float* Q, int shared_mask, long B, long T, int n, int p,
+                        int a_mode, int first, float* filt, double* nll, int* status, void* stream);
+
 /* ---- A4/A5: smooth_backward() + back-projection  eks/ensemble_kalman.py:120-164 --------
  * RTS pass over state records written by eksb_kf_forward.  S = A Vf A^T + Q is recomputed
  * per frame instead of being read back (:101,:158).  smth may equal filt (in-place).

@@ -183,6 +183,36 @@ def test_large_batches_go_out_as_groups_of_tiles(dtname, tol, monkeypatch):
     assert int(st[bad]) == 1 and int(st.sum()) == 1                    # status offset of the last group
 
 
+@pytest.mark.parametrize("dtname", ["float64", "float32"])
+@pytest.mark.parametrize("B", [70, 200])
+def test_observation_offset_equals_centring_pass(dtname, B, monkeypatch):
+    """eksb_kf_forward_offset: y - offset formed as the frames are read == filtering records centred by a separate
+    pass, bit for bit, in the pipelined kernels (three-role and two-role, grouped launches) and the plain kernel
+    (with NLL)."""
+    import torch
+    from eks_b200 import device as dev
+    dt = getattr(torch, dtname)
+    T, p, n = 260, 4, 3
+    c = _random_batch(B, T, p, n, dt, seed=5 + B)
+    d = c["obs"].device
+    off = torch.as_tensor(np.random.default_rng(B).uniform(-300, 300, size=(B, p)), dtype=dt).to(d)
+    raw = dev.pack_obs(torch.as_tensor(c["y"], dtype=dt).to(d) + off[:, None, :], torch.as_tensor(c["ev"], dtype=dt).to(d))
+    y_c = (torch.as_tensor(c["y"], dtype=dt).to(d) + off[:, None, :]) - off[:, None, :]       # the centring pass's rounding
+    centred = dev.pack_obs(y_c, torch.as_tensor(c["ev"], dtype=dt).to(d))
+    rows = lambda rec: dev.unpack_rows(rec, dev.sigma(n), 0, B, T, dev.sigma(n))             # real tracks only (not the padding lanes)
+    for env in ({}, {"EKSB_PIPE_MAX_TILES": "2", "EKSB_PIPE_GROUP_TILES": "3"}, {"EKSB_PIPE": "0"}):
+        for k in ("EKSB_PIPE_MAX_TILES", "EKSB_PIPE_GROUP_TILES", "EKSB_PIPE"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        a, _, sa = dev.kf_forward(centred, c["prm"], B, T)
+        b, _, sb = dev.kf_forward(raw, c["prm"], B, T, y_offset=off)
+        assert torch.equal(rows(a), rows(b)) and int(sa.sum()) == 0 and int(sb.sum()) == 0
+    a, na, _ = dev.kf_forward(centred, c["prm"], B, T, want_nll=True)                        # plain kernel, NLL
+    b, nb, _ = dev.kf_forward(raw, c["prm"], B, T, want_nll=True, y_offset=off)
+    assert torch.equal(rows(a), rows(b)) and torch.equal(na, nb)
+
+
 def test_inplace_smoothing_equals_out_of_place():
     import torch
     from eks_b200 import device as dev
