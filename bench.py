@@ -304,6 +304,9 @@ def gpu_main(a):
     # ---- synthesis + K1 (ensemble, fused restack): preds [M][T][blk*p] -> obs records, block by block
     gen = torch.Generator(device=d); gen.manual_seed(1234 + rank)
     obs = dev.alloc_records(B, T, 2 * P_OBS, dt, d)
+    # the ensemble kernel also leaves max_vars (row maximum of the ensemble variances) in the setup workspace
+    ws_setup = None if a.no_setup else dev.setup_workspace(B, T, P_OBS, dt, d)
+    mx_all = None if a.no_setup else dev.setup_max_var_view(ws_setup, B, T, P_OBS, dt)
     blk = 128
     tile_elems = T * 2 * P_OBS * 32
     k1_ms, k1_tf = 0.0, 0
@@ -313,7 +316,8 @@ def gpu_main(a):
         preds = synth_preds_block(torch, prm.C[b0:b0 + nb], T, dt, d, gen)
         out = obs[(b0 // 32) * tile_elems:((b0 + nb + 31) // 32) * tile_elems]
         e0.record()
-        dev.ensemble_tiled(preds, nb, P_OBS, "median", out=out)
+        mxb = None if mx_all is None else mx_all[(b0 // 32) * T * 32:((b0 + nb + 31) // 32) * T * 32]
+        dev.ensemble_tiled(preds, nb, P_OBS, "median", out=out, max_var=mxb)
         e1.record()
         torch.cuda.synchronize()
         if b0 > 0:                                             # skip the first (cold) launch
@@ -376,7 +380,7 @@ def gpu_main(a):
     launches = 2 * a.steps
     k1 = None
     if k1_ms > 0:
-        k1b = (M_ENS * P_OBS + 2 * P_OBS) * es
+        k1b = (M_ENS * P_OBS + 2 * P_OBS + (0 if a.no_setup else 1)) * es     # + the max_vars row handed to the setup
         k1 = {"kernel": "ensemble_tiled", "keypoint_frames_per_s": k1_tf / (k1_ms * 1e-3),
               "achieved_gbs": k1_tf * k1b / (k1_ms * 1e-3) / 1e9, "frac": k1_tf * k1b / (k1_ms * 1e-3) / 1e9 / peak}
 
@@ -387,14 +391,14 @@ def gpu_main(a):
     fwd_off_ms = None
     if not a.no_setup:
         s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        dev.pca_setup(obs, B, T, P_OBS, 25.0, 0.01, center=False)     # warm-up: workspace allocation (6.5 GB), first launch
+        dev.pca_setup(obs, B, T, P_OBS, 25.0, 0.01, center=False, workspace=ws_setup, mx_ready=True)     # warm-up: first launch
         torch.cuda.synchronize()
         s0.record()
-        prm_s, means_s, st_setup = dev.pca_setup(obs, B, T, P_OBS, 25.0, 0.01, center=False)
+        prm_s, means_s, st_setup = dev.pca_setup(obs, B, T, P_OBS, 25.0, 0.01, center=False, workspace=ws_setup, mx_ready=True)
         s1.record(); torch.cuda.synchronize()
         sms = s0.elapsed_time(s1)
-        sb = 2 * P_OBS * es                                        # y and the ensemble variances, read once
-        setup = {"kernel": "pca_setup (percentile select + masked moments + PCA; centring fused into kf_forward)", "ms": sms,
+        sb = (P_OBS + 1) * es                                      # y and max_vars (written by the ensemble kernel), read once
+        setup = {"kernel": "pca_setup (percentile select + masked moments + PCA; max_vars from ensemble_tiled, centring fused into kf_forward)", "ms": sms,
                  "keypoint_frames_per_s": tf / (sms * 1e-3), "achieved_gbs": tf * sb / (sms * 1e-3) / 1e9,
                  "frac": tf * sb / (sms * 1e-3) / 1e9 / peak, "failed_tracks": int(st_setup.sum())}
         launches += 48

@@ -82,7 +82,8 @@ __global__ void __launch_bounds__(256) ensemble_kernel(const T* __restrict__ pre
 // written row is a full 32-lane line.
 template <typename T, int M, int P>
 __global__ void __launch_bounds__(256) ensemble_tiled_kernel(const T* __restrict__ preds, long Tn, long B, int mode,
-                                                             const T* __restrict__ offset, T* __restrict__ obs) {
+                                                             const T* __restrict__ offset, T* __restrict__ obs,
+                                                             T* __restrict__ mxout /* [tile][t][32] or null */) {
   constexpr int kFramesPerCta = 64;
   const long nchunk = (Tn + kFramesPerCta - 1) / kFramesPerCta;
   const long g = blockIdx.x / nchunk;
@@ -97,6 +98,7 @@ __global__ void __launch_bounds__(256) ensemble_tiled_kernel(const T* __restrict
     const long t = t0 + f;
     if (t >= Tn) break;
     T* rec = obs + ((g * Tn + t) * (2 * P)) * kLanes + lane;
+    T mxv = T(1);                              // max over the P ensemble variances of this frame (padding lanes: ev = 1)
     if (b < B) {
       T v[P][M];
 #pragma unroll
@@ -111,11 +113,15 @@ __global__ void __launch_bounds__(256) ensemble_tiled_kernel(const T* __restrict
         reduce_models<T, M>(v[j], mode, a, s);
         rec[j * kLanes] = a - off[j];
         rec[(P + j) * kLanes] = s;
+        mxv = (j == 0) ? s : (s > mxv ? s : mxv);
       }
     } else {
 #pragma unroll
       for (int j = 0; j < P; ++j) { rec[j * kLanes] = T(0); rec[(P + j) * kLanes] = T(1); }
     }
+    // the parameter setup's first pass (eksb_setup.cu setup_mx_kernel: max_vars, -0.0 -> +0.0) done while the
+    // variances are in registers: 1 row written instead of P rows read back
+    if (mxout) mxout[(g * Tn + t) * kLanes + lane] = mxv + T(0);
   }
 }
 
@@ -143,24 +149,25 @@ static int ensemble_api(const T* preds, int M, long Tn, long K, int mode, T* avg
 }
 
 template <typename T, int M>
-static int launch_ensemble_tiled(const T* preds, long Tn, long B, int p, int mode, const T* offset, T* obs, cudaStream_t st) {
+static int launch_ensemble_tiled(const T* preds, long Tn, long B, int p, int mode, const T* offset, T* obs, T* mx, cudaStream_t st) {
   const unsigned grid = (unsigned)(((Tn + 63) / 64) * num_tiles(B));
   switch (p) {
-    case 4: ensemble_tiled_kernel<T, M, 4><<<grid, 256, 0, st>>>(preds, Tn, B, mode, offset, obs); break;
-    case 6: ensemble_tiled_kernel<T, M, 6><<<grid, 256, 0, st>>>(preds, Tn, B, mode, offset, obs); break;
-    case 8: ensemble_tiled_kernel<T, M, 8><<<grid, 256, 0, st>>>(preds, Tn, B, mode, offset, obs); break;
+    case 4: ensemble_tiled_kernel<T, M, 4><<<grid, 256, 0, st>>>(preds, Tn, B, mode, offset, obs, mx); break;
+    case 6: ensemble_tiled_kernel<T, M, 6><<<grid, 256, 0, st>>>(preds, Tn, B, mode, offset, obs, mx); break;
+    case 8: ensemble_tiled_kernel<T, M, 8><<<grid, 256, 0, st>>>(preds, Tn, B, mode, offset, obs, mx); break;
     default: set_error("ensemble_tiled: p=%d not in {4,6,8}", p); return EKSB_EDIM;
   }
   return check_launch("ensemble_tiled_kernel");
 }
 
 template <typename T>
-static int ensemble_tiled_api(const T* preds, int M, long Tn, long B, int p, int mode, const T* offset, T* obs, void* stream) {
+static int ensemble_tiled_api(const T* preds, int M, long Tn, long B, int p, int mode, const T* offset, T* obs, void* stream,
+                              T* mx = nullptr) {
   if (!preds || !obs || Tn <= 0 || B <= 0) { set_error("ensemble_tiled: bad argument"); return EKSB_EARG; }
   if (mode != EKSB_MODE_MEDIAN && mode != EKSB_MODE_MEAN) { set_error("ensemble_tiled: bad mode %d", mode); return EKSB_EARG; }
   cudaStream_t st = (cudaStream_t)stream;
   switch (M) {
-#define CASE(M_) case M_: return launch_ensemble_tiled<T, M_>(preds, Tn, B, p, mode, offset, obs, st);
+#define CASE(M_) case M_: return launch_ensemble_tiled<T, M_>(preds, Tn, B, p, mode, offset, obs, mx, st);
     CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
 #undef CASE
     default: set_error("ensemble_tiled: M=%d outside 1..8", M); return EKSB_EDIM;
@@ -184,4 +191,13 @@ extern "C" int eksb_ensemble_tiled_f64(const double* preds, int M, long T, long 
 extern "C" int eksb_ensemble_tiled_f32(const float* preds, int M, long T, long B, int p, int mode, const float* offset,
                                        float* obs, void* stream) {
   return ensemble_tiled_api<float>(preds, M, T, B, p, mode, offset, obs, stream);
+}
+
+extern "C" int eksb_ensemble_tiled_mx_f64(const double* preds, int M, long T, long B, int p, int mode, const double* offset,
+                                          double* obs, double* max_var, void* stream) {
+  return ensemble_tiled_api<double>(preds, M, T, B, p, mode, offset, obs, stream, max_var);
+}
+extern "C" int eksb_ensemble_tiled_mx_f32(const float* preds, int M, long T, long B, int p, int mode, const float* offset,
+                                          float* obs, float* max_var, void* stream) {
+  return ensemble_tiled_api<float>(preds, M, T, B, p, mode, offset, obs, stream, max_var);
 }

@@ -564,7 +564,7 @@ center_rows_kernel(T* __restrict__ rec, const T* __restrict__ means, long B, lon
 
 template <typename T, int P>
 static int setup_run(T* obs, long B, long Tn, int n, double q, double s, int center, T* means, T* C, T* S0, T* Q,
-                     double* ws, int* status, cudaStream_t st) {
+                     double* ws, int* status, cudaStream_t st, int mx_ready) {
   using Key = typename KeyOf<T>::type;
   static_assert(MomRows<P>::ROWS == mom_rows<P>(), "workspace row count");
   if (n != 3) { set_error("pca_setup: n=%d (the reference fits 3 components)", n); return EKSB_EDIM; }
@@ -591,7 +591,8 @@ static int setup_run(T* obs, long B, long Tn, int n, double q, double s, int cen
   const bool collect = collect_after < npass;
   if (collect) cudaMemsetAsync(cand, 0xFF, (size_t)tiles * kCandCap * kLanes * sizeof(T), st);   // all-ones key = empty slot
   setup_init_state_kernel<<<(unsigned)tiles, kLanes, 0, st>>>(state, lo);
-  setup_mx_kernel<T, P><<<(unsigned)((tiles * Tn + 7) / 8), 256, 0, st>>>(obs, tiles, Tn, mx);
+  if (!mx_ready)     // else the ensemble kernel wrote max_vars into the workspace already (eksb_ensemble_tiled_mx)
+    setup_mx_kernel<T, P><<<(unsigned)((tiles * Tn + 7) / 8), 256, 0, st>>>(obs, tiles, Tn, mx);
   for (int pass = 0; pass < npass; ++pass) {
     const int shift = 8 * (npass - 1 - pass);
     unsigned int* gh = ghist + (size_t)pass * tiles * 256 * kLanes;
@@ -616,15 +617,15 @@ static int setup_run(T* obs, long B, long Tn, int n, double q, double s, int cen
 
 template <typename T>
 static int setup_api(T* obs, long B, long Tn, int n, int p, double q, double s, int center, T* means, T* C, T* S0, T* Q,
-                     double* ws, size_t ws_bytes, int* status, void* stream) {
+                     double* ws, size_t ws_bytes, int* status, void* stream, int mx_ready = 0) {
   if (!obs || !means || !C || !S0 || !Q || !ws || B <= 0 || Tn <= 1) { set_error("pca_setup: null pointer or empty batch"); return EKSB_EARG; }
   if (!(q >= 0.0 && q <= 100.0)) { set_error("pca_setup: quantile %g outside [0,100]", q); return EKSB_EARG; }
   if (ws_bytes < eksb_pca_setup_workspace_bytes(B, Tn, p, (int)sizeof(T))) { set_error("pca_setup: workspace too small"); return EKSB_EARG; }
   cudaStream_t st = (cudaStream_t)stream;
   switch (p) {
-    case 4: return setup_run<T, 4>(obs, B, Tn, n, q, s, center, means, C, S0, Q, ws, status, st);
-    case 6: return setup_run<T, 6>(obs, B, Tn, n, q, s, center, means, C, S0, Q, ws, status, st);
-    case 8: return setup_run<T, 8>(obs, B, Tn, n, q, s, center, means, C, S0, Q, ws, status, st);
+    case 4: return setup_run<T, 4>(obs, B, Tn, n, q, s, center, means, C, S0, Q, ws, status, st, mx_ready);
+    case 6: return setup_run<T, 6>(obs, B, Tn, n, q, s, center, means, C, S0, Q, ws, status, st, mx_ready);
+    case 8: return setup_run<T, 8>(obs, B, Tn, n, q, s, center, means, C, S0, Q, ws, status, st, mx_ready);
   }
   set_error("pca_setup: p=%d not instantiated (4, 6, 8)", p);
   return EKSB_EDIM;
@@ -647,4 +648,21 @@ extern "C" int eksb_pca_setup_f32(float* obs, long B, long T, int n, int p, doub
                                   int center, float* means, float* C, float* S0, float* Q, double* workspace,
                                   size_t workspace_bytes, int* status, void* stream) {
   return setup_api<float>(obs, B, T, n, p, quantile, smooth_param, center, means, C, S0, Q, workspace, workspace_bytes, status, stream);
+}
+
+/* max_vars produced by eksb_ensemble_tiled_mx: the buffer lives inside the setup workspace at this byte offset
+ * ([tile][t][32] scalars of the obs type); pass mx_ready = 1 and the setup skips its own first pass. */
+extern "C" size_t eksb_pca_setup_mx_offset_bytes(long B, long T, int p, int elem_size) {
+  if (B <= 0 || T <= 0 || p <= 0 || (elem_size != 4 && elem_size != 8)) return 0;
+  return setup_layout(B, T, p, elem_size).mx * 8;
+}
+extern "C" int eksb_pca_setup_mx_f64(double* obs, long B, long T, int n, int p, double quantile, double smooth_param,
+                                     int center, int mx_ready, double* means, double* C, double* S0, double* Q,
+                                     double* workspace, size_t workspace_bytes, int* status, void* stream) {
+  return setup_api<double>(obs, B, T, n, p, quantile, smooth_param, center, means, C, S0, Q, workspace, workspace_bytes, status, stream, mx_ready);
+}
+extern "C" int eksb_pca_setup_mx_f32(float* obs, long B, long T, int n, int p, double quantile, double smooth_param,
+                                     int center, int mx_ready, float* means, float* C, float* S0, float* Q,
+                                     double* workspace, size_t workspace_bytes, int* status, void* stream) {
+  return setup_api<float>(obs, B, T, n, p, quantile, smooth_param, center, means, C, S0, Q, workspace, workspace_bytes, status, stream, mx_ready);
 }

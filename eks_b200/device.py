@@ -176,17 +176,38 @@ def ensemble(preds, mode="median"):
     return avg, var
 
 
-def ensemble_tiled(preds, B, p, mode="median", offset=None, out=None):
-    """preds (M,T,B*p) -> obs records, y = avg - offset (offset (B,p) or None)."""
+def ensemble_tiled(preds, B, p, mode="median", offset=None, out=None, max_var=None):
+    """preds (M,T,B*p) -> obs records, y = avg - offset (offset (B,p) or None).
+    max_var: optional [tile][T][32] buffer (setup_max_var_view) that receives max_j ev[t,j] for pca_setup(mx_ready=True)."""
     md = _mode(mode)
     _need_cuda(preds, "preds")
     M, T, K = preds.shape
     if K != B * p:
         raise ValueError("preds last dim must be B*p")
     obs = out if out is not None else alloc_records(B, T, 2 * p, preds.dtype, preds.device)
+    if max_var is not None:
+        fn = getattr(lib(), f"eksb_ensemble_tiled_mx_{_sfx(preds.dtype)}")
+        check(fn(_ptr(preds), M, T, B, p, md, _ptr(offset), _ptr(obs), _ptr(max_var), _stream(preds.device)),
+              "eksb_ensemble_tiled_mx")
+        return obs
     fn = getattr(lib(), f"eksb_ensemble_tiled_{_sfx(preds.dtype)}")
     check(fn(_ptr(preds), M, T, B, p, md, _ptr(offset), _ptr(obs), _stream(preds.device)), "eksb_ensemble_tiled")
     return obs
+
+
+def setup_workspace(B, T, p, dtype, device):
+    """Workspace of pca_setup, allocated up front so that ensemble_tiled can write max_vars into it."""
+    es = torch.empty(0, dtype=dtype).element_size()
+    nbytes = lib().eksb_pca_setup_workspace_bytes(B, T, p, es)
+    return torch.empty(max(1, nbytes // 8), dtype=torch.float64, device=device)
+
+
+def setup_max_var_view(ws, B, T, p, dtype):
+    """The max_vars region of a pca_setup workspace as a flat [tile][T][32] tensor of the obs dtype."""
+    es = torch.empty(0, dtype=dtype).element_size()
+    off = lib().eksb_pca_setup_mx_offset_bytes(B, T, p, es)
+    n = num_tiles(B) * T * 32
+    return ws.view(torch.uint8)[off:off + n * es].view(dtype)
 
 
 # ------------------------------------------------------------------ view alignment
@@ -204,7 +225,7 @@ def interp_rows(ts_src, src, ts_q, flip=None):
 
 
 # ------------------------------------------------------------------ K8 parameter setup on the device
-def pca_setup(obs, B, T, p, quantile, smooth_param, n=3, center=True, status=None):
+def pca_setup(obs, B, T, p, quantile, smooth_param, n=3, center=True, status=None, workspace=None, mx_ready=False):
     """Per-track (means, C, S0, Q) of the multi-camera smoother from UNcentred obs records
     (multiview_pca_smoother.py:684-731); with center=True the y rows of `obs` are centred in place.
     Returns (TrackParams with m0 = 0, A = I, means (B,p) tensor, status (B,) int32)."""
@@ -215,12 +236,16 @@ def pca_setup(obs, B, T, p, quantile, smooth_param, n=3, center=True, status=Non
     S0 = torch.empty((B, n, n), dtype=dt, device=dev)
     Q = torch.empty((B, n, n), dtype=dt, device=dev)
     nbytes = lib().eksb_pca_setup_workspace_bytes(B, T, p, obs.element_size())
-    ws = torch.empty(max(1, nbytes // 8), dtype=torch.float64, device=dev)
+    if mx_ready and workspace is None:
+        raise ValueError("mx_ready needs the workspace ensemble_tiled wrote max_vars into")
+    ws = workspace if workspace is not None else torch.empty(max(1, nbytes // 8), dtype=torch.float64, device=dev)
+    if ws.numel() * 8 < nbytes:
+        raise ValueError("pca_setup workspace too small")
     if status is None:
         status = torch.zeros(B, dtype=torch.int32, device=dev)
-    fn = getattr(lib(), f"eksb_pca_setup_{_sfx(dt)}")
-    check(fn(_ptr(obs), B, T, n, p, float(quantile), float(smooth_param), int(bool(center)), _ptr(means), _ptr(C),
-             _ptr(S0), _ptr(Q), _ptr(ws), nbytes, _ptr(status), _stream(dev)), "eksb_pca_setup")
+    fn = getattr(lib(), f"eksb_pca_setup_mx_{_sfx(dt)}")
+    check(fn(_ptr(obs), B, T, n, p, float(quantile), float(smooth_param), int(bool(center)), int(bool(mx_ready)),
+             _ptr(means), _ptr(C), _ptr(S0), _ptr(Q), _ptr(ws), nbytes, _ptr(status), _stream(dev)), "eksb_pca_setup")
     prm = TrackParams(torch.zeros(n, dtype=dt, device=dev), S0, C, torch.eye(n, dtype=dt, device=dev), Q,
                       a_mode=_lib.A_DIAG)
     return prm, means, status

@@ -122,8 +122,10 @@ def smooth_session_multi_cam(stack, smooth_param, quantile_keep_pca, newton=Fals
     t = stack if isinstance(stack, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(stack))
     M, T, B, p = t.shape
     preds = t.to(device=d, dtype=dtype).reshape(M, T, B * p).contiguous()
-    obs = dev.ensemble_tiled(preds, B, p, "median")
-    prm, means, status = dev.pca_setup(obs, B, T, p, quantile_keep_pca, smooth_param, n=3, center=False)
+    ws = dev.setup_workspace(B, T, p, dtype, d)                       # the ensemble kernel leaves max_vars in it
+    obs = dev.ensemble_tiled(preds, B, p, "median", max_var=dev.setup_max_var_view(ws, B, T, p, dtype))
+    prm, means, status = dev.pca_setup(obs, B, T, p, quantile_keep_pca, smooth_param, n=3, center=False,
+                                       workspace=ws, mx_ready=True)
     sg = dev.sigma(3)
     if newton:
         filt, _, st2 = dev.kf_forward(obs, prm, B, T, first=_lib.FIRST_PRIOR_ONLY, status=status, y_offset=means)

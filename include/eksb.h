@@ -255,6 +255,22 @@ EKSB_API int eksb_pca_setup_f32(float* obs, long B, long T, int n, int p, double
                        float* means, float* C, float* S0, float* Q, double* workspace, size_t workspace_bytes,
                        int* status, void* stream);
 
+/* Ensemble -> setup hand-over of max_vars (max over the p ensemble variances of a frame, :686): the ensemble kernel
+ * has them in registers, so eksb_ensemble_tiled_mx also writes that row ([tile][t][32]) -- straight into the setup
+ * workspace at eksb_pca_setup_mx_offset_bytes(...) -- and eksb_pca_setup_mx with mx_ready = 1 skips its own first pass
+ * over the records (p rows read per track-frame).  max_var may be NULL; mx_ready = 0 is plain eksb_pca_setup. */
+EKSB_API int eksb_ensemble_tiled_mx_f64(const double* preds, int M, long T, long B, int p, int mode, const double* offset,
+                        double* obs, double* max_var, void* stream);
+EKSB_API int eksb_ensemble_tiled_mx_f32(const float* preds, int M, long T, long B, int p, int mode, const float* offset,
+                        float* obs, float* max_var, void* stream);
+EKSB_API size_t eksb_pca_setup_mx_offset_bytes(long B, long T, int p, int elem_size);
+EKSB_API int eksb_pca_setup_mx_f64(double* obs, long B, long T, int n, int p, double quantile, double smooth_param,
+                        int center, int mx_ready, double* means, double* C, double* S0, double* Q, double* workspace,
+                        size_t workspace_bytes, int* status, void* stream);
+EKSB_API int eksb_pca_setup_mx_f32(float* obs, long B, long T, int n, int p, double quantile, double smooth_param,
+                        int center, int mx_ready, float* means, float* C, float* S0, float* Q, double* workspace,
+                        size_t workspace_bytes, int* status, void* stream);
+
 /* ---- asynchronous-view alignment (multiview_pca_smoother.py:70-101) -----------------
  * out[s][q][j] = linear interpolation of series s (src (S,Ts,K) row-major, sampled at the increasing times
  * ts_src (Ts)) at query time ts_q[q], with scipy interp1d's arithmetic (slope * (x - x_lo) + y_lo, no FMA:

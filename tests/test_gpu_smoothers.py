@@ -148,6 +148,29 @@ def test_percentile_select_candidate_buffer_and_overflow_fallback(dtname, rtol, 
             np.testing.assert_allclose(res["collect"][0][b].cpu().double().numpy(), yt[b].double().numpy()[good].mean(axis=0), rtol=rtol)
 
 
+@pytest.mark.parametrize("dtname", ["float64", "float32"])
+@pytest.mark.parametrize("B,T,p", [(37, 333, 6), (70, 900, 4)])
+def test_max_vars_from_the_ensemble_kernel_equal_the_setup_pass(dtname, B, T, p):
+    """eksb_ensemble_tiled_mx writes max_j ev[t,j] into the setup workspace while the variances are in registers;
+    eksb_pca_setup_mx(mx_ready=1) then skips its own pass: same records, same parameters, bit for bit."""
+    import torch
+    from eks_b200 import device as dev
+    dt = getattr(torch, dtname)
+    stack = _synthetic_session(B, T, p, seed=3 * B + T)
+    d = torch.device("cuda", 0)
+    preds = torch.as_tensor(np.ascontiguousarray(stack.reshape(5, T, B * p)), dtype=dt).to(d)
+    obs0 = dev.ensemble_tiled(preds, B, p, "median")
+    ref = dev.pca_setup(obs0.clone(), B, T, p, 25, 0.01, center=False)
+    ws = dev.setup_workspace(B, T, p, dt, d)
+    obs1 = dev.ensemble_tiled(preds, B, p, "median", max_var=dev.setup_max_var_view(ws, B, T, p, dt))
+    assert torch.equal(obs0, obs1)
+    got = dev.pca_setup(obs1, B, T, p, 25, 0.01, center=False, workspace=ws, mx_ready=True)
+    assert int(got[2].sum()) == 0
+    assert torch.equal(got[1], ref[1])
+    for a, b in ((got[0].C, ref[0].C), (got[0].S0, ref[0].S0), (got[0].Q, ref[0].Q)):
+        assert torch.equal(a, b)
+
+
 def test_session_entry_equals_per_keypoint_calls():
     """All mirror-mouse keypoints in one batched session call == the per-keypoint drop-in == shipped CSVs."""
     from eks_b200.multiview_pca_smoother import smooth_session_multi_cam, session_dfs
