@@ -84,4 +84,5 @@ SHARED_M0, SHARED_S0, SHARED_C, SHARED_A, SHARED_Q, SHARED_ALL = 1, 2, 4, 8, 16,
 A_DIAG, A_DENSE = 0, 1
 MODE_MEDIAN, MODE_MEAN = 0, 1
 FIRST_PRIOR_UPDATE, FIRST_PRIOR_ONLY = 1, 2
+STATUS_PIVOT, STATUS_NONPOS_VAR = 1, 2
 SUPPORTED_DIMS = ((2, 4), (3, 4), (3, 6), (3, 8), (4, 6), (6, 8))

@@ -38,6 +38,12 @@ int rts_backward_pipe(const T* filt, const T* C, const T* A, const T* Q, int sha
 bool use_pipe(long B);
 long pipe_groups(long tiles, int elem_size);   // number of launches a batch of `tiles` tiles is split into
 
+// Per-track status word: bits are OR-ed in (several warps / launches may report on the same track).
+__device__ __forceinline__ void set_status(int* st, bool ok, bool nonpos_var) {
+  const int bits = (ok ? 0 : kStatusPivot) | (nonpos_var ? kStatusNonPosVar : 0);
+  if (bits) atomicOr(st, bits);
+}
+
 // Device-side gather of one track's parameters into registers.
 template <typename T, int N, int P, int AM>
 __device__ __forceinline__ void load_track_params(Params<T, N, P, AM>& prm, const T* C, const T* A, const T* Q,

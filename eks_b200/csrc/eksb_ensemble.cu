@@ -76,6 +76,35 @@ __global__ void __launch_bounds__(256) ensemble_kernel(const T* __restrict__ pre
   }
 }
 
+// Any ensemble size up to kMaxModels (runtime M; values in local memory, insertion sort): the reference takes any
+// number of models (eks/ensemble_kalman.py:41-46).  Same summation order and rounding as reduce_models.
+constexpr int kMaxModels = 64;
+template <typename T>
+__global__ void __launch_bounds__(256) ensemble_anym_kernel(const T* __restrict__ preds, int M, long TK, int mode,
+                                                            T* __restrict__ avg, T* __restrict__ var) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < TK; i += stride) {
+    T v[kMaxModels];
+    bool has_nan = false;
+    for (int m = 0; m < M; ++m) { v[m] = preds[(long)m * TK + i]; has_nan = has_nan || (v[m] != v[m]); }
+    T sum = v[0];
+    for (int m = 1; m < M; ++m) sum = add_rn(sum, v[m]);
+    const T mean = div_rn(sum, T(M));
+    T ss = T(0);
+    for (int m = 0; m < M; ++m) { const T d = add_rn(v[m], -mean); ss = add_rn(ss, mul_rn(d, d)); }
+    var[i] = div_rn(div_rn(ss, T(M)), T(M));
+    if (mode == EKSB_MODE_MEAN) { avg[i] = mean; continue; }
+    for (int a = 1; a < M; ++a) {
+      const T x = v[a];
+      int c = a - 1;
+      while (c >= 0 && x < v[c]) { v[c + 1] = v[c]; --c; }
+      v[c + 1] = x;
+    }
+    const T med = (M & 1) ? v[M / 2] : mul_rn(add_rn(v[(M - 1) / 2], v[M / 2]), T(0.5));
+    avg[i] = has_nan ? quiet_nan<T>() : med;
+  }
+}
+
 // Fused restack: column k = b*P + j.  A CTA of 256 threads handles one frame-chunk of one
 // track tile: thread (w, lane) walks frames w, w+8, ... and all P observation rows of track
 // 32 g + lane... reads of one frame row are contiguous over (lane, j) = 32*P scalars, and each
@@ -144,8 +173,13 @@ static int ensemble_api(const T* preds, int M, long Tn, long K, int mode, T* avg
     CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8) CASE(9) CASE(10) CASE(11) CASE(12)
     CASE(13) CASE(14) CASE(15) CASE(16)
 #undef CASE
-    default: set_error("ensemble: M=%d outside 1..16", M); return EKSB_EDIM;
+    default: break;
   }
+  if (M < 1 || M > kMaxModels) { set_error("ensemble: M=%d outside 1..%d", M, kMaxModels); return EKSB_EDIM; }
+  long blocks = (Tn * K + 255) / 256;
+  if (blocks > 148L * 64) blocks = 148L * 64;
+  ensemble_anym_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(preds, M, Tn * K, mode, avg, var);
+  return check_launch("ensemble_anym_kernel");
 }
 
 template <typename T, int M>

@@ -142,7 +142,95 @@ kf_forward_generic_kernel(const T* __restrict__ obs, const T* m0, const T* S0, c
     for (int i = 0; i < n; ++i)
       for (int j = i; j < n; ++j) f[(t * sg + n + kk++) * kLanes] = T(0.5) * (V[i * n + j] + V[j * n + i]);
   }
-  if (b < B && status && !ok) status[b] = 1;
+  if (b < B && status) set_status(status + b, ok, false);
+}
+
+// RTS smoother, literal form (eks/ensemble_kalman.py:152-162), any n <= 8, p <= 16, dense A:
+//   J = solve(S[t], A Vf[t])^T (:158, LU with partial pivoting), Vs[t] = Vf[t] + J (Vs[t+1] - S[t]) J^T (:160),
+//   ms[t] = mf[t] + J (ms[t+1] - A mf[t]) (:161), CV[t] = Vs[t+1] J^T (:162).
+// pred (optional): NS-row packed records holding the caller's S[t] (the reference reads its S argument and never
+// touches Q); NULL recomputes S[t] = A Vf[t] A^T + Q, which is what filtering_pass stored there (:101).
+template <typename T>
+__global__ void __launch_bounds__(kLanes)
+rts_backward_generic_kernel(const T* filt, const T* __restrict__ pred, const T* C, const T* A, const T* Q, int shared_mask,
+                            long B, long Tn, int n, int p, T* smth, T* __restrict__ ym, T* __restrict__ yv,
+                            T* __restrict__ cv, int* status) {
+  const long g = blockIdx.x;
+  const int lane = threadIdx.x;
+  const long b = g * kLanes + lane;
+  const long bp = b < B ? b : B - 1;
+  const int ns = n * (n + 1) / 2, sg = n + ns;
+  const T* c = C + ((shared_mask & EKSB_SHARED_C) ? 0 : bp * p * n);
+  const T* a = A + ((shared_mask & EKSB_SHARED_A) ? 0 : bp * n * n);
+  const T* q = Q + ((shared_mask & EKSB_SHARED_Q) ? 0 : bp * n * n);
+  T m[kNMax], V[kNMax * kNMax], S[kNMax * kNMax], AV[kNMax * kNMax], J[kNMax * kNMax], W[kNMax * kNMax];
+  T ms[kNMax], Vs[kNMax * kNMax], ms1[kNMax], Vs1[kNMax * kNMax], mp[kNMax];
+  bool ok = true;
+  const T* f = filt + (g * Tn * sg) * kLanes + lane;
+  T* o = smth + (g * Tn * sg) * kLanes + lane;
+  auto unpack = [&](const T* rec, long t, int rows, int r0, T* full) {
+    int kk = 0;
+    for (int i = 0; i < n; ++i)
+      for (int j = i; j < n; ++j) { const T v = rec[(t * rows + r0 + kk++) * kLanes]; full[i * n + j] = v; full[j * n + i] = v; }
+  };
+  for (long t = Tn - 1; t >= 0; --t) {
+    for (int i = 0; i < n; ++i) m[i] = f[(t * sg + i) * kLanes];
+    unpack(f, t, sg, n, V);
+    if (t == Tn - 1) {                                       // :152-153
+      for (int i = 0; i < n; ++i) ms[i] = m[i];
+      for (int i = 0; i < n * n; ++i) Vs[i] = V[i];
+    } else {
+      for (int i = 0; i < n; ++i) { ms1[i] = ms[i]; T s = T(0); for (int l = 0; l < n; ++l) s += a[i * n + l] * m[l]; mp[i] = s; }
+      for (int i = 0; i < n * n; ++i) Vs1[i] = Vs[i];
+      for (int i = 0; i < n; ++i)
+        for (int j = 0; j < n; ++j) { T s = T(0); for (int l = 0; l < n; ++l) s += a[i * n + l] * V[l * n + j]; AV[i * n + j] = s; }
+      if (pred) {
+        unpack(pred + (g * Tn * ns) * kLanes + lane, t, ns, 0, S);
+      } else {
+        for (int i = 0; i < n; ++i)
+          for (int j = 0; j < n; ++j) { T s = q[i * n + j]; for (int l = 0; l < n; ++l) s += AV[i * n + l] * a[j * n + l]; S[i * n + j] = s; }
+      }
+      for (int i = 0; i < n * n; ++i) { W[i] = S[i]; J[i] = AV[i]; }
+      ok = lu_solve(W, n, J, n, n, n) && ok;                 // J <- S^-1 (A V);  the gain is its transpose
+      // D = Vs1 - S ;  Vs = V + J^T' ... with G = J^T: Vs = V + G D G^T, ms = m + G (ms1 - mp), CV = Vs1 G^T
+      for (int i = 0; i < n; ++i)
+        for (int j = 0; j < n; ++j) {                        // W = G D,  G[i][l] = J[l][i]
+          T s = T(0);
+          for (int l = 0; l < n; ++l) s += J[l * n + i] * (Vs1[l * n + j] - S[l * n + j]);
+          W[i * n + j] = s;
+        }
+      for (int i = 0; i < n; ++i) {
+        for (int j = 0; j < n; ++j) { T s = V[i * n + j]; for (int l = 0; l < n; ++l) s += W[i * n + l] * J[l * n + j]; Vs[i * n + j] = s; }
+        T s = m[i];
+        for (int l = 0; l < n; ++l) s += J[l * n + i] * (ms1[l] - mp[l]);
+        ms[i] = s;
+      }
+      if (cv)
+        for (int i = 0; i < n; ++i)
+          for (int j = 0; j < n; ++j) {                      // CV = Vs1 G^T = Vs1 J
+            T s = T(0);
+            for (int l = 0; l < n; ++l) s += Vs1[i * n + l] * J[l * n + j];
+            cv[((g * Tn + t) * (n * n) + i * n + j) * kLanes + lane] = s;
+          }
+    }
+    for (int i = 0; i < n; ++i) o[(t * sg + i) * kLanes] = ms[i];
+    int kk = 0;
+    for (int i = 0; i < n; ++i)
+      for (int j = i; j < n; ++j) o[(t * sg + n + kk++) * kLanes] = T(0.5) * (Vs[i * n + j] + Vs[j * n + i]);
+    if (ym || yv)
+      for (int j = 0; j < p; ++j) {
+        T s = T(0), qv = T(0);
+        for (int i = 0; i < n; ++i) {
+          s += c[j * n + i] * ms[i];
+          T acc = T(0);
+          for (int l = 0; l < n; ++l) acc += Vs[i * n + l] * c[j * n + l];
+          qv += c[j * n + i] * acc;
+        }
+        if (ym) ym[((g * Tn + t) * p + j) * kLanes + lane] = s;
+        if (yv) yv[((g * Tn + t) * p + j) * kLanes + lane] = qv;
+      }
+  }
+  if (b < B && status) set_status(status + b, ok, false);
 }
 
 template <typename T>
@@ -167,9 +255,30 @@ static int kf_forward_generic_api(const T* obs, const T* m0, const T* S0, const 
   return check_launch("kf_forward_generic_kernel");
 }
 
+template <typename T>
+static int rts_backward_generic_api(const T* filt, const T* pred, const T* C, const T* A, const T* Q, int shared_mask, long B,
+                                    long Tn, int n, int p, T* smth, T* ym, T* yv, T* cv, int* status, void* stream) {
+  if (!filt || !smth || !C || !A || !Q || B <= 0 || Tn <= 0) { set_error("rts_backward_generic: bad argument"); return EKSB_EARG; }
+  if (n < 1 || p < 1 || n > kNMax || p > kPMax) { set_error("rts_backward_generic: need n<=%d, p<=%d", kNMax, kPMax); return EKSB_EDIM; }
+  rts_backward_generic_kernel<T><<<(unsigned)num_tiles(B), kLanes, 0, (cudaStream_t)stream>>>(
+      filt, pred, C, A, Q, shared_mask, B, Tn, n, p, smth, ym, yv, cv, status);
+  return check_launch("rts_backward_generic_kernel");
+}
+
 }  // namespace eksb
 
 using namespace eksb;
+
+extern "C" int eksb_rts_backward_generic_f64(const double* filt, const double* pred, const double* C, const double* A,
+                                             const double* Q, int shared_mask, long B, long T, int n, int p, double* smth,
+                                             double* ym, double* yv, double* cv, int* status, void* stream) {
+  return rts_backward_generic_api<double>(filt, pred, C, A, Q, shared_mask, B, T, n, p, smth, ym, yv, cv, status, stream);
+}
+extern "C" int eksb_rts_backward_generic_f32(const float* filt, const float* pred, const float* C, const float* A,
+                                             const float* Q, int shared_mask, long B, long T, int n, int p, float* smth,
+                                             float* ym, float* yv, float* cv, int* status, void* stream) {
+  return rts_backward_generic_api<float>(filt, pred, C, A, Q, shared_mask, B, T, n, p, smth, ym, yv, cv, status, stream);
+}
 
 extern "C" int eksb_kalman_dot_f64(const double* array, int k, const double* V, const double* C, const double* R, int n,
                                    int p, double* out, int* status, void* stream) {

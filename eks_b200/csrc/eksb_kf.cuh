@@ -61,11 +61,12 @@ kf_forward_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* 
   T mu[P];                                 // optional per-track observation offset (camera means): y - mu, like the pipelined kernels
 #pragma unroll
   for (int j = 0; j < P; ++j) mu[j] = yoff ? yoff[bp * P + j] : T(0);
+  bool nonpos = false;
   ok = kf_forward_range_ring<T, N, P, AM, NLL>(prm, o, f, Tn, first, m, V, reinterpret_cast<T*>(kf_smem) + lane, &acc,
-                                               yoff ? mu : nullptr) && ok;
+                                               yoff ? mu : nullptr, &nonpos) && ok;
   if (b < B) {
     if (NLL) nll[(long)blockIdx.y * B + b] = 0.5 * (acc + (double)Tn * P * 1.8378770664093453 /* log 2pi */);
-    if (status && !ok) status[b] = 1;
+    if (status) set_status(status + b, ok, nonpos);
   }
 }
 
@@ -87,7 +88,7 @@ rts_backward_kernel(const T* filt, const T* __restrict__ C, const T* __restrict_
   bool ok = rts_backward_range<T, N, P, AM, kLanes, Prefetch<T, Dim<N>::SIGMA>::value>(
       prm, filt + base * SG + lane, smth + base * SG + lane, ym ? ym + base * P + lane : nullptr,
       yv ? yv + base * P + lane : nullptr, cv ? cv + base * (N * N) + lane : nullptr, Tn, true, ms, Vs);
-  if (b < B && status && !ok) status[b] = 1;
+  if (b < B && status) set_status(status + b, ok, false);
 }
 
 template <typename T, int N, int P>

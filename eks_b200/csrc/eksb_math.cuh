@@ -411,6 +411,19 @@ EKSB_HD double update(const Params<T, N, P, AM>& prm, const T* y, const T* r, co
 // ---------------------------------------------------------------------------
 enum FirstFrame { kContinue = 0, kPriorUpdate = 1, kPriorOnly = 2 };
 
+// Per-track status bits (include/eksb.h): 1 = a non-positive pivot (the reference's LinAlgError), 2 = a frame with a
+// non-positive ensemble variance.  The information-form update divides by every variance, so such a track comes out
+// NaN where the reference (which only needs R + C S C^T to be invertible) stays finite: the fast kernels flag it and
+// the caller re-runs the track through the literal p x p LU kernel (eksb_kf_forward_generic).  NaN variances are NOT
+// flagged: the reference propagates them and so do the kernels.
+constexpr int kStatusPivot = 1, kStatusNonPosVar = 2;
+template <typename T, int P> EKSB_HD bool any_nonpos(const T* r) {
+  bool bad = false;
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) bad = bad || (r[j] <= T(0));
+  return bad;
+}
+
 // Forward filter over `n` frames.  (m,V) carries the state in and out:
 //   first == kPriorUpdate : (m,V) = (m0,S0), frame 0 is an update with no predict
 //                           (eks/ensemble_kalman.py:94-96);
@@ -419,7 +432,7 @@ enum FirstFrame { kContinue = 0, kPriorUpdate = 1, kPriorOnly = 2 };
 // filt may be null (NLL-only sweeps).  PF = software prefetch depth in frames.
 template <typename T, int N, int P, int AM, int LS, int PF, bool NLL>
 EKSB_HD bool kf_forward_range(const Params<T, N, P, AM>& prm, const T* __restrict__ obs, T* __restrict__ filt,
-                              long n, int first, T* m, T* V, double& nll) {
+                              long n, int first, T* m, T* V, double& nll, const T* mu = nullptr, bool* nonpos = nullptr) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
   bool ok = true;
   T buf[PF][R2];
@@ -441,6 +454,11 @@ EKSB_HD bool kf_forward_range(const Params<T, N, P, AM>& prm, const T* __restric
         EKSB_UNROLL
         for (int r = 0; r < R2; ++r) buf[k][r] = obs[(f * R2 + r) * LS];
         const bool is_first = (t + k == 0);
+        if (mu) {
+          EKSB_UNROLL
+          for (int j = 0; j < P; ++j) cur[j] -= mu[j];
+        }
+        if (nonpos && !(is_first && first == kPriorOnly)) *nonpos = *nonpos || any_nonpos<T, P>(cur + P);
         if (!(is_first && first == kPriorOnly)) {
           T mp[N], S[NS];
           if (is_first && first == kPriorUpdate) {
@@ -1280,9 +1298,10 @@ template <> struct ScanCut<float> { static constexpr float value = 1e-11f; };
 // is kf_forward_range with a register prefetch (host tests, re-run kernels); the summary kernels pass a variant that
 // stages the frames through shared memory (eksb_scan.cuh FwdTailRing) -- same arithmetic.
 template <typename T, int N, int P, int AM, int LS, int PF> struct FwdTailPlain {
-  EKSB_HD bool operator()(const Params<T, N, P, AM>& prm, const T* obs, T* filt, long n, T* m, T* V) const {
+  EKSB_HD bool operator()(const Params<T, N, P, AM>& prm, const T* obs, T* filt, long n, T* m, T* V, const T* mu,
+                          bool* nonpos) const {
     double acc = 0.0;
-    return kf_forward_range<T, N, P, AM, LS, PF, false>(prm, obs, filt, n, kContinue, m, V, acc);
+    return kf_forward_range<T, N, P, AM, LS, PF, false>(prm, obs, filt, n, kContinue, m, V, acc, mu, nonpos);
   }
 };
 template <typename T, int N, int P, int AM, int LS, int PF> struct BwdTailPlain {
@@ -1293,7 +1312,8 @@ template <typename T, int N, int P, int AM, int LS, int PF> struct BwdTailPlain 
 
 template <typename T, int N, int P, int AM, int LS, typename Tail>
 EKSB_HD long scan_fwd_chunk(const Params<T, N, P, AM>& prm, const T* __restrict__ obs, T* __restrict__ filt, long n,
-                            bool early_out, T* sum, bool& ok, const Tail& tail) {
+                            bool early_out, T* sum, bool& ok, const Tail& tail, const T* mu = nullptr,
+                            bool* nonpos = nullptr) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
   T Phi[N][N], bb[N], Cc[NS], eta[N], J[NS];
   EKSB_UNROLL
@@ -1316,6 +1336,11 @@ EKSB_HD long scan_fwd_chunk(const Params<T, N, P, AM>& prm, const T* __restrict_
     const long f = (t + 1 < n) ? t + 1 : n - 1;
     EKSB_UNROLL
     for (int r = 0; r < R2; ++r) nxt[r] = obs[(f * R2 + r) * LS];
+    if (mu) {
+      EKSB_UNROLL
+      for (int j = 0; j < P; ++j) cur[j] -= mu[j];
+    }
+    if (nonpos) *nonpos = *nonpos || any_nonpos<T, P>(cur + P);
     fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
     fwd_summary_step<T, N, P, AM>(prm, rec, Phi, bb, Cc, eta, J, ok);
     ++t;
@@ -1338,7 +1363,7 @@ EKSB_HD long scan_fwd_chunk(const Params<T, N, P, AM>& prm, const T* __restrict_
     }
     if (t < n) {
       if (early_out) cut = t;
-      ok = tail(prm, obs + t * R2 * LS, early_out ? filt + t * SG * LS : nullptr, n - t, bb, Cc) && ok;
+      ok = tail(prm, obs + t * R2 * LS, early_out ? filt + t * SG * LS : nullptr, n - t, bb, Cc, mu, nonpos) && ok;
     }
   }
   EKSB_UNROLL

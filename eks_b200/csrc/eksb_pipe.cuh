@@ -149,6 +149,7 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
     T mu[P];
 #pragma unroll
     for (int j = 0; j < P; ++j) mu[j] = yoff ? yoff[bp * P + j] : T(0);
+    bool nonpos = false;                                   // a frame with a non-positive ensemble variance (status bit 2)
     if (issuer) {
       for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
       mbar_fence_init();
@@ -183,6 +184,7 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
 #pragma unroll
               for (int q = 0; q < P; ++q) cur[q] -= mu[q];
             }
+            nonpos = nonpos || (any_nonpos<T, P>(cur + P) && !(first == kPriorOnly && k == 0 && j == 0));
             if constexpr (kOuter) fwd_prep_outer<T, N, P>(prm.C, CC, cur, cur + P, rec);
             else fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
 #pragma unroll
@@ -198,6 +200,7 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
         bulk_g2s(raw + (size_t)st * F * R2 * kLanes, gsrc + t0 * R2 * kLanes, bytes, &full[st]);
       }
     }
+    if (b < B && status) set_status(status + b, true, nonpos);
     return;
   }
 
@@ -271,7 +274,7 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
     f += F * SG * kLanes;
     tile_barrier(bar_id, bar_cnt);                         // batch k consumed / batch k+1 ready
   }
-  if (b < B && status && !ok) status[b] = 1;
+  if (b < B && status) set_status(status + b, ok, false);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -334,6 +337,7 @@ kf_forward_pipe3_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
     T mu[P];                                               // optional per-track observation offset, as in the two-role kernel
 #pragma unroll
     for (int j = 0; j < P; ++j) mu[j] = yoff ? yoff[bp * P + j] : T(0);
+    bool nonpos = false;                                   // a frame with a non-positive ensemble variance (status bit 2)
     if (issuer) {
       for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
       mbar_fence_init();
@@ -367,6 +371,7 @@ kf_forward_pipe3_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
 #pragma unroll
               for (int q = 0; q < P; ++q) cur[q] -= mu[q];
             }
+            nonpos = nonpos || (any_nonpos<T, P>(cur + P) && !(first == kPriorOnly && k == 0 && j == 0));
             if constexpr (kOuter) fwd_prep_outer<T, N, P>(prm.C, CC, cur, cur + P, rec);
             else fwd_prep<T, N, P, 0>(prm, cur, cur + P, rec);
 #pragma unroll
@@ -382,6 +387,7 @@ kf_forward_pipe3_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
         bulk_g2s(raw + (size_t)st * F * R2 * kLanes, gsrc + t0 * R2 * kLanes, bytes, &full[st]);
       }
     }
+    if (b < B && status) set_status(status + b, true, nonpos);
     return;
   }
 
@@ -433,7 +439,7 @@ kf_forward_pipe3_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
       }
       tile_barrier(bar_id, bar_cnt);
     }
-    if (b < B && status && !ok) status[b] = 1;
+    if (b < B && status) set_status(status + b, ok, false);
     return;
   }
 
@@ -593,7 +599,7 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
         bulk_g2s(raw + (size_t)st * F * SG * kLanes, gsrc + t_lo * SG * kLanes, (uint32_t)nfr * kFrameBytes, &full[st]);
       }
     }
-    if (b < B && status && !ok) status[b] = 1;
+    if (b < B && status) set_status(status + b, ok, false);
     return;
   }
 

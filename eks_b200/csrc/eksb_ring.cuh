@@ -33,7 +33,8 @@ template <typename T, int ROWS> __host__ __device__ constexpr size_t ring_bytes_
 template <typename T, int N, int P, int AM, bool NLL = false>
 __device__ bool kf_forward_range_ring(const Params<T, N, P, AM>& prm, const T* __restrict__ obs, T* __restrict__ filt,
                                       long n, int first, T* m, T* V, T* ring, double* nll = nullptr,
-                                      const T* mu = nullptr /* P per-track observation offsets in registers, or null */) {
+                                      const T* mu = nullptr /* P per-track observation offsets in registers, or null */,
+                                      bool* nonpos = nullptr /* set when a frame has a non-positive ensemble variance */) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, D = kRingDepth;
   bool ok = true;
 #pragma unroll
@@ -55,6 +56,7 @@ __device__ bool kf_forward_range_ring(const Params<T, N, P, AM>& prm, const T* _
       for (int j = 0; j < P; ++j) cur[j] -= mu[j];
     }
     const bool is_first = (t == 0);
+    if (nonpos && !(is_first && first == kPriorOnly)) *nonpos = *nonpos || any_nonpos<T, P>(cur + P);
     if (!(is_first && first == kPriorOnly)) {
       T mp[N], S[NS];
       if (is_first && first == kPriorUpdate) {

@@ -24,8 +24,9 @@ constexpr int kScanWarps = 4;   // warps (= chunks) per CTA
 
 template <typename T, int N, int P, int AM> struct FwdTailRing {
   T* ring;
-  __device__ bool operator()(const Params<T, N, P, AM>& prm, const T* obs, T* filt, long n, T* m, T* V) const {
-    return kf_forward_range_ring<T, N, P, AM>(prm, obs, filt, n, kContinue, m, V, ring);
+  __device__ bool operator()(const Params<T, N, P, AM>& prm, const T* obs, T* filt, long n, T* m, T* V, const T* mu,
+                             bool* nonpos) const {
+    return kf_forward_range_ring<T, N, P, AM>(prm, obs, filt, n, kContinue, m, V, ring, nullptr, mu, nonpos);
   }
 };
 template <typename T, int N, int P, int AM> struct BwdTailRing {
@@ -44,12 +45,12 @@ template <typename T, int N, int P, int AM> struct BwdTailRing {
 // rest of the chunk is the plain filter (2.4x cheaper) whose records are final and written at once;
 // fcut[g*nc+c] = number of leading frames of the chunk that still need the re-run.
 // three CTAs (12 warps) per SM for state dim <= 3, as the chunk policy assumes (eksb_scan_impl.cuh scan_auto_chunk)
-template <typename T, int N, int P, int AM>
+template <typename T, int N, int P, int AM, bool OFF>
 __global__ void __launch_bounds__(kScanWarps* kLanes, N <= 3 ? 3 : 1)
 scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                         const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
-                        long B, long Tn, long L, long nc, int early_out, T* __restrict__ fsum,
-                        long* __restrict__ fcut, int* __restrict__ alive, T* __restrict__ filt,
+                        long B, long Tn, long L, long nc, int early_out, int first, const T* __restrict__ yoff,
+                        T* __restrict__ fsum, long* __restrict__ fcut, int* __restrict__ alive, T* __restrict__ filt,
                         int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, SR = ScanRec<N>::FWD;
   extern __shared__ __align__(16) unsigned char scan_smem[];
@@ -69,10 +70,19 @@ scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
 #pragma unroll
     for (int i = 0; i < N; ++i) m[i] = pm[i];
     load_sym<T, N>(V, ps);
-    const long t1 = L < Tn ? L : Tn;
-    const bool ok0 = kf_forward_range_ring<T, N, P, AM>(prm, obs + (g * Tn * R2) * kLanes + lane,
-                                                        filt + (g * Tn * SG) * kLanes + lane, t1, kPriorUpdate, m, V, ring);
-    if (b < B && status && !ok0) status[b] = 1;
+    bool ok0 = true, nonpos0 = false;
+    if (first == kPriorOnly) {   // eks/newton_eks.py:132 : P starts at inv(S0)
+      T Vi[NS];
+      sym_inv<T, N>(V, Vi, ok0);
+#pragma unroll
+      for (int i = 0; i < NS; ++i) V[i] = Vi[i];
+    }
+    const T* mu = OFF ? yoff + bp * P : nullptr;           // read per frame (L1-resident); OFF is compile time so that
+    const long t1 = L < Tn ? L : Tn;                       // the common no-offset kernel carries no extra registers
+    ok0 = kf_forward_range_ring<T, N, P, AM>(prm, obs + (g * Tn * R2) * kLanes + lane,
+                                             filt + (g * Tn * SG) * kLanes + lane, t1, first, m, V, ring, nullptr,
+                                             mu, &nonpos0) && ok0;
+    if (b < B && status) set_status(status + b, ok0, nonpos0);
     return;
   }
   const long wi = w - tiles;                               // work item = g*(nc-1) + (c-1)
@@ -80,12 +90,13 @@ scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
   const long c = wi - g * (nc - 1) + 1;
   const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
-  bool ok = true;
+  bool ok = true, nonpos = false;
   const long t0 = c * L, t1 = (c + 1) * L < Tn ? (c + 1) * L : Tn;
   T sum[SR];
+  const T* mu = OFF ? yoff + bp * P : nullptr;
   const long cut = scan_fwd_chunk<T, N, P, AM, kLanes>(prm, obs + ((g * Tn + t0) * R2) * kLanes + lane,
                                                        filt + ((g * Tn + t0) * SG) * kLanes + lane, t1 - t0,
-                                                       early_out != 0, sum, ok, FwdTailRing<T, N, P, AM>{ring});
+                                                       early_out != 0, sum, ok, FwdTailRing<T, N, P, AM>{ring}, mu, &nonpos);
   if (lane == 0) {
     fcut[g * nc + c] = cut;
     if (cut >= t1 - t0) atomicOr(alive, 1);                // its last frame is not final: the fold has to run
@@ -93,7 +104,7 @@ scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
   T* out = fsum + ((g * nc + c) * SR) * kLanes + lane;
 #pragma unroll
   for (int r = 0; r < SR; ++r) out[r * kLanes] = sum[r];
-  if (b < B && status && !ok) status[b] = 1;
+  if (b < B && status) set_status(status + b, ok, nonpos);
 }
 
 // ---- 2a. forward fold: exact filtered state at the frame before every chunk ---------------------
@@ -137,16 +148,16 @@ scan_fwd_fold_kernel(const T* __restrict__ filt, const T* __restrict__ fsum, lon
     }
     fwd_apply_summary<T, N>(sum, m, V, ok);
   }
-  if (b < B && status && !ok) status[b] = 1;
+  if (b < B && status) set_status(status + b, ok, false);
 }
 
 // ---- 3a. forward re-run of chunks [c_lo, c_hi) ---------------------------------------------------
-template <typename T, int N, int P, int AM>
+template <typename T, int N, int P, int AM, bool OFF>
 __global__ void __launch_bounds__(kScanWarps* kLanes)
 scan_fwd_rerun_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                       const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask, long B,
-                      long Tn, long L, long nc, long c_lo, long c_hi, const T* __restrict__ finit,
-                      const long* __restrict__ fcut, T* filt, int* __restrict__ status) {
+                      long Tn, long L, long nc, long c_lo, long c_hi, int first0, const T* __restrict__ yoff,
+                      const T* __restrict__ finit, const long* __restrict__ fcut, T* filt, int* __restrict__ status) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
   const int lane = threadIdx.x & 31;
   const long span = c_hi - c_lo;
@@ -159,13 +170,20 @@ scan_fwd_rerun_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
   T m[N], V[NS];
   int first = kContinue;
+  bool ok = true;
   if (c == 0) {
     const T* pm = m0 + ((shared_mask & EKSB_SHARED_M0) ? 0 : bp * N);
     const T* ps = S0 + ((shared_mask & EKSB_SHARED_S0) ? 0 : bp * (N * N));
 #pragma unroll
     for (int i = 0; i < N; ++i) m[i] = pm[i];
     load_sym<T, N>(V, ps);
-    first = kPriorUpdate;
+    first = first0;
+    if (first == kPriorOnly) {
+      T Vi[NS];
+      sym_inv<T, N>(V, Vi, ok);
+#pragma unroll
+      for (int i = 0; i < NS; ++i) V[i] = Vi[i];
+    }
   } else {
     // start state: the last frame of chunk c-1 if that chunk wrote it itself (chunk 0 always did), else the fold's
     const bool prev_final = (c == 1) || (fcut && fcut[g * nc + c - 1] < L);
@@ -181,10 +199,11 @@ scan_fwd_rerun_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const
   if (fcut && c > 0) t1 = t0 + fcut[g * nc + c];           // the summary kernel wrote the frames from the cut on
   if (t1 <= t0) return;
   double acc = 0.0;
-  bool ok = kf_forward_range<T, N, P, AM, kLanes, 2, false>(prm, obs + ((g * Tn + t0) * R2) * kLanes + lane,
-                                                            filt + ((g * Tn + t0) * SG) * kLanes + lane, t1 - t0, first,
-                                                            m, V, acc);
-  if (b < B && status && !ok) status[b] = 1;
+  bool nonpos = false;
+  ok = kf_forward_range<T, N, P, AM, kLanes, 2, false>(prm, obs + ((g * Tn + t0) * R2) * kLanes + lane,
+                                                       filt + ((g * Tn + t0) * SG) * kLanes + lane, t1 - t0, first,
+                                                       m, V, acc, OFF ? yoff + bp * P : nullptr, &nonpos) && ok;
+  if (b < B && status) set_status(status + b, ok, nonpos);
 }
 
 // ---- 1b. backward chunk summaries, chunks [0, nc-1), plus the sequential run of the last chunk --------
@@ -216,7 +235,7 @@ scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restr
     const long base = (g * Tn + t0) * kLanes;
     const bool ok0 = rts_backward_range_ring<T, N, P, AM>(prm, filt + base * SG + lane, smth + base * SG + lane,
                                                           ym ? ym + base * P + lane : nullptr, Tn - t0, true, ms, Vs, ring);
-    if (b < B && status && !ok0) status[b] = 1;
+    if (b < B && status) set_status(status + b, ok0, false);
     return;
   }
   const long wi = w - tiles;
@@ -237,7 +256,7 @@ scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restr
   T* out = bsum + ((g * nc + c) * SR) * kLanes + lane;
 #pragma unroll
   for (int r = 0; r < SR; ++r) out[r * kLanes] = acc[r];
-  if (b < B && status && !ok) status[b] = 1;
+  if (b < B && status) set_status(status + b, ok, false);
 }
 
 // ---- 2b. backward fold: exact smoothed state of the frame after every chunk ----------------------
@@ -306,7 +325,7 @@ scan_bwd_rerun_kernel(const T* filt, const T* __restrict__ C, const T* __restric
   bool ok = rts_backward_range<T, N, P, AM, kLanes, 2>(prm, filt + base * SG + lane, smth + base * SG + lane,
                                                       ym ? ym + base * P + lane : nullptr, nullptr, nullptr, t1 - t0,
                                                       terminal, ms, Vs);
-  if (b < B && status && !ok) status[b] = 1;
+  if (b < B && status) set_status(status + b, ok, false);
 }
 
 }  // namespace eksb

@@ -20,59 +20,125 @@ inline size_t scan_workspace_elems(long B, long Tn, int n, long L) {
 
 inline long scan_auto_chunk(long B, long Tn, int n, int elem_size) {
   // warps = tiles * chunks.  The summary kernels keep 12 (f64) / 16 (f32) warps resident per SM (register-bound,
-  // n <= 3) and stage their frames through per-lane cp.async rings, so bytes in flight do not hinge on occupancy:
-  // fewer, longer chunks win because every chunk pays K warm-up frames before its summary has forgotten the
-  // boundary state (eksb_math.cuh scan_fwd_chunk).  Measured, 64 tracks x 10 M frames, 8 / 12 / 16 / 24 warps per
-  // SM: f64 34.8 / 35.1 / 35.5 / 36.4 ms, f32 17.8 / - / 18.2 / 20.1 ms.
-  (void)n;
-  const long per_sm = scan_env_long("EKSB_SCAN_WARPS_PER_SM", 8);
-  const long want_chunks = (148L * per_sm + num_tiles(B) - 1) / num_tiles(B);
-  long L = (Tn + want_chunks - 1) / want_chunks;
-  if (L < 64) L = 64;
-  return L;
+  // n <= 3) and stage their frames through per-lane cp.async rings, so bytes in flight do not hinge on occupancy.
+  // Two opposing effects set the chunk length: every chunk pays K warm-up frames (150-800 on the synthetic data)
+  // before its summary has forgotten the boundary state (eksb_math.cuh scan_fwd_chunk), which favours few long
+  // chunks; more warps per SM hide more of the thread-per-track latency.  Measured (tools/route_sweep.py, f64,
+  // 100 000 frames, 8 vs 12 warps per SM): 32 tiles 6.68 / 7.61 ms, 64 tiles 13.03 / 12.83, 96 tiles 20.2 / 18.3,
+  // 128 tiles 26.8 / 24.0, 192 tiles 38.1 / 35.0, 256 tiles 52.2 / 45.8; 64 tracks x 10 M frames 34.8 / 35.1.
+  // Hence 12 warps per SM when the chunks stay >= 3 500 frames, else 8.
+  (void)n; (void)elem_size;
+  const long tiles = num_tiles(B);
+  auto len = [&](long per_sm) {
+    const long want_chunks = (148L * per_sm + tiles - 1) / tiles;
+    long L = (Tn + want_chunks - 1) / want_chunks;
+    return L < 64 ? 64L : L;
+  };
+  const long forced = scan_env_long("EKSB_SCAN_WARPS_PER_SM", 0);
+  if (forced > 0) return len(forced);
+  const long L12 = len(12);
+  return L12 >= 3500 ? L12 : len(8);
 }
 
-template <typename T, int N, int P, int AM>
-static int scan_run(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int mask, long B, long Tn,
-                    long L, T* ws, T* filt, T* smth, T* ym, int* status, cudaStream_t st) {
-  constexpr int SG = Dim<N>::SIGMA;
+// Workspace layout shared by the forward and the backward half (they may be launched by separate calls).
+template <typename T, int N> struct ScanWs {
+  T *fsum, *bsum, *finit, *binit;
+  long *fcut, *bcut;
+  int* alive;   // [0] forward, [1] backward: "the fold must run"
+  ScanWs(T* ws, long tiles, long nc) {
+    constexpr int SG = Dim<N>::SIGMA;
+    fsum = ws;
+    bsum = fsum + (size_t)tiles * nc * ScanRec<N>::FWD * kLanes;
+    finit = bsum + (size_t)tiles * nc * ScanRec<N>::BWD * kLanes;
+    binit = finit + (size_t)tiles * nc * SG * kLanes;
+    fcut = reinterpret_cast<long*>(binit + (size_t)tiles * nc * SG * kLanes);   // 32 T's (>= 16 B) per (tile, chunk)
+    bcut = fcut + tiles * nc;
+    alive = reinterpret_cast<int*>(bcut + tiles * nc);
+  }
+};
+
+inline unsigned scan_blocks(long items) { return (unsigned)((items + kScanWarps - 1) / kScanWarps); }
+
+// forward half: obs -> filt
+template <typename T, int N, int P, int AM, bool OFF>
+static int scan_run_fwd_off(const T* obs, const T* yoff, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int mask,
+                            long B, long Tn, long L, int first, T* ws, T* filt, int* status, cudaStream_t st) {
   const long tiles = num_tiles(B), nc = (Tn + L - 1) / L;
-  T* fsum = ws;
-  T* bsum = fsum + (size_t)tiles * nc * ScanRec<N>::FWD * kLanes;
-  T* finit = bsum + (size_t)tiles * nc * ScanRec<N>::BWD * kLanes;
-  T* binit = finit + (size_t)tiles * nc * SG * kLanes;
-  long* fcut = reinterpret_cast<long*>(binit + (size_t)tiles * nc * SG * kLanes);   // 32 T's (>= 16 B) per (tile, chunk)
-  long* bcut = fcut + tiles * nc;
-  int* alive = reinterpret_cast<int*>(bcut + tiles * nc);   // [0] forward, [1] backward: "the fold must run"
-  if (nc > 1 && cudaMemsetAsync(alive, 0, 2 * sizeof(int), st) != cudaSuccess) return check_launch("scan flags");
+  ScanWs<T, N> w(ws, tiles, nc);
+  if (nc > 1 && cudaMemsetAsync(w.alive, 0, sizeof(int), st) != cudaSuccess) return check_launch("scan flags");
   const int early = scan_env_long("EKSB_SCAN_NO_EARLY", 0) ? 0 : 1;                 // A/B switch: old 2-read behaviour
-  auto blocks = [&](long items) { return (unsigned)((items + kScanWarps - 1) / kScanWarps); };
   const int thr = kScanWarps * kLanes;
-  // per-lane frame rings of the summary kernels (eksb_scan.cuh), one per warp
-  const size_t smem_f = kScanWarps * ring_bytes_per_warp<T, 2 * P>(), smem_b = kScanWarps * ring_bytes_per_warp<T, SG>();
-  cudaFuncSetAttribute(scan_fwd_summary_kernel<T, N, P, AM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f);
-  cudaFuncSetAttribute(scan_bwd_summary_kernel<T, N, P, AM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b);
-  // forward pass
+  const size_t smem_f = kScanWarps * ring_bytes_per_warp<T, 2 * P>();               // per-lane frame rings, one per warp
+  cudaFuncSetAttribute(scan_fwd_summary_kernel<T, N, P, AM, OFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f);
   if (nc == 1) {
-    scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 0, 1, finit, nullptr, filt, status);
+    scan_fwd_rerun_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 0, 1, first, yoff, w.finit, nullptr, filt, status);
   } else {
     // chunk 0 (sequential from the prior) rides in the same launch as the summaries of chunks >= 1
-    scan_fwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, smem_f, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, early, fsum, fcut, alive, filt, status);
-    scan_fwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(filt, fsum, B, Tn, L, nc, alive, finit, status);
-    scan_fwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 1, nc, finit, fcut, filt, status);
+    scan_fwd_summary_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * nc), thr, smem_f, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, early, first, yoff, w.fsum, w.fcut, w.alive, filt, status);
+    scan_fwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(filt, w.fsum, B, Tn, L, nc, w.alive, w.finit, status);
+    scan_fwd_rerun_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 1, nc, first, yoff, w.finit, w.fcut, filt, status);
   }
-  int rc = check_launch("scan forward kernels");
-  if (rc != EKSB_OK || !smth) return rc;
-  // backward pass (smth may alias filt: a chunk only reads and writes its own frames)
+  return check_launch("scan forward kernels");
+}
+template <typename T, int N, int P, int AM>
+static int scan_run_fwd(const T* obs, const T* yoff, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int mask,
+                        long B, long Tn, long L, int first, T* ws, T* filt, int* status, cudaStream_t st) {
+  return yoff ? scan_run_fwd_off<T, N, P, AM, true>(obs, yoff, m0, S0, C, A, Q, mask, B, Tn, L, first, ws, filt, status, st)
+              : scan_run_fwd_off<T, N, P, AM, false>(obs, yoff, m0, S0, C, A, Q, mask, B, Tn, L, first, ws, filt, status, st);
+}
+
+// backward half: filt -> smth (+ ym); smth may alias filt (a chunk only reads and writes its own frames)
+template <typename T, int N, int P, int AM>
+static int scan_run_bwd(const T* filt, const T* C, const T* A, const T* Q, int mask, long B, long Tn, long L, T* ws, T* smth,
+                        T* ym, int* status, cudaStream_t st) {
+  constexpr int SG = Dim<N>::SIGMA;
+  const long tiles = num_tiles(B), nc = (Tn + L - 1) / L;
+  ScanWs<T, N> w(ws, tiles, nc);
+  if (nc > 1 && cudaMemsetAsync(w.alive + 1, 0, sizeof(int), st) != cudaSuccess) return check_launch("scan flags");
+  const int early = scan_env_long("EKSB_SCAN_NO_EARLY", 0) ? 0 : 1;
+  const int thr = kScanWarps * kLanes;
+  const size_t smem_b = kScanWarps * ring_bytes_per_warp<T, SG>();
+  cudaFuncSetAttribute(scan_bwd_summary_kernel<T, N, P, AM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b);
   if (nc == 1) {
-    scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, nc - 1, nc, binit, nullptr, smth, ym, status);
+    scan_bwd_rerun_kernel<T, N, P, AM><<<scan_blocks(tiles), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, nc - 1, nc, w.binit, nullptr, smth, ym, status);
   } else {
     // the terminal chunk (sequential from the end of the track) rides in the summary launch
-    scan_bwd_summary_kernel<T, N, P, AM><<<blocks(tiles * nc), thr, smem_b, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, early, bsum, bcut, alive + 1, smth, ym, status);
-    scan_bwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(smth, bsum, B, Tn, L, nc, alive + 1, binit);
-    scan_bwd_rerun_kernel<T, N, P, AM><<<blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, 0, nc - 1, binit, bcut, smth, ym, status);
+    scan_bwd_summary_kernel<T, N, P, AM><<<scan_blocks(tiles * nc), thr, smem_b, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, early, w.bsum, w.bcut, w.alive + 1, smth, ym, status);
+    scan_bwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(smth, w.bsum, B, Tn, L, nc, w.alive + 1, w.binit);
+    scan_bwd_rerun_kernel<T, N, P, AM><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, 0, nc - 1, w.binit, w.bcut, smth, ym, status);
   }
   return check_launch("scan backward kernels");
+}
+
+#define EKSB_FOR_EACH_SCAN_DIM(X) X(2, 4) X(3, 4) X(3, 6) X(3, 8) X(4, 6)
+inline bool scan_dims_ok(int n, int p) {
+#define X(N_, P_) if (n == N_ && p == P_) return true;
+  EKSB_FOR_EACH_SCAN_DIM(X)
+#undef X
+  return false;
+}
+
+// which == 1: forward half, 2: backward half, 3: both
+template <typename T>
+static int scan_dispatch(int which, const T* obs, const T* yoff, const T* m0, const T* S0, const T* C, const T* A, const T* Q,
+                         int mask, long B, long Tn, int n, int p, int a_mode, long L, int first, T* ws, T* filt, T* smth,
+                         T* ym, int* status, cudaStream_t st) {
+#define X(N_, P_)                                                                                                        \
+  if (n == N_ && p == P_) {                                                                                              \
+    int rc = EKSB_OK;                                                                                                    \
+    if (which & 1)                                                                                                       \
+      rc = a_mode == EKSB_A_DIAG                                                                                         \
+               ? scan_run_fwd<T, N_, P_, 0>(obs, yoff, m0, S0, C, A, Q, mask, B, Tn, L, first, ws, filt, status, st)      \
+               : scan_run_fwd<T, N_, P_, 1>(obs, yoff, m0, S0, C, A, Q, mask, B, Tn, L, first, ws, filt, status, st);     \
+    if (rc == EKSB_OK && (which & 2))                                                                                    \
+      rc = a_mode == EKSB_A_DIAG ? scan_run_bwd<T, N_, P_, 0>(filt, C, A, Q, mask, B, Tn, L, ws, smth, ym, status, st)    \
+                                 : scan_run_bwd<T, N_, P_, 1>(filt, C, A, Q, mask, B, Tn, L, ws, smth, ym, status, st);   \
+    return rc;                                                                                                           \
+  }
+  EKSB_FOR_EACH_SCAN_DIM(X)
+#undef X
+  set_error("kf_rts_scan: (n=%d,p=%d) not instantiated (state dim <= 4)", n, p);
+  return EKSB_EDIM;
 }
 
 template <typename T>
@@ -83,15 +149,83 @@ static int scan_api(const T* obs, const T* m0, const T* S0, const T* C, const T*
   if (a_mode != EKSB_A_DIAG && a_mode != EKSB_A_DENSE) { set_error("kf_rts_scan: bad a_mode %d", a_mode); return EKSB_EARG; }
   const long L = chunk > 0 ? chunk : scan_auto_chunk(B, Tn, n, (int)sizeof(T));
   if (scan_workspace_elems(B, Tn, n, L) * sizeof(T) > ws_bytes) { set_error("kf_rts_scan: workspace too small (%zu bytes needed)", scan_workspace_elems(B, Tn, n, L) * sizeof(T)); return EKSB_EARG; }
-#define X(N_, P_)                                                                                                   \
-  if (n == N_ && p == P_)                                                                                           \
-    return a_mode == EKSB_A_DIAG                                                                                    \
-               ? scan_run<T, N_, P_, 0>(obs, m0, S0, C, A, Q, mask, B, Tn, L, ws, filt, smth, ym, status, (cudaStream_t)stream) \
-               : scan_run<T, N_, P_, 1>(obs, m0, S0, C, A, Q, mask, B, Tn, L, ws, filt, smth, ym, status, (cudaStream_t)stream);
-  X(2, 4) X(3, 4) X(3, 6) X(3, 8) X(4, 6)
-#undef X
-  set_error("kf_rts_scan: (n=%d,p=%d) not instantiated (state dim <= 4)", n, p);
-  return EKSB_EDIM;
+  return scan_dispatch<T>(smth ? 3 : 1, obs, (const T*)nullptr, m0, S0, C, A, Q, mask, B, Tn, n, p, a_mode, L, kPriorUpdate, ws,
+                          filt, smth, ym, status, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Routed entry points (eksb_kf_forward_ws / eksb_rts_backward_ws): the same contracts as eksb_kf_forward_offset /
+// eksb_rts_backward plus a caller-owned workspace.  The sequential warp-specialised kernels keep one chain warp per
+// track tile, so a batch with fewer tiles than the GPU has SMs (or an awkward count between one and two tiles per
+// SM) runs at one warp's pace no matter how few bytes it moves; such batches go through the two halves of the
+// parallel-in-time scan instead.  Measured, f64, 100 000 frames, sequential vs scan (tools/route_sweep.py):
+//   32 tiles 22.8 / 6.7 ms, 64 tiles 22.8 / 12.8, 96 tiles 23.3 / 18.3, 128 tiles 25.4 / 24.0, 171 tiles 36.2 / 31.8,
+//   192 tiles 38.4 / 35.0, 256 tiles 43.6 / 45.8 (f32: 64 tiles 16.7 / 7.1, 128 tiles 16.7 / 13.7, 256 tiles 24.3 / 27.0).
+// Policy: T >= 4096 and a scan instantiation; up to 96 tiles always, up to 208 tiles when the scan's chunks are
+// at least 2048 frames long.  EKSB_ROUTE=seq|scan forces a side (read per call).
+// ------------------------------------------------------------------------------------------------------------
+inline bool route_scan(long B, long Tn, int n, int p, int elem_size) {
+  if (B <= 0 || Tn <= 0 || !scan_dims_ok(n, p)) return false;
+  const char* e = getenv("EKSB_ROUTE");
+  if (e && e[0] == 's' && e[1] == 'e') return false;
+  if (e && e[0] == 's' && e[1] == 'c') return true;
+  if (Tn < 4096) return false;
+  const long tiles = num_tiles(B);
+  if (tiles <= 96) return true;
+  return tiles <= 208 && scan_auto_chunk(B, Tn, n, elem_size) >= 2048;
+}
+
+// Sequential entry points of the other translation units (same shared library).
+template <typename T> struct SeqApi;
+template <> struct SeqApi<double> {
+  static int fwd(const double* obs, const double* yoff, const double* m0, const double* S0, const double* C, const double* A,
+                 const double* Q, int mask, long B, long Tn, int n, int p, int am, int first, double* filt, double* nll,
+                 int* status, void* st) {
+    return eksb_kf_forward_offset_f64(obs, yoff, m0, S0, C, A, Q, mask, B, Tn, n, p, am, first, filt, nll, status, st);
+  }
+  static int bwd(const double* filt, const double* C, const double* A, const double* Q, int mask, long B, long Tn, int n, int p,
+                 int am, double* smth, double* ym, double* yv, double* cv, int* status, void* st) {
+    return eksb_rts_backward_f64(filt, C, A, Q, mask, B, Tn, n, p, am, smth, ym, yv, cv, status, st);
+  }
+};
+template <> struct SeqApi<float> {
+  static int fwd(const float* obs, const float* yoff, const float* m0, const float* S0, const float* C, const float* A,
+                 const float* Q, int mask, long B, long Tn, int n, int p, int am, int first, float* filt, double* nll,
+                 int* status, void* st) {
+    return eksb_kf_forward_offset_f32(obs, yoff, m0, S0, C, A, Q, mask, B, Tn, n, p, am, first, filt, nll, status, st);
+  }
+  static int bwd(const float* filt, const float* C, const float* A, const float* Q, int mask, long B, long Tn, int n, int p,
+                 int am, float* smth, float* ym, float* yv, float* cv, int* status, void* st) {
+    return eksb_rts_backward_f32(filt, C, A, Q, mask, B, Tn, n, p, am, smth, ym, yv, cv, status, st);
+  }
+};
+
+inline size_t route_workspace_bytes(long B, long Tn, int n, int p, int elem_size) {
+  if (!route_scan(B, Tn, n, p, elem_size)) return 0;
+  return scan_workspace_elems(B, Tn, n, scan_auto_chunk(B, Tn, n, elem_size)) * (size_t)elem_size;
+}
+
+template <typename T>
+static int forward_ws_api(const T* obs, const T* yoff, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int mask,
+                          long B, long Tn, int n, int p, int a_mode, int first, T* filt, double* nll, int* status, T* ws,
+                          size_t ws_bytes, void* stream) {
+  const size_t need = (ws && filt && !nll) ? route_workspace_bytes(B, Tn, n, p, (int)sizeof(T)) : 0;
+  if (need == 0 || ws_bytes < need || !obs || !m0 || !S0 || !C || !A || !Q ||
+      (first != kPriorUpdate && first != kPriorOnly) || (a_mode != EKSB_A_DIAG && a_mode != EKSB_A_DENSE))
+    return SeqApi<T>::fwd(obs, yoff, m0, S0, C, A, Q, mask, B, Tn, n, p, a_mode, first, filt, nll, status, stream);
+  return scan_dispatch<T>(1, obs, yoff, m0, S0, C, A, Q, mask, B, Tn, n, p, a_mode, scan_auto_chunk(B, Tn, n, (int)sizeof(T)),
+                          first, ws, filt, (T*)nullptr, (T*)nullptr, status, (cudaStream_t)stream);
+}
+
+template <typename T>
+static int backward_ws_api(const T* filt, const T* C, const T* A, const T* Q, int mask, long B, long Tn, int n, int p, int a_mode,
+                           T* smth, T* ym, T* yv, T* cv, int* status, T* ws, size_t ws_bytes, void* stream) {
+  const size_t need = (ws && !yv && !cv) ? route_workspace_bytes(B, Tn, n, p, (int)sizeof(T)) : 0;
+  if (need == 0 || ws_bytes < need || !filt || !smth || !C || !A || !Q || (a_mode != EKSB_A_DIAG && a_mode != EKSB_A_DENSE))
+    return SeqApi<T>::bwd(filt, C, A, Q, mask, B, Tn, n, p, a_mode, smth, ym, yv, cv, status, stream);
+  return scan_dispatch<T>(2, (const T*)nullptr, (const T*)nullptr, (const T*)nullptr, (const T*)nullptr, C, A, Q, mask, B, Tn, n, p,
+                          a_mode, scan_auto_chunk(B, Tn, n, (int)sizeof(T)), kPriorUpdate, ws, const_cast<T*>(filt), smth, ym,
+                          status, (cudaStream_t)stream);
 }
 
 }  // namespace eksb

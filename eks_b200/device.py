@@ -251,12 +251,30 @@ def pca_setup(obs, B, T, p, quantile, smooth_param, n=3, center=True, status=Non
     return prm, means, status
 
 
+# ------------------------------------------------------------------ routing workspace
+def route_workspace(B, T, n, p, dtype, device):
+    """Workspace for kf_forward(workspace=...) / rts_backward(workspace=...): with it the library sends batches
+    that have too few track tiles for the sequential kernels through the parallel-in-time scan
+    (eksb_route_workspace_bytes; None when this shape always runs the sequential kernels)."""
+    es = torch.empty(0, dtype=dtype).element_size()
+    nbytes = lib().eksb_route_workspace_bytes(B, T, n, p, es)
+    if nbytes == 0:
+        return None
+    return torch.empty((nbytes + es - 1) // es, dtype=dtype, device=device)
+
+
+def routes_to_scan(B, T, n, p, dtype):
+    return lib().eksb_route_workspace_bytes(B, T, n, p, torch.empty(0, dtype=dtype).element_size()) > 0
+
+
 # ------------------------------------------------------------------ A2 / A6 forward
 def kf_forward(obs, prm: TrackParams, B, T, first=_lib.FIRST_PRIOR_UPDATE, q_scale=None, want_filt=True,
-               want_nll=False, filt=None, status=None, y_offset=None):
+               want_nll=False, filt=None, status=None, y_offset=None, workspace=None):
     """Forward filter.  Returns (filt or None, nll (n_scale,B) float64 or None, status (B,) int32).
     y_offset: (B,p) per-track offsets subtracted from y as the frames are read (the camera means of
-    multiview_pca_smoother.py:698-705 without a centring pass over the records); not with q_scale."""
+    multiview_pca_smoother.py:698-705 without a centring pass over the records); not with q_scale.
+    workspace: route_workspace(...) tensor; lets the library pick the parallel-in-time kernels for few-tile batches.
+    status bits: 1 = non-positive pivot, 2 = a non-positive ensemble variance (see include/eksb.h)."""
     _need_cuda(obs, "obs")
     dev, dt = obs.device, obs.dtype
     if prm.dtype != dt:
@@ -274,6 +292,15 @@ def kf_forward(obs, prm: TrackParams, B, T, first=_lib.FIRST_PRIOR_UPDATE, q_sca
             raise ValueError("y_offset and q_scale cannot be combined")
         if y_offset.dtype != dt or tuple(y_offset.shape) != (B, prm.p) or not y_offset.is_contiguous():
             raise ValueError("y_offset must be a contiguous (B,p) tensor of the obs dtype")
+    if workspace is not None and q_scale is None:
+        if workspace.dtype != dt:
+            raise TypeError("workspace dtype differs from obs")
+        fn = getattr(lib(), f"eksb_kf_forward_ws_{_sfx(dt)}")
+        check(fn(_ptr(obs), _ptr(y_offset), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q),
+                 prm.shared_mask, B, T, prm.n, prm.p, prm.a_mode, first, _ptr(filt), _ptr(nll), _ptr(status),
+                 _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(dev)), "eksb_kf_forward_ws")
+        return filt, nll, status
+    if y_offset is not None:
         fn = getattr(lib(), f"eksb_kf_forward_offset_{_sfx(dt)}")
         check(fn(_ptr(obs), _ptr(y_offset), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q),
                  prm.shared_mask, B, T, prm.n, prm.p, prm.a_mode, first, _ptr(filt), _ptr(nll), _ptr(status),
@@ -303,8 +330,9 @@ def kf_forward_generic(obs, prm: TrackParams, B, T, R=None, first=_lib.FIRST_PRI
 
 # ------------------------------------------------------------------ A4 / A5 backward
 def rts_backward(filt, prm: TrackParams, B, T, inplace=False, want_ym=True, want_yv=False, want_cv=False,
-                 smth=None, ym=None, status=None):
-    """RTS pass.  Returns dict(smth, ym, yv, cv, status); smth is filt itself when inplace."""
+                 smth=None, ym=None, yv=None, status=None, workspace=None):
+    """RTS pass.  Returns dict(smth, ym, yv, cv, status); smth is filt itself when inplace.
+    workspace: route_workspace(...) tensor (may be the one the forward call used)."""
     _need_cuda(filt, "filt")
     dev, dt = filt.device, filt.dtype
     n, p = prm.n, prm.p
@@ -314,14 +342,56 @@ def rts_backward(filt, prm: TrackParams, B, T, inplace=False, want_ym=True, want
         ym = alloc_records(B, T, p, dt, dev)
     if not want_ym:
         ym = None
-    yv = alloc_records(B, T, p, dt, dev) if want_yv else None
+    if want_yv and yv is None:
+        yv = alloc_records(B, T, p, dt, dev)
+    if not want_yv:
+        yv = None
     cv = alloc_records(B, T, n * n, dt, dev).zero_() if want_cv else None
     if status is None:
         status = torch.zeros(B, dtype=torch.int32, device=dev)
+    if workspace is not None:
+        if workspace.dtype != dt:
+            raise TypeError("workspace dtype differs from filt")
+        fn = getattr(lib(), f"eksb_rts_backward_ws_{_sfx(dt)}")
+        check(fn(_ptr(filt), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), prm.shared_mask, B, T, n, p, prm.a_mode, _ptr(smth),
+                 _ptr(ym), _ptr(yv), _ptr(cv), _ptr(status), _ptr(workspace),
+                 workspace.numel() * workspace.element_size(), _stream(dev)), "eksb_rts_backward_ws")
+        return dict(smth=smth, ym=ym, yv=yv, cv=cv, status=status)
     fn = getattr(lib(), f"eksb_rts_backward_{_sfx(dt)}")
     check(fn(_ptr(filt), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), prm.shared_mask, B, T, n, p, prm.a_mode, _ptr(smth),
              _ptr(ym), _ptr(yv), _ptr(cv), _ptr(status), _stream(dev)), "eksb_rts_backward")
     return dict(smth=smth, ym=ym, yv=yv, cv=cv, status=status)
+
+
+def rts_backward_generic(filt, prm: TrackParams, B, T, pred=None, want_ym=True, want_yv=False, want_cv=False,
+                         status=None):
+    """Literal-arithmetic RTS pass (LU solve per frame, any n<=8, p<=16, dense A).  pred: optional packed
+    NS-row records with the caller's own S[t] (eks/ensemble_kalman.py:158 reads its S argument).
+    Returns dict(smth, ym, yv, cv, status)."""
+    _need_cuda(filt, "filt")
+    dev, dt = filt.device, filt.dtype
+    n, p = prm.n, prm.p
+    smth = torch.empty_like(filt)
+    ym = alloc_records(B, T, p, dt, dev) if want_ym else None
+    yv = alloc_records(B, T, p, dt, dev) if want_yv else None
+    cv = alloc_records(B, T, n * n, dt, dev).zero_() if want_cv else None
+    if status is None:
+        status = torch.zeros(B, dtype=torch.int32, device=dev)
+    fn = getattr(lib(), f"eksb_rts_backward_generic_{_sfx(dt)}")
+    check(fn(_ptr(filt), _ptr(pred), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q), prm.shared_mask, B, T, n, p, _ptr(smth),
+             _ptr(ym), _ptr(yv), _ptr(cv), _ptr(status), _stream(dev)), "eksb_rts_backward_generic")
+    return dict(smth=smth, ym=ym, yv=yv, cv=cv, status=status)
+
+
+def pack_sym(dense):
+    """dense (B,T,n,n) -> packed NS-row records (upper triangle of the symmetrised matrix, row-major)."""
+    B, T, n, _ = dense.shape
+    iu = torch.triu_indices(n, n, device=dense.device)
+    sym = 0.5 * (dense + dense.transpose(-1, -2))
+    rows = sym[:, :, iu[0], iu[1]].contiguous()
+    ns = rows.shape[-1]
+    rec = alloc_records(B, T, ns, dense.dtype, dense.device)
+    return pack_rows(rows, rec, ns, 0, 0.0)
 
 
 # ------------------------------------------------------------------ A7 block-tridiagonal solve
@@ -336,7 +406,7 @@ def btd_solve(obs, prm: TrackParams, B, T, want_ym=False, inplace=True, status=N
     _need_cuda(obs, "obs")
     dev, dt = obs.device, obs.dtype
     if scan is None:
-        scan = num_tiles(B) < 148 and T >= 4096 and prm.n <= 4
+        scan = routes_to_scan(B, T, prm.n, prm.p, dt)
     if scan:
         out = kf_rts_scan(obs, prm, B, T, smooth=True, inplace=True, want_ym=want_ym, status=status)
         return dict(sol=out["smth"], ym=out["ym"], status=out["status"])

@@ -30,8 +30,14 @@ def _to_dev(a, d):
 
 
 def _raise_if_singular(status):
-    if bool(status.any().item()):
+    """A non-positive pivot anywhere in the batch is the reference's numpy.linalg.LinAlgError."""
+    if bool(((status & _lib.STATUS_PIVOT) != 0).any().item()):
         raise np.linalg.LinAlgError("Singular matrix")
+
+
+def _nonpositive_variance(status):
+    """True if a fast kernel met an ensemble variance <= 0 (it cannot divide by it; the literal LU kernel can)."""
+    return bool(((status & _lib.STATUS_NONPOS_VAR) != 0).any().item())
 
 
 def ensemble(markers_list, keys, mode='median'):
@@ -83,6 +89,10 @@ def filtering_pass(y, m0, S0, C, R, A, Q, ensemble_vars):
         filt, status = dev.kf_forward_generic(obs, prm, 1, T, R=_to_dev(Rm, d), status=status)
     else:
         filt, _, status = dev.kf_forward(obs, prm, 1, T, status=status)
+        if _nonpositive_variance(status):
+            # every ensemble member agreed to the last bit in some frame: R has a zero on its diagonal, which the
+            # reference's R + C S C^T solve (:112-113) takes in its stride; so does the literal kernel
+            filt, status = dev.kf_forward_generic(obs, prm, 1, T, R=_to_dev(Rm, d))
     mean, cov, pred = dev.expand_state(filt, 1, T, prm, want_pred=True)
     mf, Vf, S = mean[0].cpu().numpy(), cov[0].cpu().numpy(), pred[0].cpu().numpy()
     _raise_if_singular(status)
@@ -110,16 +120,29 @@ def kalman_dot(array, V, C, R):
 
 def smooth_backward(y, mf, Vf, S, A, Q, C):
     """eks/ensemble_kalman.py:120-164.  Returns ms (T,n), Vs (T,n,n), CV (T-1,n,n).
-    Like the reference only y.shape[0] is used from y.  S is recomputed on the device as
-    A Vf A^T + Q (what filtering_pass stored in it, :101) instead of being uploaded."""
+    Like the reference only y.shape[0] is used from y, and Q is not read when S is usable: the reference takes the
+    predicted covariances from its S argument (:158-160).  When S is what filtering_pass returns (S[t] = A Vf[t] A^T
+    + Q, :101) the register-resident kernel recomputes it on the device instead of uploading it; a caller-modified
+    S, or an (n,p) without a template instantiation, goes through the literal LU kernel with S uploaded."""
     d = _cuda()
     T = np.asarray(y).shape[0]
     mf = np.asarray(mf, dtype=np.float64)
+    Vf = np.asarray(Vf, dtype=np.float64)
     n = mf.shape[1]
     p = np.asarray(C).shape[0]
     prm = _params(d, np.zeros(n), np.eye(n), C, A, Q)
-    filt = dev.pack_state(_to_dev(mf[None], d), _to_dev(np.asarray(Vf)[None], d))
-    out = dev.rts_backward(filt, prm, 1, T, want_ym=False, want_cv=True)
+    filt = dev.pack_state(_to_dev(mf[None], d), _to_dev(Vf[None], d))
+    S = None if S is None else np.asarray(S, dtype=np.float64)
+    own_S = False
+    if S is not None and T > 1:
+        An, Qn = np.asarray(A, dtype=np.float64), np.asarray(Q, dtype=np.float64)
+        want = An @ Vf[:T - 1] @ An.T + Qn
+        own_S = not np.allclose(S[:T - 1], want, rtol=1e-9, atol=1e-12 * max(1.0, float(np.abs(want).max())))
+    if own_S or not prm.fast_path:
+        pred = dev.pack_sym(_to_dev(S[None], d)) if S is not None else None
+        out = dev.rts_backward_generic(filt, prm, 1, T, pred=pred, want_ym=False, want_cv=True)
+    else:
+        out = dev.rts_backward(filt, prm, 1, T, want_ym=False, want_cv=True)
     _raise_if_singular(out["status"])
     mean, cov = dev.expand_state(out["smth"], 1, T, prm)
     cv = dev.unpack_rows(out["cv"], n * n, 0, 1, T, n * n)[0].cpu().numpy().reshape(T, n, n)

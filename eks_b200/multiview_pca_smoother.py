@@ -14,7 +14,8 @@ import pandas as pd
 import torch
 
 from . import _lib, device as dev
-from .ensemble_kalman import ensemble, filtering_pass, kalman_dot, smooth_backward, _cuda  # noqa: F401 (re-exported like the reference :7)
+from .ensemble_kalman import (ensemble, filtering_pass, kalman_dot, smooth_backward, _cuda,  # noqa: F401 (re-exported like the reference :7)
+                              _raise_if_singular, _nonpositive_variance)
 from .newton_eks import kalman_newton_recursive  # noqa: F401
 from .utils import make_dlc_pandas_index
 
@@ -84,18 +85,25 @@ def _run_tracks(tracks, newton=False):
     prm = dev.TrackParams.from_numpy(stk("m0"), stk("S0"), stk("C"), stk("A"), stk("Q"), dtype=torch.float64, device=d)
     obs = dev.pack_obs(to(stk("y")), to(stk("ev")))
     sg = dev.sigma(n)
+    first = _lib.FIRST_PRIOR_ONLY if newton else _lib.FIRST_PRIOR_UPDATE
+    fast = prm.fast_path
+    if fast:
+        filt, _, status = dev.kf_forward(obs, prm, B, T, first=first)
+        if _nonpositive_variance(status):
+            fast = False            # a zero ensemble variance: the literal LU kernels have the reference's semantics
+    if not fast:
+        # (n,p) without a register-resident instantiation (e.g. five cameras, p = 10): runtime-dimension kernels
+        filt, status = dev.kf_forward_generic(obs, prm, B, T, first=first)
     if newton:
-        filt, _, status = dev.kf_forward(obs, prm, B, T, first=_lib.FIRST_PRIOR_ONLY)
         lat = dev.unpack_rows(filt, sg, 0, B, T, n).cpu().numpy()
         ym = dev.unpack_rows(dev.project(filt, prm, B, T), p, 0, B, T, p).cpu().numpy()   # y_m = B q (:555, :905)
     else:
-        filt, _, status = dev.kf_forward(obs, prm, B, T)
-        out = dev.rts_backward(filt, prm, B, T, inplace=True, want_ym=True)
+        out = (dev.rts_backward(filt, prm, B, T, inplace=True, want_ym=True) if prm.fast_path
+               else dev.rts_backward_generic(filt, prm, B, T, want_ym=True))
         status = status | out["status"]
         lat = dev.unpack_rows(out["smth"], sg, 0, B, T, n).cpu().numpy()
         ym = dev.unpack_rows(out["ym"], p, 0, B, T, p).cpu().numpy()  # C ms fused into the RTS kernel (:745)
-    if bool(status.any().item()):
-        raise np.linalg.LinAlgError("Singular matrix")
+    _raise_if_singular(status)
     return [(lat[b], ym[b]) for b in range(B)]
 
 
@@ -121,25 +129,51 @@ def smooth_session_multi_cam(stack, smooth_param, quantile_keep_pca, newton=Fals
     d = _cuda()
     t = stack if isinstance(stack, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(stack))
     M, T, B, p = t.shape
+    if M > 8 or p not in (4, 6, 8):
+        return _smooth_session_general(t, smooth_param, quantile_keep_pca, newton)
     preds = t.to(device=d, dtype=dtype).reshape(M, T, B * p).contiguous()
     ws = dev.setup_workspace(B, T, p, dtype, d)                       # the ensemble kernel leaves max_vars in it
     obs = dev.ensemble_tiled(preds, B, p, "median", max_var=dev.setup_max_var_view(ws, B, T, p, dtype))
     prm, means, status = dev.pca_setup(obs, B, T, p, quantile_keep_pca, smooth_param, n=3, center=False,
                                        workspace=ws, mx_ready=True)
     sg = dev.sigma(3)
+    first = _lib.FIRST_PRIOR_ONLY if newton else _lib.FIRST_PRIOR_UPDATE
+    rws = dev.route_workspace(B, T, 3, p, dtype, d)                   # few keypoints x long session: parallel in time
+    filt, _, _ = dev.kf_forward(obs, prm, B, T, first=first, status=status, y_offset=means, workspace=rws)
+    if _nonpositive_variance(status):
+        # some frame had every ensemble member agree to the last bit: redo the session with the literal LU kernels
+        return _smooth_session_general(t, smooth_param, quantile_keep_pca, newton)
     if newton:
-        filt, _, st2 = dev.kf_forward(obs, prm, B, T, first=_lib.FIRST_PRIOR_ONLY, status=status, y_offset=means)
         lat = dev.unpack_rows(filt, sg, 0, B, T, 3)
         ym = dev.unpack_rows(dev.project(filt, prm, B, T), p, 0, B, T, p)
     else:
-        filt, _, _ = dev.kf_forward(obs, prm, B, T, status=status, y_offset=means)
-        out = dev.rts_backward(filt, prm, B, T, inplace=True, want_ym=True, status=status)
+        out = dev.rts_backward(filt, prm, B, T, inplace=True, want_ym=True, status=status, workspace=rws)
         lat = dev.unpack_rows(out["smth"], sg, 0, B, T, 3)
         ym = dev.unpack_rows(out["ym"], p, 0, B, T, p)
-    if bool(status.any().item()):
-        raise np.linalg.LinAlgError("Singular matrix")
+    _raise_if_singular(status)                                        # includes "< 3 good frames" from the setup
     y = (ym + means[:, None, :]).cpu().numpy().astype(np.float64)
     return dict(y=y, latent=lat.cpu().numpy().astype(np.float64), means=means.cpu().numpy().astype(np.float64))
+
+
+def _smooth_session_general(t, smooth_param, quantile_keep_pca, newton):
+    """Any ensemble size (<= 64) and any camera count: plain ensemble kernel, the parameter setup of
+    multiview_pca_smoother.py:684-731 in host numpy (as the paw path does), runtime-dimension filter / RTS
+    kernels where (3, p) has no register-resident instantiation.  Same results, not the fused device pipeline."""
+    M, T, B, p = t.shape
+    stack = t.detach().cpu().numpy().astype(np.float64) if isinstance(t, torch.Tensor) else np.asarray(t, dtype=np.float64)
+    preds, evars = _ensemble_median(stack.reshape(M, T, B * p))
+    tracks, means = [], np.empty((B, p))
+    for b in range(B):
+        yb, evb = preds[:, b * p:(b + 1) * p], evars[:, b * p:(b + 1) * p]
+        good = _good_frames(evb, quantile_keep_pca)
+        means[b] = yb[good].mean(axis=0)                                   # :698-700
+        yc = yb - means[b]
+        pca_, _ = pca(yc[good], 3)                                         # :707-708
+        m0, S0, A, Q, C = _kf_params(pca_, pca_.transform(yc)[good], smooth_param)
+        tracks.append(dict(y=yc, ev=evb, m0=m0, S0=S0, A=A, Q=Q, C=C))
+    res = _run_tracks(tracks, newton=newton)
+    y = np.stack([r[1] for r in res]) + means[:, None, :]
+    return dict(y=y, latent=np.stack([r[0] for r in res]), means=means)
 
 
 def session_dfs(y, keypoint_names, camera_names):

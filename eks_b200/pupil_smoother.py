@@ -92,12 +92,21 @@ def ensemble_kalman_smoother_pupil(markers_list, keypoint_names, tracker_name, s
     return _frames(ym, ms, mean_x, mean_y, keypoint_names, tracker_name)
 
 
-def eks_opti_smoother_pupil(markers_list, keypoint_names, tracker_name, state_transition_matrix, plot=False):
+def eks_opti_smoother_pupil(markers_list, keypoint_names, tracker_name, state_transition_matrix, plot=True):
     """pupil_smoother.py:227-364.  Like the reference it ignores `state_transition_matrix` and uses
     A = 0.99 I (:301-305).  latents_df are the Newton-recursive latents (pinned by the shipped
-    opti_eks_latents.csv); markers_df = B q + means.  (The reference rebuilds markers_df from a CSV of
-    the *standard* smoother read from a hard-coded /Users path and raises UnboundLocalError with
-    plot=False, :325-332; that quirk is not reproduced.)"""
-    trk, mean_x, mean_y = _setup(markers_list, np.diag([0.99, 0.99, 0.99]))
+    opti_eks_latents.csv).  markers_df with the reference's default plot=True: the reference then overwrites q with
+    the latents CSV of the STANDARD smoother (:325-329; its shipped kalman_smoothed_latents.csv is the standard
+    smoother at A = 0.99 I with the means already added to com_x / com_y) and returns B q + means (:332-346) --
+    reproduced here by running the standard smoother instead of reading a hard-coded /Users path, and pinned by
+    the shipped opti_eks_pupil_traces.csv.  With plot=False the reference raises UnboundLocalError (q is never
+    assigned); here that case returns markers_df = B q_newton + means.  Nothing is plotted either way."""
+    A = np.diag([0.99, 0.99, 0.99])
+    trk, mean_x, mean_y = _setup(markers_list, A)
+    if plot:
+        (q, _), = _run_tracks([trk], newton=True)
+        (ms, _), = _run_tracks([trk])
+        std_latents = np.column_stack([ms[:, 0], ms[:, 1] + mean_x, ms[:, 2] + mean_y])     # what the CSV holds
+        return _frames(std_latents @ C_PUPIL.T, q, mean_x, mean_y, keypoint_names, tracker_name)
     (q, ym), = _run_tracks([trk], newton=True)
     return _frames(ym, q, mean_x, mean_y, keypoint_names, tracker_name)

@@ -13,7 +13,13 @@
  *  - All calls are asynchronous on `stream` and return 0, or a negative EKSB_E* code
  *    (message via eksb_last_error_string()).  Numerical trouble inside a track (a
  *    non-positive pivot: the reference would raise numpy.linalg.LinAlgError) is reported
- *    per track through the optional `status` array (0 ok, 1 = non-positive pivot seen).
+ *    per track through the optional `status` array, a bit mask OR-ed into the caller's (zeroed) words:
+ *      EKSB_STATUS_PIVOT (1)      a non-positive pivot was seen;
+ *      EKSB_STATUS_NONPOS_VAR (2) a frame of the track has an ensemble variance <= 0.  The fast kernels update in
+ *                                 information form (they divide by every variance), so their output for such a
+ *                                 track is NaN where the reference -- which only needs R + C S C^T to be invertible
+ *                                 (eks/ensemble_kalman.py:112) -- stays finite: re-run the track through
+ *                                 eksb_kf_forward_generic, which does the reference's p x p LU arithmetic.
  *  - _f32 / _f64 suffix = arithmetic and storage type of every non-integer buffer.
  *  - "Track-tile" layout (all per-frame device arrays): tracks are grouped in tiles of
  *    EKSB_LANES = 32; a frame record has ROWS scalars per track;
@@ -54,6 +60,9 @@ extern "C" {
 #define EKSB_EARG (-2)    /* bad argument (null pointer, non-positive size, bad mode) */
 #define EKSB_ECUDA (-3)   /* CUDA runtime error; see eksb_last_error_string() */
 
+#define EKSB_STATUS_PIVOT 1
+#define EKSB_STATUS_NONPOS_VAR 2
+
 #define EKSB_SHARED_M0 1
 #define EKSB_SHARED_S0 2
 #define EKSB_SHARED_C 4
@@ -80,7 +89,7 @@ EKSB_API int eksb_supported_dims(int n, int p); /* 1 if (n,p) is instantiated */
  * preds is the raw prediction tensor [M][T][K] (models x frames x keypoint columns, K fastest).
  * avg = median or mean over models (:45), var = population variance / M (:46).  Medians and
  * means are bit-exact w.r.t. numpy (same summation order, no FMA contraction); NaN propagates.
- * 1 <= M <= 16. */
+ * 1 <= M <= 64 (register sort network up to 16 models, a local-memory insertion sort above). */
 EKSB_API int eksb_ensemble_f64(const double* preds, int M, long T, long K, int mode, double* avg, double* var, void* stream);
 EKSB_API int eksb_ensemble_f32(const float* preds, int M, long T, long K, int mode, float* avg, float* var, void* stream);
 
@@ -176,6 +185,19 @@ EKSB_API int eksb_kf_forward_generic_f64(const double* obs, const double* m0, co
 EKSB_API int eksb_kf_forward_generic_f32(const float* obs, const float* m0, const float* S0, const float* C, const float* A,
                                 const float* Q, const float* R, int r_shared, int shared_mask, long B, long T, int n,
                                 int p, int first, float* filt, int* status, void* stream);
+
+/* smooth_backward in the reference's literal arithmetic (eks/ensemble_kalman.py:152-162: J = solve(S, A Vf)^T by LU
+ * with partial pivoting) for any n <= 8, p <= 16 and dense A -- the backward twin of eksb_kf_forward_generic, so
+ * every shape filtering_pass accepts can also be smoothed (5 cameras: n = 3..5, p = 10).  Same records and optional
+ * outputs (ym, yv, cv) as eksb_rts_backward; smth may alias filt only when cv == NULL and pred == NULL is not
+ * required (a frame is read before it is written).  pred: optional NS-row packed records with the caller's S[t]
+ * (the reference reads its S argument and ignores Q); NULL recomputes S[t] = A Vf[t] A^T + Q (:101). */
+EKSB_API int eksb_rts_backward_generic_f64(const double* filt, const double* pred, const double* C, const double* A,
+                                  const double* Q, int shared_mask, long B, long T, int n, int p, double* smth,
+                                  double* ym, double* yv, double* cv, int* status, void* stream);
+EKSB_API int eksb_rts_backward_generic_f32(const float* filt, const float* pred, const float* C, const float* A,
+                                  const float* Q, int shared_mask, long B, long T, int n, int p, float* smth,
+                                  float* ym, float* yv, float* cv, int* status, void* stream);
 
 /* ym = C * mean over a state record buffer with `rows` rows per record (mean = rows [0,n)):
  * y_m_smooth = C ms (multiview_pca_smoother.py:745) or B q for the Newton variant (:905).
@@ -298,6 +320,32 @@ EKSB_API int eksb_csv_dlc_read_host(const char* path, double* data_host, long n_
                            char* header_host, size_t header_cap, int n_threads);
 EKSB_API int eksb_csv_dlc_write_host(const char* path, const char* header_host, const long* index_host,
                             const double* data_host, long n_rows, int n_cols);
+
+/* ---- routed filter / smoother: the library picks sequential or parallel-in-time kernels -----------------------
+ * Same contracts as eksb_kf_forward_offset (y_offset may be NULL) and eksb_rts_backward, plus a caller-owned
+ * workspace of eksb_route_workspace_bytes(B, T, n, p, sizeof(scalar)) bytes (0: this shape always runs the sequential
+ * kernels and workspace may be NULL).  The sequential kernels keep one dependency chain per track tile, so a batch with
+ * fewer tiles than the GPU has SMs -- a 2 048-track shard of configs[3] on one of 8 GPUs, the per-body-part loop of
+ * scripts/multicam_example.py:106 batched into one call -- runs at one warp's pace; with a workspace such batches go
+ * through the forward / backward half of eksb_kf_rts_scan instead (same results up to rounding; policy and the
+ * measurements behind it: csrc/eksb_scan_impl.cuh route_scan).  Requests the scan cannot serve (nll, yv, cv, a
+ * too-small or NULL workspace, an (n,p) without a scan instantiation) take the sequential kernels.  The forward and
+ * the backward call of one batch may share the workspace. */
+EKSB_API size_t eksb_route_workspace_bytes(long B, long T, int n, int p, int elem_size);
+EKSB_API int eksb_kf_forward_ws_f64(const double* obs, const double* y_offset, const double* m0, const double* S0,
+                        const double* C, const double* A, const double* Q, int shared_mask, long B, long T, int n, int p,
+                        int a_mode, int first, double* filt, double* nll, int* status, double* workspace,
+                        size_t workspace_bytes, void* stream);
+EKSB_API int eksb_kf_forward_ws_f32(const float* obs, const float* y_offset, const float* m0, const float* S0,
+                        const float* C, const float* A, const float* Q, int shared_mask, long B, long T, int n, int p,
+                        int a_mode, int first, float* filt, double* nll, int* status, float* workspace,
+                        size_t workspace_bytes, void* stream);
+EKSB_API int eksb_rts_backward_ws_f64(const double* filt, const double* C, const double* A, const double* Q, int shared_mask,
+                          long B, long T, int n, int p, int a_mode, double* smth, double* ym, double* yv, double* cv,
+                          int* status, double* workspace, size_t workspace_bytes, void* stream);
+EKSB_API int eksb_rts_backward_ws_f32(const float* filt, const float* C, const float* A, const float* Q, int shared_mask,
+                          long B, long T, int n, int p, int a_mode, float* smth, float* ym, float* yv, float* cv,
+                          int* status, float* workspace, size_t workspace_bytes, void* stream);
 
 /* EKSB_DECLS_END (new declarations go above this line) */
 #ifdef __cplusplus

@@ -158,7 +158,8 @@ def paw_setup(left_stack, right_stack, smooth_param, quantile):
 
 def ensemble_kalman_smoother_paw_asynchronous(markers_list_left_cam, markers_list_right_cam,
                                               timestamps_left_cam, timestamps_right_cam,
-                                              keypoint_names, smooth_param, quantile_keep_pca):
+                                              keypoint_names, smooth_param, quantile_keep_pca, newton=False):
+    """multiview_pca_smoother.py:34-322; newton=True is its opti twin (:326-608, Newton filter at :552)."""
     aligned = [paw_align(l.to_numpy(), r.to_numpy(), timestamps_left_cam, timestamps_right_cam)
                for l, r in zip(markers_list_left_cam, markers_list_right_cam)]
     left_stack = np.stack([a[0] for a in aligned])
@@ -167,8 +168,11 @@ def ensemble_kalman_smoother_paw_asynchronous(markers_list_left_cam, markers_lis
     ym = []
     for st in tracks:
         R = np.eye(4)
-        mf, Vf, S = core.filtering_pass(st["y"], st["m0"], st["S0"], st["C"], R, st["A"], st["Q"], st["ev"])
-        ms, _, _ = core.smooth_backward(st["y"], mf, Vf, S, st["A"], st["Q"], st["C"])
+        if newton:
+            ms = core.kalman_newton_recursive(st["y"], st["m0"], st["S0"], st["A"], st["C"], st["ev"], st["Q"])
+        else:
+            mf, Vf, S = core.filtering_pass(st["y"], st["m0"], st["S0"], st["C"], R, st["A"], st["Q"], st["ev"])
+            ms, _, _ = core.smooth_backward(st["y"], mf, Vf, S, st["A"], st["Q"], st["C"])
         ym.append(ms @ st["C"].T + means)
     T = ym[0].shape[0]
     nan = np.full(T, np.nan)
@@ -178,6 +182,13 @@ def ensemble_kalman_smoother_paw_asynchronous(markers_list_left_cam, markers_lis
                              IMG_WIDTH - ym[0][:, 2], ym[0][:, 3], nan])
     idx = dlc_index(keypoint_names)
     return {"left_df": pd.DataFrame(left, columns=idx), "right_df": pd.DataFrame(right, columns=idx)}
+
+
+def eks_opti_smoother_paw_asynchronous(markers_list_left_cam, markers_list_right_cam, timestamps_left_cam,
+                                       timestamps_right_cam, keypoint_names, smooth_param, quantile_keep_pca):
+    return ensemble_kalman_smoother_paw_asynchronous(markers_list_left_cam, markers_list_right_cam, timestamps_left_cam,
+                                                     timestamps_right_cam, keypoint_names, smooth_param,
+                                                     quantile_keep_pca, newton=True)
 
 
 # --------------------------------------------------------------------------
@@ -266,3 +277,15 @@ def eks_opti_pupil_latents(markers_list):
     st = pupil_setup(_pupil_stack(markers_list), np.diag([0.99, 0.99, 0.99]))
     q = core.kalman_newton_recursive(st["y"], st["m0"], st["S0"], st["A"], st["C"], st["ev"], st["Q"])
     return np.column_stack([q[:, 0], q[:, 1] + st["mean_x"], q[:, 2] + st["mean_y"]])
+
+
+def eks_opti_smoother_pupil(markers_list, keypoint_names, tracker_name, state_transition_matrix=None):
+    """eks_opti_smoother_pupil with its default plot=True (pupil_smoother.py:227-364).  latents_df: the Newton
+    latents.  markers_df: the reference overwrites q with the latents CSV of the STANDARD smoother (:325-329; the
+    shipped kalman_smoothed_latents.csv = the standard smoother at A = 0.99 I, means already added to com_x/com_y)
+    and forms B q + means from it (:332-337), so the means enter twice.  Reproduced as shipped."""
+    A = np.diag([0.99, 0.99, 0.99])
+    st = pupil_setup(_pupil_stack(markers_list), A)
+    q = core.kalman_newton_recursive(st["y"], st["m0"], st["S0"], st["A"], st["C"], st["ev"], st["Q"])
+    std = ensemble_kalman_smoother_pupil(markers_list, keypoint_names, tracker_name, A)["latents_df"].to_numpy()
+    return _pupil_frames(std @ st["C"].T, q, st, keypoint_names, tracker_name)

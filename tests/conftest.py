@@ -33,3 +33,27 @@ def cases_of(z, prefix_filter=None):
 @pytest.fixture(scope="session")
 def golden():
     return load_golden
+
+
+# north_star's parity bars, used verbatim by the tests: relative error of smoothed means and
+# variances <= 1e-5 in fp64 and <= 1e-3 in fp32.
+RTOL_F64 = 1e-5
+RTOL_F32 = 1e-3
+
+
+def rel(a, b, time_axis=None):
+    """Largest error of `a` against the expected `b`, each COMPONENT scaled by its own largest magnitude over time
+    (so a small covariance entry is not graded against the largest number in the array).  time_axis defaults to 0
+    for (T, ...) arrays; pass 1 for (B, T, ...).  A component that is (numerically) zero throughout -- the reference's
+    all-zero S[T-1], a structurally zero covariance entry -- is scaled by 1e-6 of the array's largest magnitude."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    if b.size == 0:
+        return 0.0
+    if b.ndim == 0 or (b.ndim == 1 and time_axis is None):
+        return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
+    ax = 0 if time_axis is None else time_axis
+    scale = np.abs(b).max(axis=ax, keepdims=True)
+    floor = max(float(np.abs(b).max()) * 1e-6, 1e-300)
+    return float((np.abs(a - b) / np.maximum(scale, floor)).max())

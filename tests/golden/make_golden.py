@@ -103,6 +103,8 @@ def pupil():
     z["shipped/latents"] = pd.read_csv(os.path.join(t, "kalman_smoothed_latents.csv"), header=[0, 1], index_col=0).to_numpy()
     z["shipped/markers"] = pd.read_csv(os.path.join(t, "kalman_smoothed_pupil_traces.csv"), header=[0, 1, 2], index_col=0).to_numpy()
     z["shipped/opti_latents"] = pd.read_csv(os.path.join(t, "opti_eks_latents.csv"), header=[0, 1], index_col=0).to_numpy()
+    # the reference's opti pupil markers (pupil_smoother.py:325-346): built from the STANDARD smoother's latents CSV
+    z["shipped/opti_markers"] = pd.read_csv(os.path.join(t, "opti_eks_pupil_traces.csv"), header=[0, 1, 2], index_col=0).to_numpy()
     np.savez_compressed(os.path.join(OUT, "pupil.npz"), **z)
     print("pupil", np.nanmax(np.abs(z["a99/latents"] - z["shipped/latents"])),
           np.nanmax(np.abs(z["a99/markers"] - z["shipped/markers"])))
@@ -123,8 +125,11 @@ def paw():
              ts_left=np.asarray(tl, dtype=np.float64), ts_right=np.asarray(tr, dtype=np.float64),
              keypoint_names=np.asarray(kp),
              left_df=out["left_df"].to_numpy(), right_df=out["right_df"].to_numpy())
+    opti = mv.eks_opti_smoother_paw_asynchronous(left, right, tl, tr, kp, 0.01, 25)      # :326, Newton filter at :552
+    z["opti_left_df"] = opti["left_df"].to_numpy()
+    z["opti_right_df"] = opti["right_df"].to_numpy()
     np.savez_compressed(os.path.join(OUT, "paw.npz"), **z)
-    print("paw", z["left_df"].shape, z["right_df"].shape)
+    print("paw", z["left_df"].shape, z["right_df"].shape, z["opti_left_df"].shape)
 
 
 def fish(n_clips=10):
@@ -219,11 +224,81 @@ def core_kats():
     print("core_kats", len(z))
 
 
+def extra_kats():
+    """Round-2 additions (own file and own seed so the round-1 fixtures stay byte-stable): a zero ensemble variance,
+    shapes outside the template instantiations, kalman_newton_recursive(max_iter>1), smooth_backward with a
+    caller-modified S, a 20-model ensemble, and a five-camera / ten-model multi-camera smoother call."""
+    rng = np.random.default_rng(777)
+    z = {}
+
+    def synth(T, p, n):
+        C = np.linalg.qr(rng.normal(size=(p, n)))[0] if p >= n else rng.normal(size=(p, n))
+        A = np.diag(rng.uniform(0.9, 1.0, size=n))
+        L = rng.normal(size=(n, n)) * 0.1
+        Q = L @ L.T + 0.01 * np.eye(n)
+        S0 = np.diag(rng.uniform(0.5, 2.0, size=n))
+        m0 = rng.normal(size=n)
+        x = np.cumsum(rng.normal(size=(T, n)) * 0.1, axis=0)
+        sd = np.exp(rng.normal(np.log(0.5), 0.8, size=(T, p)))
+        return x @ C.T + sd * rng.normal(size=(T, p)), m0, S0, C, A, Q, sd ** 2 / 5
+
+    y, m0, S0, C, A, Q, ev = synth(50, 4, 3)
+    ev[10, 2] = 0.0; ev[20, 0] = 0.0; ev[21, 0] = 0.0             # every model agreed to the last bit
+    case = core_case(y, m0, S0, C, A, Q, ev)
+    # (no Newton twin here: kalman_newton_recursive inverts D_t itself, newton_eks.py:136, so a zero variance is inf)
+    for k, v in case.items():
+        z[f"zerovar/{k}"] = v
+    for name, (T, p, n) in {"n5p10": (40, 10, 5), "n5p4": (40, 4, 5), "n7p12": (30, 12, 7), "n3p10": (60, 10, 3)}.items():
+        y, m0, S0, C, A, Q, ev = synth(T, p, n)
+        case = core_case(y, m0, S0, C, A, Q, ev)
+        case["newton"] = kalman_newton_recursive(y, m0, S0, A, C, ev, Q, max_iter=1)
+        for k, v in case.items():
+            z[f"{name}/{k}"] = v
+    y, m0, S0, C, A, Q, ev = synth(120, 4, 3)
+    q3, loss3 = kalman_newton_recursive(y, m0, S0, A, C, ev, Q, max_iter=3)
+    for k, v in dict(y=y, m0=m0, S0=S0, C=C, A=A, Q=Q, ev=ev, q3=q3, loss3=loss3,
+                     q1=kalman_newton_recursive(y, m0, S0, A, C, ev, Q, max_iter=1)).items():
+        z[f"newton3/{k}"] = v
+    case = core_case(y, m0, S0, C, A, Q, ev)
+    S_own = case["S"] * 1.1 + 0.01 * np.eye(3)                    # the reference reads S, never Q (:158-160)
+    ms, Vs, CV = ek.smooth_backward(y, case["mf"], case["Vf"], S_own, A, Q, C)
+    for k, v in dict(y=y, mf=case["mf"], Vf=case["Vf"], S_own=S_own, A=A, Q=Q, C=C, ms=ms, Vs=Vs, CV=CV).items():
+        z[f"ownS/{k}"] = v
+    st = rng.normal(size=(20, 30, 3)) * 10
+    keys = ["k0", "k1", "k2"]
+    dfs = [pd.DataFrame(st[m], columns=keys) for m in range(20)]
+    for mode in ("median", "mean"):
+        pr, va, *_ = ek.ensemble(dfs, keys, mode)
+        z[f"ens_m20/{mode}_preds"] = pr
+        z[f"ens_m20/{mode}_vars"] = va
+    z["ens_m20/stack"] = st
+    # five cameras (p = 10), ten ensemble members, through the reference's multi-camera smoother
+    M, T, ncam = 10, 300, 5
+    Cx = rng.normal(size=(2 * ncam, 3))
+    x = np.cumsum(rng.normal(size=(T, 3)) * 0.3, axis=0)
+    clean = x @ Cx.T + rng.normal(size=2 * ncam) * 50
+    sd = np.exp(rng.normal(np.log(0.5), 0.8, size=(T, 2 * ncam)))
+    stack = clean[None] + sd[None] * rng.normal(size=(M, T, 2 * ncam))
+    cams = [f"cam{c}" for c in range(ncam)]
+    mlc = [[pd.DataFrame(np.column_stack([stack[m][:, 2 * c], stack[m][:, 2 * c + 1], np.ones(T)]),
+                         columns=[f"kp_{cams[c]}_x", f"kp_{cams[c]}_y", f"kp_{cams[c]}_likelihood"]) for m in range(M)]
+           for c in range(ncam)]
+    out = mv.ensemble_kalman_smoother_multi_cam(mlc, "kp", 0.01, 25, cams)
+    z["multicam5/stack"] = stack
+    z["multicam5/ref"] = np.column_stack([out[f"{c}_df"].to_numpy()[:, :2] for c in cams])
+    np.savez_compressed(os.path.join(OUT, "extra_kats.npz"), **z)
+    print("extra_kats", len(z))
+
+
 if __name__ == "__main__":
+    if sys.argv[1:] == ["extra"]:
+        extra_kats(); pupil(); paw()
+        sys.exit(0)
     if sys.argv[1:] == ["fish"]:
         fish()
         sys.exit(0)
     core_kats()
+    extra_kats()
     mirror_mouse()
     pupil()
     paw()

@@ -3,7 +3,7 @@ import numpy as np
 import pandas as pd
 import pytest
 
-from conftest import load_golden, cases_of
+from conftest import load_golden, cases_of, rel, RTOL_F32
 from oracle import restated as o
 
 pytestmark = pytest.mark.gpu
@@ -11,10 +11,6 @@ pytestmark = pytest.mark.gpu
 CORE = cases_of(load_golden("core_kats.npz"))
 KF_CASES = [k for k in CORE if not k.startswith("ens_") and k != "denseAR"]
 RTOL64 = 1e-5   # north_star: smoothed means/variances within 1e-5 relative in fp64 (we get ~1e-13)
-
-
-def rel(a, b):
-    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
 
 
 @pytest.mark.parametrize("name", KF_CASES)
@@ -165,14 +161,17 @@ def test_large_batches_go_out_as_groups_of_tiles(dtname, tol, monkeypatch):
     grouped = run()
     monkeypatch.setenv("EKSB_PIPE", "0")
     plain = run()
-    tol_plain = 1e-9 if dtname == "float64" else 2e-3                  # different arithmetic order (north_star bars 1e-5 / 1e-3)
+    tol_plain = 1e-9 if dtname == "float64" else RTOL_F32                  # different arithmetic order (north_star bars 1e-5 / 1e-3)
+    def rel_t(x, ref):                                                 # conftest.rel on [tile][T][row][32] records
+        x, ref = x.double().reshape(-1, T, x.numel() // (dev.num_tiles(B) * T * 32), 32), ref.double().reshape(-1, T, ref.numel() // (dev.num_tiles(B) * T * 32), 32)
+        scale = ref.abs().amax(dim=1, keepdim=True).clamp_min(float(ref.abs().max()) * 1e-6)
+        return float(((x - ref).abs() / scale).max())
     for a, b, e in zip(one[:4], grouped[:4], plain[:4]):
-        scale = float(a.abs().max())
-        assert float((a - b).abs().max()) <= tol * scale
-        assert float((b - e).abs().max()) <= tol_plain * scale
+        assert rel_t(b, a) <= tol
+        assert rel_t(e, b) <= tol_plain
     for a, b in zip(one[6:], grouped[6:]):                             # block-tridiagonal solve, same grouping
-        assert float((a - b).abs().max()) <= tol * float(a.abs().max())
-    assert float((grouped[6] - grouped[1]).abs().max()) <= tol_plain * float(grouped[1].abs().max())   # == filter + RTS
+        assert rel_t(b, a) <= tol
+    assert rel_t(grouped[6], grouped[1]) <= tol_plain                  # == filter + RTS
     assert int(grouped[4].sum()) == 0 and int(grouped[5].sum()) == 0
     # a track with a non-positive ensemble variance in the last group reports through its own status slot
     monkeypatch.setenv("EKSB_PIPE", "1")
@@ -180,7 +179,7 @@ def test_large_batches_go_out_as_groups_of_tiles(dtname, tol, monkeypatch):
     obs = c["obs"].clone().reshape(-1, T, 2 * p, 32)
     obs[bad // 32, 10, p:, bad % 32] = -1e-6           # det(Id + Lam S) < 0 at that frame
     _, _, st = dev.kf_forward(obs.reshape(-1), c["prm"], B, T)
-    assert int(st[bad]) == 1 and int(st.sum()) == 1                    # status offset of the last group
+    assert int(st[bad]) & 2 and int((st != 0).sum()) == 1              # EKSB_STATUS_NONPOS_VAR, in the last group's slot
 
 
 @pytest.mark.parametrize("dtname", ["float64", "float32"])
@@ -237,7 +236,7 @@ def test_block_tridiagonal_solve_equals_rts(name):
 def test_block_tridiagonal_batched_f32_and_dense_A():
     import torch
     from eks_b200 import device as dev
-    for dtname, tol, a_diag in (("float32", 2e-3, True), ("float64", 1e-9, False)):
+    for dtname, tol, a_diag in (("float32", RTOL_F32, True), ("float64", 1e-9, False)):
         dt = getattr(torch, dtname)
         B, T, p, n = 45, 131, 4, 3
         c = _random_batch(B, T, p, n, dt, seed=11, a_diag=a_diag)
@@ -313,8 +312,10 @@ def test_batched_host_api_matches_oracle():
     B, T, p, n = 70, 140, 4, 3
     c = _random_batch(B, T, p, n, torch.float64, seed=41)
     cnt = {}
-    out = batched.smooth_tracks(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], block_tracks=32, counters=cnt)
-    assert cnt["launches"] == 7 * 3 and cnt["h2d_bytes"] == 2 * B * T * p * 8
+    out = batched.smooth_tracks(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], block_tracks=32, counters=cnt,
+                                outputs=("ms", "Vs", "ym"))
+    assert cnt["launches"] == 9 * 3 and cnt["h2d_bytes"] == 2 * B * T * p * 8
+    assert cnt["d2h_bytes"] == B * T * (3 + 6 + 4) * 8 + B * 4
     iu = np.triu_indices(n)
     for b in (0, 31, 32, 69):
         mf, Vf, S = o.filtering_pass(c["y"][b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], c["ev"][b])
@@ -331,11 +332,12 @@ def test_batched_host_api_scan_path_matches_oracle():
     from eks_b200 import batched
     B, T, p, n = 40, 4500, 4, 3
     c = _random_batch(B, T, p, n, torch.float64, seed=43)
-    auto = batched.smooth_tracks(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], block_tracks=32)   # T >= 4096 -> scan
-    seq = batched.smooth_tracks(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], block_tracks=32, scan=False)
+    full = ("ms", "Vs", "ym")
+    auto = batched.smooth_tracks(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], block_tracks=32, outputs=full)   # T >= 4096 -> scan
+    seq = batched.smooth_tracks(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], block_tracks=32, scan=False, outputs=full)
     iu = np.triu_indices(n)
-    for k in ("ms", "Vs", "ym"):
-        assert rel(auto[k].numpy(), seq[k].numpy()) < 1e-9
+    for k in full:
+        assert rel(auto[k].numpy(), seq[k].numpy(), time_axis=1) < 1e-9
     for b in (0, 39):
         mf, Vf, S = o.filtering_pass(c["y"][b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], c["ev"][b])
         ms, Vs, _ = o.smooth_backward(c["y"][b], mf, Vf, S, c["A"], c["Q"], c["C"][b])
@@ -343,7 +345,7 @@ def test_batched_host_api_scan_path_matches_oracle():
     assert int(auto["status"].sum()) == 0
 
 
-@pytest.mark.parametrize("dtname,tol", [("float64", 1e-9), ("float32", 2e-3)])
+@pytest.mark.parametrize("dtname,tol", [("float64", 1e-9), ("float32", RTOL_F32)])
 @pytest.mark.parametrize("B,T,chunk", [(3, 1000, 64), (40, 777, 100), (2, 5000, 0), (33, 129, 200)])
 def test_parallel_in_time_scan_equals_sequential(dtname, tol, B, T, chunk):
     """K4: the chunked scan reproduces the sequential kernels (and through them the oracle),
@@ -360,12 +362,12 @@ def test_parallel_in_time_scan_equals_sequential(dtname, tol, B, T, chunk):
     ym_seq = dev.unpack_rows(seq["ym"], p, 0, B, T, p).cpu().numpy().astype(np.float64)
     f_only = dev.kf_rts_scan(c["obs"], c["prm"], B, T, chunk=chunk, smooth=False)
     mf_scan = dev.unpack_rows(f_only["filt"], dev.sigma(n), 0, B, T, dev.sigma(n)).cpu().numpy().astype(np.float64)
-    assert rel(mf_scan, mf_seq) < tol
+    assert rel(mf_scan, mf_seq, time_axis=1) < tol
     out = dev.kf_rts_scan(c["obs"], c["prm"], B, T, chunk=chunk)
     assert int(out["status"].sum()) == 0
     ms_scan = dev.unpack_rows(out["smth"], dev.sigma(n), 0, B, T, dev.sigma(n)).cpu().numpy().astype(np.float64)
     ym_scan = dev.unpack_rows(out["ym"], p, 0, B, T, p).cpu().numpy().astype(np.float64)
-    assert rel(ms_scan, ms_seq) < tol and rel(ym_scan, ym_seq) < tol
+    assert rel(ms_scan, ms_seq, time_axis=1) < tol and rel(ym_scan, ym_seq, time_axis=1) < tol
     if dtname == "float64":
         b = B - 1
         mf, Vf, S = o.filtering_pass(c["y"][b], c["m0"], c["S0"], c["C"][b], np.eye(p), c["A"], c["Q"], c["ev"][b])

@@ -5,15 +5,11 @@ import numpy as np
 import pytest
 
 import hostsim
-from conftest import load_golden, cases_of
+from conftest import load_golden, cases_of, rel
 from oracle import restated as o
 
 CORE = cases_of(load_golden("core_kats.npz"))
 KF_CASES = [k for k in CORE if not k.startswith("ens_") and k != "denseAR"]
-
-
-def rel(a, b):
-    return float(np.abs(a - b).max() / np.abs(b).max())
 
 
 @pytest.mark.parametrize("name", KF_CASES)
@@ -82,7 +78,7 @@ def test_split_form_real_data(dtype, tol):
 
 
 @pytest.mark.parametrize("name", [k for k in KF_CASES if "ms" in CORE[k]] + ["T1"])
-@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 2e-3)])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 1e-3)])
 def test_block_tridiagonal_solve_equals_rts(name, dtype, tol):
     """A7: one Newton step of the block-tridiagonal system == RTS mean, H^-1 diagonal blocks == Vs
     (SURVEY fact 0.8), and == the oracle's block-Thomas restatement."""
@@ -98,7 +94,7 @@ def test_block_tridiagonal_solve_equals_rts(name, dtype, tol):
 
 
 @pytest.mark.parametrize("name,chunk", [("p4", 16), ("p4", 257), ("p4", 300), ("p8", 7), ("n2p4", 5), ("n4p6", 9), ("T2", 1)])
-@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 2e-3)])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 1e-3)])
 def test_chunked_scan_equals_sequential(name, chunk, dtype, tol):
     """K4: summaries + fold + re-run reproduce the sequential filter and smoother exactly
     (any chunk length, including ragged last chunks and a single chunk)."""
@@ -118,7 +114,7 @@ def _long_track(T, q, seed=0, p=4, n=3):
     return y, ev, np.zeros(n), np.eye(n), C, np.eye(n), q * np.eye(n)
 
 
-@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-10), (np.float32, 2e-3)])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-10), (np.float32, 1e-3)])
 def test_scan_early_writeout_equals_sequential(dtype, tol):
     """K4 early write-out: once a chunk's summary has forgotten the boundary state the summary pass
     writes the records itself; the result still equals the sequential recursion (and the scan without
@@ -149,7 +145,7 @@ def test_scan_early_writeout_never_cuts_a_slowly_forgetting_filter():
         assert rel(r[k], seq[k]) < 1e-9, k
 
 
-@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 2e-3)])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 1e-3)])
 def test_scan_mixed_chunks_some_forget_some_do_not(dtype, tol):
     """A stretch of uninformative frames (huge ensemble variance) keeps some chunks from forgetting their
     start: those go through the fold and a full re-run, their neighbours start from the records the summary

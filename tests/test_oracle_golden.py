@@ -115,6 +115,70 @@ def test_paw():
     np.testing.assert_allclose(out["right_df"].to_numpy(), z["right_df"], rtol=0, atol=1e-9, equal_nan=True)
 
 
+def test_paw_opti_twin():
+    z = load_golden("paw.npz")
+    cols = ["paw_l_x", "paw_l_y", "paw_l_likelihood", "paw_r_x", "paw_r_y", "paw_r_likelihood"]
+    left = [pd.DataFrame(a, columns=cols) for a in z["left"]]
+    right = [pd.DataFrame(a, columns=cols) for a in z["right"]]
+    out = osm.eks_opti_smoother_paw_asynchronous(
+        left, right, z["ts_left"], z["ts_right"], [str(s) for s in z["keypoint_names"]], 0.01, 25)
+    np.testing.assert_allclose(out["left_df"].to_numpy(), z["opti_left_df"], rtol=0, atol=1e-9, equal_nan=True)
+    np.testing.assert_allclose(out["right_df"].to_numpy(), z["opti_right_df"], rtol=0, atol=1e-9, equal_nan=True)
+
+
+def test_pupil_opti_markers_as_shipped():
+    """data/misc/pupil-test/opti_eks_pupil_traces.csv: markers rebuilt from the standard smoother's latents with
+    the means added twice (pupil_smoother.py:325-346)."""
+    z = load_golden("pupil.npz")
+    dfs = [pd.DataFrame(a, columns=osm.PUPIL_KEYS) for a in z["stack"]]
+    kp = [str(s) for s in z["keypoint_names"]]
+    out = osm.eks_opti_smoother_pupil(dfs, kp, "ensemble-kalman_tracker")
+    np.testing.assert_allclose(out["markers_df"].to_numpy(), z["shipped/opti_markers"], rtol=0, atol=1e-9, equal_nan=True)
+    np.testing.assert_allclose(out["latents_df"].to_numpy(), z["shipped/opti_latents"], rtol=0, atol=1e-10)
+
+
+EXTRA = cases_of(load_golden("extra_kats.npz"))
+
+
+@pytest.mark.parametrize("name", ["zerovar", "n5p10", "n5p4", "n7p12", "n3p10"])
+def test_oracle_extra_shapes_and_zero_variance(name):
+    c = EXTRA[name]
+    R = np.eye(c["C"].shape[0])
+    mf, Vf, S = o.filtering_pass(c["y"], c["m0"], c["S0"], c["C"], R, c["A"], c["Q"], c["ev"])
+    ms, Vs, CV = o.smooth_backward(c["y"], mf, Vf, S, c["A"], c["Q"], c["C"])
+    for a, b in ((mf, c["mf"]), (Vf, c["Vf"]), (S, c["S"]), (ms, c["ms"]), (Vs, c["Vs"]), (CV, c["CV"])):
+        assert np.isfinite(b).all()
+        np.testing.assert_allclose(a, b, rtol=0, atol=1e-10 * max(1.0, np.abs(b).max()))
+    if "newton" in c:
+        np.testing.assert_allclose(o.kalman_newton_recursive(c["y"], c["m0"], c["S0"], c["A"], c["C"], c["ev"], c["Q"]),
+                                   c["newton"], rtol=0, atol=1e-10)
+
+
+def test_oracle_newton_sweeps_and_own_S():
+    c = EXTRA["newton3"]
+    q3, loss = o.kalman_newton_recursive(c["y"], c["m0"], c["S0"], c["A"], c["C"], c["ev"], c["Q"], max_iter=3)
+    np.testing.assert_allclose(q3, c["q3"], rtol=0, atol=1e-10)
+    np.testing.assert_array_equal(loss, c["loss3"])
+    assert np.abs(c["q3"] - c["q1"]).max() > 1e-6              # the extra sweeps do change q (P is carried on)
+    c = EXTRA["ownS"]
+    ms, Vs, CV = o.smooth_backward(c["y"], c["mf"], c["Vf"], c["S_own"], c["A"], c["Q"], c["C"])
+    for a, b in ((ms, c["ms"]), (Vs, c["Vs"]), (CV, c["CV"])):
+        np.testing.assert_allclose(a, b, rtol=0, atol=1e-10)
+
+
+def test_oracle_twenty_model_ensemble_and_five_cameras():
+    c = EXTRA["ens_m20"]
+    for mode in ("median", "mean"):
+        pr, va = o.ensemble_arrays(c["stack"], mode)
+        np.testing.assert_array_equal(pr, c[f"{mode}_preds"])
+        np.testing.assert_array_equal(va, c[f"{mode}_vars"])
+    c = EXTRA["multicam5"]
+    st = osm.multicam_setup(c["stack"], 0.01, 25)
+    mf, Vf, S = o.filtering_pass(st["y"], st["m0"], st["S0"], st["C"], np.eye(10), st["A"], st["Q"], st["ev"])
+    ms, _, _ = o.smooth_backward(st["y"], mf, Vf, S, st["A"], st["Q"], st["C"])
+    np.testing.assert_allclose(ms @ st["C"].T + st["means"], c["ref"], rtol=0, atol=1e-8)
+
+
 def test_nll_matches_dense_gaussian():
     from scipy.stats import multivariate_normal
     rng = np.random.default_rng(3)
