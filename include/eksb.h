@@ -347,6 +347,24 @@ EKSB_API int eksb_rts_backward_ws_f32(const float* filt, const float* C, const f
                           long B, long T, int n, int p, int a_mode, float* smth, float* ym, float* yv, float* cv,
                           int* status, float* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- no-allocation variant of the parallel-in-time scan -------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs
+ * and arithmetic as eksb_kf_rts_scan_f64, but the scan's workspace is a file-scope `static __device__` array of
+ * EKSB_SCAN_STATIC_SCRATCH_BYTES inside the library (csrc/eksb_scan_f64.cu) instead of a caller buffer: the call
+ * allocates nothing (no cudaMalloc / cudaFree / allocating library routine), and every GPU that loads the library
+ * holds that much device memory until the process exits.  The first call on each device looks the array's device
+ * address up (cudaGetSymbolAddress, that device current) -- make that first call outside a graph capture.
+ * Limit: eksb_scan_workspace_bytes(B, T, n, chunk, 8) <= EKSB_SCAN_STATIC_SCRATCH_BYTES, else EKSB_EARG with a
+ * message naming both sizes (the library's own chunk policy needs < 30 MiB for any B with state dim 3; a short
+ * explicit chunk on many long tracks can need more).  All calls share the array and it keeps the last call's
+ * contents; every call clears on `stream` the words that must start at zero.  Calls that overlap on the GPU
+ * (two streams, or unordered host threads) race on it: serialise them. */
+#define EKSB_SCAN_STATIC_SCRATCH_BYTES (32u << 20)
+EKSB_API int eksb_kf_rts_scan_static_f64(const double* obs, const double* m0, const double* S0, const double* C,
+                         const double* A, const double* Q, int shared_mask, long B, long T, int n, int p, int a_mode,
+                         long chunk, double* filt, double* smth, double* ym, int* status, void* stream);
+
 /* EKSB_DECLS_END (new declarations go above this line) */
 #ifdef __cplusplus
 }
