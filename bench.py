@@ -466,7 +466,7 @@ def gpu_main(a):
     # ---- groups: the largest number of tracks whose output buffers fit beside the resident inputs
     per_track = T * (SIGMA + P_OBS) * es
     free_b, total_b = torch.cuda.mem_get_info(d)
-    margin = 1 << 30
+    margin = 256 << 20                                         # headroom for the small tensors allocated after this
     filt = ym = None
     cands = [min(B, a.group)] if a.group else [c for c in (B, 8192, 4096, 2048, 1024, 512) if c <= B]
     for G in cands:                                            # try the allocation itself: at N = 1 the 8192-track
@@ -537,11 +537,12 @@ def gpu_main(a):
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         total_ms = float(tmax.item())
     value = a.tracks * T * a.steps / (total_ms * 1e-3)
-    launches += (a.steps + a.warmup) * sum(6 if r else 2 for r in routed)
+    launches += (a.steps + a.warmup) * sum(10 if r else 2 for r in routed)
 
     # ---- roofline of the dominant kernel (algorithmic bytes per track-frame: DESIGN.md section 4).  A "launch" here is
     # one call of the entry point on one group; when the library routes the group through the parallel-in-time scan the
-    # call is three kernels (summary + fold + re-run; the summary kernel carries > 90 % of it, see profiles/).
+    # call is a warm-up kernel (K frames per chunk) + the pipelined kernel over (tile, chunk) virtual tiles (> 90 % of
+    # it, see profiles/) + three fallback kernels that exit at once.
     tf_group = Gmax * T
     n_calls = n_groups
     kern = {"kf_forward": {"ms_per_step": fwd_ms, "ms_per_launch": fwd_ms / n_calls, "bytes_per_tf": (2 * P_OBS + SIGMA) * es},
@@ -551,9 +552,10 @@ def gpu_main(a):
         k["frac"] = k["achieved_gbs"] / peak
     dom = max(kern, key=lambda k: kern[k]["ms_per_step"])
     any_routed, all_routed = any(routed), all(routed)
-    route = "parallel-in-time scan" if all_routed else ("mixed" if any_routed else "sequential warp-specialised kernels")
-    kname = {"kf_forward": ("eksb_kf_forward_ws -> " + ("scan_fwd_summary_kernel (+ fold, re-run)" if all_routed else "kf_forward_pipe_kernel")),
-             "rts_backward": ("eksb_rts_backward_ws -> " + ("scan_bwd_summary_kernel (+ fold, re-run)" if all_routed else "rts_backward_pipe_kernel"))}
+    route = ("time-split pipelined scan (warm-up + pipelined kernels over (tile, chunk) virtual tiles)" if all_routed
+             else ("mixed" if any_routed else "sequential warp-specialised kernels"))
+    kname = {"kf_forward": ("eksb_kf_forward_ws -> " + ("scan_fwd_warm_kernel + kf_forward_pipe_kernel over virtual tiles" if all_routed else "kf_forward_pipe_kernel")),
+             "rts_backward": ("eksb_rts_backward_ws -> " + ("scan_bwd_warm_kernel + rts_backward_pipe_kernel over virtual tiles" if all_routed else "rts_backward_pipe_kernel"))}
     traffic = None if any_routed else committed_traffic(a.dtype)
     if traffic is not None and Gmax != 8192:
         traffic = None                                              # the committed capture is of an 8192-track launch
@@ -578,7 +580,7 @@ def gpu_main(a):
             parg = dict(par, C=par["C"][gi * G:gi * G + nb])
             worst = max(worst, oracle_parity(obs_g[gi], parg, T, dt, tr, filt, ym, lambda gi=gi: fwd(gi), lambda gi=gi: bwd(gi)))
             checked += [lo + gi * G + b for b in tr]
-            launches += 6 if routed[gi] else 2
+            launches += 10 if routed[gi] else 2
         parity = {"max_rel": worst, "tol": tol, "tracks": checked, "frames_each": "first 2000 filtered + last 2000 smoothed",
                   "oracle": "oracle/restated.py filtering_pass + smooth_backward", "metric": "per-component max over time"}
         if any_routed and free_b > 2 * Gmax * per_track + margin:
@@ -610,7 +612,7 @@ def gpu_main(a):
             dev.kf_forward(obs_g[0], prm_g[0], nb0, T, filt=filt, status=status[:nb0], y_offset=means_s[:nb0].contiguous(), workspace=ws)
             s1.record(); torch.cuda.synchronize()
         fwd_off_ms = s0.elapsed_time(s1) * (B / nb0)             # scaled to the whole shard, like fwd_ms
-        launches += 2 * (3 if routed[0] else 1)
+        launches += 2 * (5 if routed[0] else 1)
     k1 = None
     if k1_ms > 0:
         k1b = (M_ENS * P_OBS + 2 * P_OBS + 1) * es                 # + the max_vars row handed to the setup
@@ -830,12 +832,12 @@ def config5(a, torch, dev, d, dt, es, peak):
     assert int(status.sum()) == 0
     tf = B * T
     step_b = tf * (3 * P_OBS + 3 * SIGMA) * es
-    out = {"workload": f"{B} tracks x {T} frames (p=4, n=3), {a.dtype}, 1 GPU", "route": "parallel-in-time scan (eksb_kf_forward_ws + eksb_rts_backward_ws)",
+    out = {"workload": f"{B} tracks x {T} frames (p=4, n=3), {a.dtype}, 1 GPU", "route": "time-split pipelined scan (eksb_kf_forward_ws + eksb_rts_backward_ws: warm-up + pipelined kernels over virtual tiles)",
            "chunk_frames": int(dev.lib().eksb_scan_chunk_len(B, T, N_LAT, 0, es)),
            "filter_rts": {"ms": f_ms + b_ms, "fwd_ms": f_ms, "bwd_ms": b_ms, "keypoint_frames_per_s": tf / ((f_ms + b_ms) * 1e-3),
                           "algorithmic_gbs": step_b / ((f_ms + b_ms) * 1e-3) / 1e9, "frac": step_b / ((f_ms + b_ms) * 1e-3) / 1e9 / peak,
                           "bytes_per_track_frame": (3 * P_OBS + 3 * SIGMA) * es}}
-    launches = 6 * (reps + 1)
+    launches = 10 * (reps + 1)
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["config5_" + a.dtype]
         out["filter_rts"]["dram_bytes_ncu"] = t["dram_bytes"]
@@ -847,7 +849,7 @@ def config5(a, torch, dev, d, dt, es, peak):
         tol = 1e-9 if a.dtype == "f64" else 1e-3
         tr = sorted({0, B // 3, (2 * B) // 3, B - 1})
         worst = oracle_parity(obs, par, T, dt, tr, filt, ym, fwd, bwd)
-        launches += 6
+        launches += 10
         # gate 2: the whole batch against the sequential kernels (one warp per tile: ~1 s per pass)
         f2 = dev.alloc_records(B, T, SIGMA, dt, d)
         st2 = torch.zeros(B, dtype=torch.int32, device=d)
@@ -880,8 +882,8 @@ def config5(a, torch, dev, d, dt, es, peak):
     if not a.no_parity:
         fwd(); bwd(); torch.cuda.synchronize()
         out["btd_solve"]["vs_filter_rts_max_rel"] = rel_records(sol["sol"], filt, T, SIGMA)
-        launches += 6
-    launches += 18
+        launches += 10
+    launches += 30
     del sol, obs, filt, ym
     torch.cuda.empty_cache()
     out["_launches"] = launches

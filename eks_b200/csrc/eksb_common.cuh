@@ -22,6 +22,17 @@ inline int check_launch(const char* what) {
 __host__ __device__ inline long num_tiles(long B) { return (B + kLanes - 1) / kLanes; }
 __device__ __forceinline__ long num_tiles_dev(long B) { return (B + kLanes - 1) / kLanes; }
 
+// Virtual tiles of the time-split pipelined scan (eksb_scan.cuh): with nc > 1 every (track tile, chunk of L frames)
+// pair is a tile of its own for the pipelined kernels.  cut[g*nc + c] = warm-up frames K_c of chunk c (forward: from
+// the chunk's start, backward: from its end); init = workspace records with the backward start states; the kernels
+// exit at once when *gate != 0 (some chunk never forgot its start: the fallback kernels do the pass).  nc <= 1: off.
+struct VTiles {
+  long L = 0, nc = 0;
+  const long* cut = nullptr;
+  const void* init = nullptr;
+  const int* gate = nullptr;
+};
+
 // Warp-specialised (pipelined) variants, defined in eksb_pipe_*.cu.  Return EKSB_EDIM when the
 // (n,p) pair has no pipelined instantiation (the caller then uses the plain kernel).
 template <typename T>
@@ -30,6 +41,15 @@ int kf_forward_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T*
 template <typename T>
 int rts_backward_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, int n, int p,
                       int a_mode, T* smth, T* ym, T* yv, int* status, cudaStream_t st);
+// The same kernels over virtual tiles (vt.nc > 1); diagonal-R Kalman filter / RTS smoother only.
+template <typename T>
+int kf_forward_pipe_vt(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B,
+                       long Tn, int n, int p, int a_mode, int first, T* filt, int* status, const T* yoff, VTiles vt,
+                       cudaStream_t st);
+template <typename T>
+int rts_backward_pipe_vt(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, int n, int p,
+                         int a_mode, T* smth, T* ym, int* status, VTiles vt, cudaStream_t st);
+size_t pipe_vt_target_tiles(int n, int p, int elem_size);   // virtual tiles that fill the GPU for this shape (148 x tiles per SM)
 // Policy: the pipelined kernels run every (n,p) they are instantiated for (EKSB_PIPE=0 disables them).  They
 // are at their best with up to 4 tiles per SM, so a batch of more than EKSB_PIPE_MAX_TILES (592) tiles goes
 // out as several launches over equal groups of about EKSB_PIPE_GROUP_TILES (512) tiles, back to back on the

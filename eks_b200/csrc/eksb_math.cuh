@@ -1208,6 +1208,96 @@ EKSB_HD void fwd_summary_step(const Params<T, N, P, AM>& prm, const T* rec, T (*
   for (int k = 0; k < NS; ++k) C[k] = V[k];
 }
 
+// The sensitivity-only part of fwd_summary_step: the ordinary filter step on (b, C) plus Phi <- G A Phi, without
+// the likelihood terms (J, eta).  Enough to find the frame after which a chunk's running state no longer depends on
+// the unknown state before the chunk (the warm-up kernels of the time-split pipelined scan, eksb_scan.cuh).
+template <typename T, int N, int P, int AM>
+EKSB_HD void fwd_phi_step(const Params<T, N, P, AM>& prm, const T* rec, T (*Phi)[N], T* b, T* C, bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T mp[N], S[NS], u[N], Vu[N];
+  predict<T, N, P, AM>(prm, b, C, mp, S);
+  sym_matvec<T, N>(rec, mp, u);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
+  T Psi[N][N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      if (AM == 0) {
+        Psi[i][j] = prm.A[i] * Phi[i][j];
+      } else {
+        T s = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) s += prm.A[i * N + k] * Phi[k][j];
+        Psi[i][j] = s;
+      }
+    }
+  }
+  T Mi[N][N], V[NS];                    // Mi = (Id + Lam S)^-1 ;  V = S Mi ;  G = V S^-1 = Mi^T
+  if (N <= 3) {
+    T M[N][N], adj[N][N], det;
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) {
+        T a = (i == j) ? T(1) : T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) a += rec[sym_idx<N>(i, k)] * S[sym_idx<N>(k, j)];
+        M[i][j] = a;
+      }
+    }
+    gen_adjugate<T, N>(M, adj, det);
+    ok = ok && !(det <= T(0)) && !(S[0] <= T(0));
+    const T r = rcp(det);
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) Mi[i][j] = adj[i][j] * r;
+    }
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = i; j < N; ++j) {
+        T a = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) a += S[sym_idx<N>(i, k)] * Mi[k][j];
+        V[sym_idx<N>(i, j)] = a;
+      }
+    }
+  } else {
+    T Sinv[NS], Lam[NS];
+    sym_inv<T, N>(S, Sinv, ok);
+    EKSB_UNROLL
+    for (int k = 0; k < NS; ++k) Lam[k] = Sinv[k] + rec[k];
+    sym_inv<T, N>(Lam, V, ok);
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      EKSB_UNROLL
+      for (int j = 0; j < N; ++j) {
+        T a = T(0);
+        EKSB_UNROLL
+        for (int k = 0; k < N; ++k) a += Sinv[sym_idx<N>(i, k)] * V[sym_idx<N>(k, j)];
+        Mi[i][j] = a;
+      }
+    }
+  }
+  sym_matvec<T, N>(V, u, Vu);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    EKSB_UNROLL
+    for (int j = 0; j < N; ++j) {
+      T a = T(0);
+      EKSB_UNROLL
+      for (int k = 0; k < N; ++k) a += Mi[k][i] * Psi[k][j];
+      Phi[i][j] = a;
+    }
+    b[i] = mp[i] + Vu[i];
+  }
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) C[k] = V[k];
+}
+
 // Fold a chunk summary into the filtered state just before the chunk: (m,P) -> state at the chunk's end.
 template <typename T, int N>
 EKSB_HD void fwd_apply_summary(const T* sum, T* m, T* P, bool& ok) {

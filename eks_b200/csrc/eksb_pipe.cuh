@@ -112,8 +112,9 @@ template <typename T, int N, int P, int AM, int OP, typename Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS)
 kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                        const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
-                       long B, long Tn, int first, T* __restrict__ filt, int* __restrict__ status,
-                       const T* __restrict__ yoff, int tpc, const __grid_constant__ RoleMap roles) {
+                       long B, long Tn_full, int first, T* __restrict__ filt, int* __restrict__ status,
+                       const T* __restrict__ yoff, int tpc, const __grid_constant__ RoleMap roles,
+                       const __grid_constant__ VTiles vt) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, REC = Rec<N>::FWD;
   constexpr int H = Cfg::H, F = Cfg::F, NST = Cfg::NST;
   const int TPC = tpc;
@@ -124,8 +125,21 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
   if (tile_in_cta < 0) return;                             // filler warp (keeps w % 4 placement)
   const bool is_chain = roles.h[warp] < 0;
   const int h = is_chain ? 0 : roles.h[warp];
-  const long g = (long)blockIdx.x * TPC + tile_in_cta;
-  if (g >= num_tiles_dev(B)) return;                       // chain + helpers of a tile leave together
+  // virtual tiles (eksb_scan.cuh): slot v = (tile g, chunk c) covers frames [t_begin, t_end) of tile g; it starts from
+  // the prior (c == 0) or from the exact filtered record of frame t_begin - 1 the warm-up kernel left in filt
+  const bool virt = vt.nc > 1;
+  if (virt && *vt.gate != 0) return;                       // some chunk never forgot its start: the fallback kernels run
+  const long v = (long)blockIdx.x * TPC + tile_in_cta;
+  if (v >= num_tiles_dev(B) * (virt ? vt.nc : 1)) return;  // chain + helpers of a tile leave together
+  long g = v, t_begin = 0, t_end = Tn_full;
+  if (virt) {
+    g = v / vt.nc;
+    const long c = v - g * vt.nc;
+    t_begin = c ? c * vt.L + vt.cut[g * vt.nc + c] : 0;
+    t_end = (c + 1 < vt.nc) ? (c + 1) * vt.L + vt.cut[g * vt.nc + c + 1] - 1 : Tn_full;
+  }
+  const long Tn = t_end - t_begin;                         // frames of THIS (virtual) tile
+  const bool has_prior = (t_begin == 0);
   unsigned char* tile_smem = smem_raw + (size_t)tile_in_cta * SM::kTile;
   T* raw = reinterpret_cast<T*>(tile_smem);
   T* recb = reinterpret_cast<T*>(tile_smem + SM::kRaw);
@@ -136,7 +150,7 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
   Params<T, N, P, AM> prm;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
   const long nb = (Tn + F - 1) / F;
-  const T* gsrc = obs + (g * Tn * R2) * kLanes;            // tile base (lane 0)
+  const T* gsrc = obs + ((g * Tn_full + t_begin) * R2) * kLanes;   // (virtual) tile base (lane 0)
   constexpr uint32_t kFrameBytes = R2 * kLanes * sizeof(T);
 
   if (!is_chain) {
@@ -184,7 +198,7 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
 #pragma unroll
               for (int q = 0; q < P; ++q) cur[q] -= mu[q];
             }
-            nonpos = nonpos || (any_nonpos<T, P>(cur + P) && !(first == kPriorOnly && k == 0 && j == 0));
+            nonpos = nonpos || (any_nonpos<T, P>(cur + P) && !(has_prior && first == kPriorOnly && k == 0 && j == 0));
             if constexpr (kOuter) fwd_prep_outer<T, N, P>(prm.C, CC, cur, cur + P, rec);
             else fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
 #pragma unroll
@@ -213,6 +227,13 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
     for (int i = 0; i < N; ++i) m[i] = pm[i];
     load_sym<T, N>(V, ps);
   }
+  if (!has_prior) {                                        // exact filtered state of frame t_begin - 1 (warm-up kernel)
+    const T* s0 = filt + ((g * Tn_full + t_begin - 1) * SG) * kLanes + lane;
+#pragma unroll
+    for (int i = 0; i < N; ++i) m[i] = s0[i * kLanes];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) V[i] = s0[(N + i) * kLanes];
+  }
   bool ok = true;
   BtdConst<T, N> bc;
   T iS0[NS], iS0m0[N];
@@ -224,13 +245,13 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
     for (int i = 0; i < N; ++i) m[i] = T(0);
 #pragma unroll
     for (int i = 0; i < NS; ++i) V[i] = T(0);
-  } else if (first == kPriorOnly) {
+  } else if (has_prior && first == kPriorOnly) {
     T Vi[NS];
     sym_inv<T, N>(V, Vi, ok);
 #pragma unroll
     for (int i = 0; i < NS; ++i) V[i] = Vi[i];
   }
-  T* f = filt + (g * Tn * SG) * kLanes + lane;
+  T* f = filt + ((g * Tn_full + t_begin) * SG) * kLanes + lane;
   // covariance carried as V = Nm * rr between frames (fwd_chain_scaled) where the fast path applies
   constexpr bool kScaled = (OP == 0 && AM == 0 && N <= 3);
   T Nm[NS], rr = T(1);
@@ -268,7 +289,7 @@ kf_forward_pipe_kernel(const T* __restrict__ obs, const T* __restrict__ m0, cons
 #pragma unroll
       for (int j = 0; j < F; ++j) {
         const long t = k * F + j;
-        if (t < Tn) frame(src, j, t == 0, t == Tn - 1);
+        if (t < Tn) frame(src, j, has_prior && t == 0, t == Tn - 1);
       }
     }
     f += F * SG * kLanes;
@@ -498,8 +519,9 @@ kf_forward_pipe3_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
 template <typename T, int N, int P, int AM, int OP, int OUT, typename Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS)
 rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
-                         int shared_mask, long B, long Tn, T* smth, T* __restrict__ ym, T* __restrict__ yv,
-                         int* __restrict__ status, int tpc, const __grid_constant__ RoleMap roles) {
+                         int shared_mask, long B, long Tn_full, T* smth, T* __restrict__ ym, T* __restrict__ yv,
+                         int* __restrict__ status, int tpc, const __grid_constant__ RoleMap roles,
+                         const __grid_constant__ VTiles vt) {
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, REC = Rec<N>::BWD;
   constexpr int H = Cfg::H, F = Cfg::F, NST = Cfg::NST;
   const int TPC = tpc;
@@ -510,8 +532,24 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
   if (tile_in_cta < 0) return;
   const bool is_chain = roles.h[warp] < 0;
   const int h = is_chain ? 0 : roles.h[warp];
-  const long g = (long)blockIdx.x * TPC + tile_in_cta;
-  if (g >= num_tiles_dev(B)) return;
+  // virtual tiles (eksb_scan.cuh): slot v = (tile g, chunk c) smooths frames [t_lo, t_hi] of tile g downwards; below
+  // the track's last chunk its first frame t_hi = w_c is GIVEN (exact smoothed state from the warm-up kernel, in vinit)
+  const bool virt = vt.nc > 1;
+  if (virt && *vt.gate != 0) return;
+  const long v = (long)blockIdx.x * TPC + tile_in_cta;
+  if (v >= num_tiles_dev(B) * (virt ? vt.nc : 1)) return;
+  long g = v, t_lo = 0, t_hi = Tn_full - 1;
+  const T* vinit = nullptr;
+  if (virt) {
+    g = v / vt.nc;
+    const long c = v - g * vt.nc;
+    if (c > 0) t_lo = c * vt.L - vt.cut[g * vt.nc + c - 1] + 1;
+    if (c + 1 < vt.nc) {
+      t_hi = (c + 1) * vt.L - vt.cut[g * vt.nc + c];
+      vinit = static_cast<const T*>(vt.init) + ((g * vt.nc + c) * SG) * kLanes + lane;
+    }
+  }
+  const long Tn = t_hi - t_lo + 1;                         // frames of THIS (virtual) tile
   unsigned char* tile_smem = smem_raw + (size_t)tile_in_cta * SM::kTile;
   T* raw = reinterpret_cast<T*>(tile_smem);
   T* recb = reinterpret_cast<T*>(tile_smem + SM::kRaw);
@@ -522,7 +560,7 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
   Params<T, N, P, AM> prm;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
   const long nb = (Tn + F - 1) / F;
-  const T* gsrc = filt + (g * Tn * SG) * kLanes;
+  const T* gsrc = filt + ((g * Tn_full + t_lo) * SG) * kLanes;
   constexpr uint32_t kFrameBytes = SG * kLanes * sizeof(T);
   bool ok = true;
 
@@ -562,13 +600,14 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
           if constexpr (OP == 1) {
             btd_bwd_prep<T, N>(bc, cur, cur + N, terminal, rec);
           } else {
-            if (terminal) {                                // last frame: ms = mf, Vs = Vf  (:152-153)
+            if (terminal) {                                // last frame: ms = mf, Vs = Vf  (:152-153); or, in a
+                                                           // virtual tile below the last chunk, the given state
 #pragma unroll
               for (int r = 0; r < N * N; ++r) rec[r] = T(0);
 #pragma unroll
-              for (int r = 0; r < NS; ++r) rec[N * N + r] = cur[N + r];
+              for (int r = 0; r < NS; ++r) rec[N * N + r] = vinit ? vinit[(N + r) * kLanes] : cur[N + r];
 #pragma unroll
-              for (int r = 0; r < N; ++r) rec[N * N + NS + r] = cur[r];
+              for (int r = 0; r < N; ++r) rec[N * N + NS + r] = vinit ? vinit[r * kLanes] : cur[r];
             } else {
               bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
             }
@@ -610,9 +649,9 @@ rts_backward_pipe_kernel(const T* filt, const T* __restrict__ C, const T* __rest
   for (int i = 0; i < NS; ++i) Vs[i] = T(0);
   constexpr bool kYm = (OUT & 1) != 0, kYv = (OUT & 2) != 0;
   // running output pointers at frame t = T-1 (the first frame the chain emits); they walk down
-  T* so = smth + ((g * Tn + (Tn - 1)) * SG) * kLanes + lane;
-  T* ymo = kYm ? ym + ((g * Tn + (Tn - 1)) * P) * kLanes + lane : nullptr;
-  T* yvo = kYv ? yv + ((g * Tn + (Tn - 1)) * P) * kLanes + lane : nullptr;
+  T* so = smth + ((g * Tn_full + t_hi) * SG) * kLanes + lane;
+  T* ymo = kYm ? ym + ((g * Tn_full + t_hi) * P) * kLanes + lane : nullptr;
+  T* yvo = kYv ? yv + ((g * Tn_full + t_hi) * P) * kLanes + lane : nullptr;
   // one frame of the chain: record j of the current batch -> frame (base pointers) - j
   auto frame = [&](const T* src, int j) {
     T rec[REC];

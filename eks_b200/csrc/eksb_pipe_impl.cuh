@@ -83,6 +83,9 @@ inline int make_roles(int tpc, int H, float w_chain, float w_helper, RoleMap& rm
 #define EKSB_PIPE_TPC 4
 #endif
 
+// tiles the launch covers: real track tiles, or (tile, chunk) pairs of the time-split scan
+inline long vtile_count(long B, const VTiles& vt) { return num_tiles(B) * (vt.nc > 1 ? vt.nc : 1); }
+
 template <typename T, int ROWS_IN, int REC, int H, int F, int NST> struct TileBytes {
   static constexpr size_t value = PipeSmem<T, ROWS_IN, REC, PipeCfg<H, F, NST, 1>>::kTile;
 };
@@ -147,16 +150,18 @@ constexpr float kFwdChainW = 118, kFwdHelperW = 125, kBwdChainW = 103, kBwdHelpe
 
 template <typename T, int N, int P, int AM, int OP, typename Auto>
 static int launch_fwd_cfg(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
-                          long B, long Tn, int first, T* filt, int* status, const T* yoff, cudaStream_t st) {
+                          long B, long Tn, int first, T* filt, int* status, const T* yoff, cudaStream_t st,
+                          const VTiles& vt = VTiles()) {
   using Cfg = typename Auto::type;
   auto kern = kf_forward_pipe_kernel<T, N, P, AM, OP, Cfg>;
-  const int tpc = pick_tpc(num_tiles(B), Cfg::TPC, Auto::kTileSmem);
+  const long nvt = vtile_count(B, vt);
+  const int tpc = pick_tpc(nvt, Cfg::TPC, Auto::kTileSmem);
   const size_t smem = Auto::kTileSmem * tpc;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(Auto::kTileSmem * Cfg::TPC));
-  const unsigned grid = (unsigned)((num_tiles(B) + tpc - 1) / tpc);
+  const unsigned grid = (unsigned)((nvt + tpc - 1) / tpc);
   RoleMap rm;
   const int warps = make_roles(tpc, Cfg::H, kFwdChainW, kFwdHelperW, rm);
-  kern<<<grid, warps * kLanes, smem, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, tpc, rm);
+  kern<<<grid, warps * kLanes, smem, st>>>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, tpc, rm, vt);
   return check_launch("kf_forward_pipe_kernel");
 }
 
@@ -232,42 +237,45 @@ static int launch_fwd_pipe3(const T* obs, const T* m0, const T* S0, const T* C, 
 // that to ~6.4 TB/s.  It needs ~100 KB per f64 tile, so it is used when the tiles of an SM fit.
 template <typename T, int N, int P, int AM, int OP = 0>
 static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
-                           long B, long Tn, int first, T* filt, int* status, const T* yoff, cudaStream_t st) {
+                           long B, long Tn, int first, T* filt, int* status, const T* yoff, cudaStream_t st,
+                           const VTiles& vt = VTiles()) {
   using Shallow = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, EKSB_FWD_F, EKSB_FWD_NST>;
   using Deep = AutoCfg<T, EKSB_FWD_DEEP_H, 2 * P, Rec<N>::FWD, 8, 4>;
+  const long nvt = vtile_count(B, vt);
   if constexpr (OP == 0 && AM == 0 && N <= 3 && Auto3<T, N, P, Fwd3Helpers<T>::value>::ok) {
-    const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
+    const long per_sm = (nvt + kSMs - 1) / kSMs;
     // Measured (f64, 100 000 frames, sustained): one tile per SM 16.2 -> 13.5 ms (the pass runs at the chain's
     // pace); two tiles per SM 18.3 -> 20.8 ms (the FP64 pipes of the two helper schedulers saturate once they
     // also carry the mean warps, and the two-role kernel is already HBM-bound there).  Hence: one tile per SM only.
     static const int max_per_sm = getenv("EKSB_FWD3_MAX") ? atoi(getenv("EKSB_FWD3_MAX")) : 1;
-    if (per_sm <= max_per_sm && per_sm <= 2)
+    if (vt.nc <= 1 && per_sm <= max_per_sm && per_sm <= 2)     // (the three-role kernel has no virtual-tile mode)
       return launch_fwd_pipe3<T, N, P>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff,
                                        (int)(per_sm < 1 ? 1 : per_sm), st);
   }
   if constexpr (N <= 3 && Deep::ok) {
-    const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
+    const long per_sm = (nvt + kSMs - 1) / kSMs;
     static const bool shallow_only = getenv("EKSB_FWD_SHALLOW") != nullptr;
     if (!shallow_only && per_sm <= Deep::TPC && per_sm * Deep::kTileSmem + 1024 <= kCtaSmemBudget)
-      return launch_fwd_cfg<T, N, P, AM, OP, Deep>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st);
+      return launch_fwd_cfg<T, N, P, AM, OP, Deep>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st, vt);
   }
   if (!Shallow::ok) return EKSB_EDIM;
-  return launch_fwd_cfg<T, N, P, AM, OP, Shallow>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st);
+  return launch_fwd_cfg<T, N, P, AM, OP, Shallow>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st, vt);
 }
 
 template <typename T, int N, int P, int AM, int OP, int OUT, typename Auto>
 static int launch_bwd_cfg(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
-                          T* smth, T* ym, T* yv, int* status, cudaStream_t st) {
+                          T* smth, T* ym, T* yv, int* status, cudaStream_t st, const VTiles& vt = VTiles()) {
   using Cfg = typename Auto::type;
   auto kern = rts_backward_pipe_kernel<T, N, P, AM, OP, OUT, Cfg>;
-  const int tpc = pick_tpc(num_tiles(B), Cfg::TPC, Auto::kTileSmem);
+  const long nvt = vtile_count(B, vt);
+  const int tpc = pick_tpc(nvt, Cfg::TPC, Auto::kTileSmem);
   const size_t smem = Auto::kTileSmem * tpc;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(Auto::kTileSmem * Cfg::TPC));
-  const unsigned grid = (unsigned)((num_tiles(B) + tpc - 1) / tpc);
+  const unsigned grid = (unsigned)((nvt + tpc - 1) / tpc);
   RoleMap rm;
   static const bool no_split = getenv("EKSB_BWD_NO_SPLIT") != nullptr;
   const int warps = make_roles(tpc, Cfg::H, kBwdChainW, kBwdHelperW, rm, !no_split);
-  kern<<<grid, warps * kLanes, smem, st>>>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, tpc, rm);
+  kern<<<grid, warps * kLanes, smem, st>>>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, tpc, rm, vt);
   return check_launch("rts_backward_pipe_kernel");
 }
 
@@ -277,7 +285,8 @@ static int launch_bwd_cfg(const T* filt, const T* C, const T* A, const T* Q, int
 // 4-frame batches) is used.  Wide is instantiated for state dim <= 3 only (every shipped config).
 template <typename T, int N, int P, int AM, int OP, int OUT>
 static int launch_bwd_pipe_out(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
-                               T* smth, T* ym, T* yv, int* status, cudaStream_t st) {
+                               T* smth, T* ym, T* yv, int* status, cudaStream_t st, const VTiles& vt = VTiles()) {
+  const long nvt = vtile_count(B, vt);
   using Narrow = AutoCfg<T, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_F, EKSB_BWD_NST>;
   using Wide = AutoCfg<T, EKSB_BWD_WIDE_H, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_WIDE_F, EKSB_BWD_WIDE_NST>;
   // "Solo": an SM holds one tile, so the whole shared memory and all four schedulers serve it -- 4 helpers on
@@ -285,28 +294,28 @@ static int launch_bwd_pipe_out(const T* filt, const T* C, const T* A, const T* Q
   using Solo = AutoCfg<T, EKSB_BWD_SOLO_H, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_SOLO_F, 3>;
   if constexpr (N <= 3 && Solo::ok) {
     static const bool no_solo = getenv("EKSB_BWD_NO_SOLO") != nullptr;
-    if (!no_solo && num_tiles(B) <= kSMs)
-      return launch_bwd_cfg<T, N, P, AM, OP, OUT, Solo>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+    if (!no_solo && nvt <= kSMs)
+      return launch_bwd_cfg<T, N, P, AM, OP, OUT, Solo>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st, vt);
   }
   if constexpr (N <= 3 && Wide::ok) {
-    const long per_sm = (num_tiles(B) + kSMs - 1) / kSMs;
+    const long per_sm = (nvt + kSMs - 1) / kSMs;
     static const bool narrow_only = getenv("EKSB_BWD_NARROW") != nullptr;
     if (!narrow_only && per_sm <= Wide::TPC && per_sm * Wide::kTileSmem + 1024 <= kCtaSmemBudget)
-      return launch_bwd_cfg<T, N, P, AM, OP, OUT, Wide>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+      return launch_bwd_cfg<T, N, P, AM, OP, OUT, Wide>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st, vt);
   }
   if (!Narrow::ok) return EKSB_EDIM;
-  return launch_bwd_cfg<T, N, P, AM, OP, OUT, Narrow>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+  return launch_bwd_cfg<T, N, P, AM, OP, OUT, Narrow>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st, vt);
 }
 
 // The projections are compile-time variants: a runtime `if (yv)` leaves ~50 predicated-off
 // FMAs per frame on the chain warp's issue path (seen in the ncu source page, round 1).
 template <typename T, int N, int P, int AM, int OP = 0>
 static int launch_bwd_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, T* smth,
-                           T* ym, T* yv, int* status, cudaStream_t st) {
-  if (ym && yv) return launch_bwd_pipe_out<T, N, P, AM, OP, 3>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
-  if (ym) return launch_bwd_pipe_out<T, N, P, AM, OP, 1>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
-  if (yv) return launch_bwd_pipe_out<T, N, P, AM, OP, 2>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
-  return launch_bwd_pipe_out<T, N, P, AM, OP, 0>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st);
+                           T* ym, T* yv, int* status, cudaStream_t st, const VTiles& vt = VTiles()) {
+  if (ym && yv) return launch_bwd_pipe_out<T, N, P, AM, OP, 3>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st, vt);
+  if (ym) return launch_bwd_pipe_out<T, N, P, AM, OP, 1>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st, vt);
+  if (yv) return launch_bwd_pipe_out<T, N, P, AM, OP, 2>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st, vt);
+  return launch_bwd_pipe_out<T, N, P, AM, OP, 0>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, yv, status, st, vt);
 }
 
 // pipelined instantiations: state dim <= 4 (larger records do not fit the shared-memory ring)
@@ -327,7 +336,47 @@ int kf_forward_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T*
 }
 #endif
 
+#ifdef EKSB_PIPE_FWD
+template <typename T>
+int kf_forward_pipe_vt(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B,
+                       long Tn, int n, int p, int a_mode, int first, T* filt, int* status, const T* yoff, VTiles vt,
+                       cudaStream_t st) {
+#define X(N_, P_)                                                                                                          \
+  if (n == N_ && p == P_)                                                                                                  \
+    return a_mode == EKSB_A_DIAG                                                                                           \
+               ? launch_fwd_pipe<T, N_, P_, 0>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st, vt) \
+               : launch_fwd_pipe<T, N_, P_, 1>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, first, filt, status, yoff, st, vt);
+  EKSB_FOR_EACH_PIPE_DIM(X)
+#undef X
+  return EKSB_EDIM;
+}
+// Virtual tiles that fill the GPU: 148 SMs x the tiles one SM holds with the ring the forward pass would use
+// (the backward rings are no larger).
+inline size_t pipe_vt_target_tiles_impl(int n, int p, int elem_size) {
+#define X(N_, P_)                                                                                              \
+  if (n == N_ && p == P_)                                                                                      \
+    return (size_t)kSMs * (elem_size == 8 ? AutoCfg<double, kFwdHelpers, 2 * P_, Rec<N_>::FWD, EKSB_FWD_F, EKSB_FWD_NST>::TPC \
+                                          : AutoCfg<float, kFwdHelpers, 2 * P_, Rec<N_>::FWD, EKSB_FWD_F, EKSB_FWD_NST>::TPC);
+  EKSB_FOR_EACH_PIPE_DIM(X)
+#undef X
+  return 0;
+}
+#endif
+
 #ifdef EKSB_PIPE_BWD
+template <typename T>
+int rts_backward_pipe_vt(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, int n, int p,
+                         int a_mode, T* smth, T* ym, int* status, VTiles vt, cudaStream_t st) {
+#define X(N_, P_)                                                                                                       \
+  if (n == N_ && p == P_)                                                                                               \
+    return a_mode == EKSB_A_DIAG                                                                                        \
+               ? launch_bwd_pipe<T, N_, P_, 0>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, (T*)nullptr, status, st, vt) \
+               : launch_bwd_pipe<T, N_, P_, 1>(filt, C, A, Q, shared_mask, B, Tn, smth, ym, (T*)nullptr, status, st, vt);
+  EKSB_FOR_EACH_PIPE_DIM(X)
+#undef X
+  return EKSB_EDIM;
+}
+
 template <typename T>
 int rts_backward_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, int n, int p,
                       int a_mode, T* smth, T* ym, T* yv, int* status, cudaStream_t st) {

@@ -51,7 +51,8 @@ scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
                         const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask,
                         long B, long Tn, long L, long nc, int early_out, int first, const T* __restrict__ yoff,
                         T* __restrict__ fsum, long* __restrict__ fcut, int* __restrict__ alive, T* __restrict__ filt,
-                        int* __restrict__ status) {
+                        int* __restrict__ status, const int* __restrict__ gate) {
+  if (gate && *gate == 0) return;   // fallback path of the time-split scan: only when some chunk never forgot its start
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, SR = ScanRec<N>::FWD;
   extern __shared__ __align__(16) unsigned char scan_smem[];
   const int lane = threadIdx.x & 31;
@@ -113,7 +114,8 @@ scan_fwd_summary_kernel(const T* __restrict__ obs, const T* __restrict__ m0, con
 template <typename T, int N>
 __global__ void __launch_bounds__(kLanes)
 scan_fwd_fold_kernel(const T* __restrict__ filt, const T* __restrict__ fsum, long B, long Tn, long L, long nc,
-                     const int* __restrict__ alive, T* __restrict__ finit, int* __restrict__ status) {
+                     const int* __restrict__ alive, T* __restrict__ finit, int* __restrict__ status, const int* __restrict__ gate) {
+  if (gate && *gate == 0) return;   // fallback path of the time-split scan: only when some chunk never forgot its start
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::FWD;
   if (*alive == 0) return;       // every chunk wrote its own last frame: the re-run reads its start states from filt
   const int lane = threadIdx.x;
@@ -157,7 +159,8 @@ __global__ void __launch_bounds__(kScanWarps* kLanes)
 scan_fwd_rerun_kernel(const T* __restrict__ obs, const T* __restrict__ m0, const T* __restrict__ S0,
                       const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q, int shared_mask, long B,
                       long Tn, long L, long nc, long c_lo, long c_hi, int first0, const T* __restrict__ yoff,
-                      const T* __restrict__ finit, const long* __restrict__ fcut, T* filt, int* __restrict__ status) {
+                      const T* __restrict__ finit, const long* __restrict__ fcut, T* filt, int* __restrict__ status, const int* __restrict__ gate) {
+  if (gate && *gate == 0) return;   // fallback path of the time-split scan: only when some chunk never forgot its start
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
   const int lane = threadIdx.x & 31;
   const long span = c_hi - c_lo;
@@ -217,7 +220,8 @@ __global__ void __launch_bounds__(kScanWarps* kLanes, N <= 3 ? 3 : 1)
 scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A,
                         const T* __restrict__ Q, int shared_mask, long B, long Tn, long L, long nc, int early_out,
                         T* __restrict__ bsum, long* __restrict__ bcut, int* __restrict__ alive, T* smth, T* ym,
-                        int* __restrict__ status) {
+                        int* __restrict__ status, const int* __restrict__ gate) {
+  if (gate && *gate == 0) return;   // fallback path of the time-split scan: only when some chunk never forgot its start
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
   extern __shared__ __align__(16) unsigned char scan_smem[];
   const int lane = threadIdx.x & 31;
@@ -263,7 +267,8 @@ scan_bwd_summary_kernel(const T* filt, const T* __restrict__ C, const T* __restr
 template <typename T, int N>
 __global__ void __launch_bounds__(kLanes)
 scan_bwd_fold_kernel(const T* __restrict__ smth, const T* __restrict__ bsum, long B, long Tn, long L, long nc,
-                     const int* __restrict__ alive, T* __restrict__ binit) {
+                     const int* __restrict__ alive, T* __restrict__ binit, const int* __restrict__ gate) {
+  if (gate && *gate == 0) return;   // fallback path of the time-split scan: only when some chunk never forgot its start
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
   if (*alive == 0) return;       // every chunk smoothed its own first frame: the re-run reads it from smth
   const int lane = threadIdx.x;
@@ -294,7 +299,8 @@ __global__ void __launch_bounds__(kScanWarps* kLanes)
 scan_bwd_rerun_kernel(const T* filt, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
                       int shared_mask, long B, long Tn, long L, long nc, long c_lo, long c_hi,
                       const T* __restrict__ binit, const long* __restrict__ bcut, T* smth, T* ym,
-                      int* __restrict__ status) {
+                      int* __restrict__ status, const int* __restrict__ gate) {
+  if (gate && *gate == 0) return;   // fallback path of the time-split scan: only when some chunk never forgot its start
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA;
   const int lane = threadIdx.x & 31;
   const long span = c_hi - c_lo;
@@ -326,6 +332,147 @@ scan_bwd_rerun_kernel(const T* filt, const T* __restrict__ C, const T* __restric
                                                       ym ? ym + base * P + lane : nullptr, nullptr, nullptr, t1 - t0,
                                                       terminal, ms, Vs);
   if (b < B && status) set_status(status + b, ok, false);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Time-split pipelined scan (the primary parallel-in-time route; the summary / fold / re-run kernels above are its
+// fallback).  A track tile's timeline is cut into nc chunks of L frames and every (tile, chunk) pair becomes a
+// "virtual tile" of the TMA-fed warp-specialised kernels (eksb_pipe.cuh), so a batch with few real tiles still puts
+// ~4 tiles on every SM -- the regime in which those kernels run on the HBM roofline.  What a virtual tile needs is an
+// exact start state, and the filter provides it almost for free: it forgets its start exponentially, so
+//   forward : the ordinary filter started at frame c L from (0, 0), carrying the sensitivity Phi of its state to the
+//             unknown state before the chunk, IS the exact filter once |Phi| < ScanCut -- after K_c frames
+//             (150-800 on the shapes of BASELINE.json).  The warm-up kernel below runs just those K_c frames per
+//             chunk, one warp per (tile, chunk), writes the exact filtered record of frame c L + K_c - 1 and K_c;
+//             virtual tile c then covers frames [c L + K_c, (c+1) L + K_{c+1} - 1): it carries on through the next
+//             chunk's warm-up frames, so nothing is run twice except the K frames of the warm-up itself;
+//   backward: the same with the smoothing element (E, g, L): after K_c frames down from the chunk's end, E is dead
+//             and (g, L) is the exact smoothed state of frame w_c = (c+1) L - K_c; it goes to the workspace (the
+//             records may be smoothed in place, and the fallback needs them untouched) and virtual tile c covers
+//             frames (w_{c-1}, w_c], emitting frame w_c from the workspace.
+// A chunk that has not forgotten by its end (tiny process noise, a blind stretch) sets the gate: the virtual-tile
+// kernels then exit at once and the summary / fold / re-run kernels above do the whole pass, exactly, as before.
+// ---------------------------------------------------------------------------------------------------------
+template <typename T, int N, int P, int AM, bool OFF>
+__global__ void __launch_bounds__(kScanWarps* kLanes)
+scan_fwd_warm_kernel(const T* __restrict__ obs, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
+                     int shared_mask, long B, long Tn, long L, long nc, const T* __restrict__ yoff,
+                     long* __restrict__ fcut, int* __restrict__ gate, T* __restrict__ filt) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
+  const int lane = threadIdx.x & 31;
+  const long tiles = num_tiles_dev(B);
+  const long w = (long)blockIdx.x * kScanWarps + (threadIdx.x >> 5);
+  if (w >= tiles * (nc - 1)) return;
+  const long g = w / (nc - 1), c = w - g * (nc - 1) + 1;
+  const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
+  Params<T, N, P, AM> prm;
+  load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
+  const T* mu = OFF ? yoff + bp * P : nullptr;
+  const long t0 = c * L, n = ((c + 1) * L < Tn ? (c + 1) * L : Tn) - t0;
+  const T* o = obs + ((g * Tn + t0) * R2) * kLanes + lane;
+  T Phi[N][N], bb[N], Cc[NS];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    bb[i] = T(0);
+#pragma unroll
+    for (int j = 0; j < N; ++j) Phi[i][j] = (i == j) ? T(1) : T(0);
+  }
+#pragma unroll
+  for (int i = 0; i < NS; ++i) Cc[i] = T(0);
+  T nxt[R2];
+#pragma unroll
+  for (int r = 0; r < R2; ++r) nxt[r] = o[r * kLanes];
+  bool ok = true, dead = false;
+  long t = 0;
+  while (t < n - 1) {                                       // the cut must leave the chunk at least one frame
+    T cur[R2], rec[Rec<N>::FWD];
+#pragma unroll
+    for (int r = 0; r < R2; ++r) cur[r] = nxt[r];
+#pragma unroll
+    for (int r = 0; r < R2; ++r) nxt[r] = o[((t + 1) * R2 + r) * kLanes];
+    if (OFF) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) cur[j] -= mu[j];
+    }
+    fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
+    fwd_phi_step<T, N, P, AM>(prm, rec, Phi, bb, Cc, ok);
+    ++t;
+    if ((t & 15) == 0) {
+      T mx = T(0);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) mx = fmax(mx, fabs(Phi[i][j]));
+      }
+      if (__all_sync(0xffffffffu, mx < ScanCut<T>::value)) { dead = true; break; }
+    }
+  }
+  if (dead) {                                               // (bb, Cc) is the exact filtered state of frame t0 + t - 1
+    T* f = filt + ((g * Tn + t0 + t - 1) * SG) * kLanes + lane;
+#pragma unroll
+    for (int i = 0; i < N; ++i) f[i * kLanes] = bb[i];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) f[(N + i) * kLanes] = Cc[i];
+  }
+  if (lane == 0) {
+    fcut[g * nc + c] = dead ? t : n;
+    if (!dead) atomicOr(gate, 1);
+  }
+}
+
+template <typename T, int N, int P, int AM>
+__global__ void __launch_bounds__(kScanWarps* kLanes)
+scan_bwd_warm_kernel(const T* __restrict__ filt, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
+                     int shared_mask, long B, long Tn, long L, long nc, long* __restrict__ bcut, int* __restrict__ gate,
+                     T* __restrict__ binit) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD;
+  const int lane = threadIdx.x & 31;
+  const long tiles = num_tiles_dev(B);
+  const long w = (long)blockIdx.x * kScanWarps + (threadIdx.x >> 5);
+  if (w >= tiles * (nc - 1)) return;
+  const long g = w / (nc - 1), c = w - g * (nc - 1);         // chunks [0, nc-1): the last one starts at the track's end
+  const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
+  Params<T, N, P, AM> prm;
+  load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
+  const T* f = filt + ((g * Tn + c * L) * SG) * kLanes + lane;   // chunk c is full length (c < nc - 1)
+  T acc[SR];
+#pragma unroll
+  for (int i = 0; i < SR; ++i) acc[i] = T(0);
+#pragma unroll
+  for (int i = 0; i < N; ++i) acc[i * N + i] = T(1);
+  T nxt[SG];
+#pragma unroll
+  for (int r = 0; r < SG; ++r) nxt[r] = f[((L - 1) * SG + r) * kLanes];
+  bool ok = true, dead = false;
+  long done = 0;
+  while (done < L - 2) {                                     // leave the virtual tile below at least one frame of its own
+    T cur[SG], rec[Rec<N>::BWD];
+#pragma unroll
+    for (int r = 0; r < SG; ++r) cur[r] = nxt[r];
+    const long tn = L - 2 - done;                            // next frame down (>= 0 inside the loop)
+#pragma unroll
+    for (int r = 0; r < SG; ++r) nxt[r] = f[(tn * SG + r) * kLanes];
+    bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
+    bwd_summary_step<T, N>(rec, acc);
+    ++done;
+    if ((done & 15) == 0) {
+      T mx = T(0);
+#pragma unroll
+      for (int i = 0; i < N * N; ++i) mx = fmax(mx, fabs(acc[i]));
+      if (__all_sync(0xffffffffu, mx < ScanCut<T>::value)) { dead = true; break; }
+    }
+  }
+  if (dead) {                                               // (g, L) of the element = smoothed (ms, Vs) of frame (c+1) L - done
+    T* o = binit + ((g * nc + c) * SG) * kLanes + lane;
+#pragma unroll
+    for (int i = 0; i < N; ++i) o[i * kLanes] = acc[N * N + NS + i];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) o[(N + i) * kLanes] = acc[N * N + i];
+  }
+  if (lane == 0) {
+    bcut[g * nc + c] = dead ? done : L;
+    if (!dead) atomicOr(gate, 1);
+  }
 }
 
 }  // namespace eksb

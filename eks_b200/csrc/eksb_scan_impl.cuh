@@ -18,33 +18,44 @@ inline size_t scan_workspace_elems(long B, long Tn, int n, long L) {
   return (size_t)num_tiles(B) * nc * per * kLanes;
 }
 
-inline long scan_auto_chunk(long B, long Tn, int n, int elem_size) {
-  // warps = tiles * chunks.  The summary kernels keep 12 (f64) / 16 (f32) warps resident per SM (register-bound,
-  // n <= 3) and stage their frames through per-lane cp.async rings, so bytes in flight do not hinge on occupancy.
-  // Two opposing effects set the chunk length: every chunk pays K warm-up frames (150-800 on the synthetic data)
-  // before its summary has forgotten the boundary state (eksb_math.cuh scan_fwd_chunk), which favours few long
-  // chunks; more warps per SM hide more of the thread-per-track latency.  Measured (tools/route_sweep.py, f64,
-  // 100 000 frames, 8 vs 12 warps per SM): 32 tiles 6.68 / 7.61 ms, 64 tiles 13.03 / 12.83, 96 tiles 20.2 / 18.3,
-  // 128 tiles 26.8 / 24.0, 192 tiles 38.1 / 35.0, 256 tiles 52.2 / 45.8; 64 tracks x 10 M frames 34.8 / 35.1.
-  // Hence 12 warps per SM when the chunks stay >= 3 500 frames, else 8.
-  (void)n; (void)elem_size;
+inline bool scan_v2_enabled() {
+  const char* e = getenv("EKSB_SCAN_V2");                  // A/B switch: 0 = the thread-per-track summary / fold / re-run scan only
+  return !(e && e[0] == '0');
+}
+
+// Chunk length.  Primary route (time-split pipelined scan): as many chunks per tile as give the pipelined kernels a full
+// GPU of virtual tiles -- 148 SMs x the tiles one SM's shared memory holds (4 for p = 4, 3 for p = 8) -- in ONE wave, but
+// chunks of at least 2048 frames so that the K warm-up frames per chunk (150-800) stay a small fraction.
+// EKSB_SCAN_V2=0 (summary / fold / re-run kernels only): warps = tiles * chunks, 12 resident warps per SM when the
+// chunks stay >= 3 500 frames, else 8 (measured, tools/route_sweep.py, f64, 100 000 frames, 8 vs 12 warps per SM:
+// 32 tiles 6.68 / 7.61 ms, 64 tiles 13.03 / 12.83, 128 tiles 26.8 / 24.0, 256 tiles 52.2 / 45.8).
+inline long scan_auto_chunk(long B, long Tn, int n, int elem_size, int p = 4) {
   const long tiles = num_tiles(B);
-  auto len = [&](long per_sm) {
-    const long want_chunks = (148L * per_sm + tiles - 1) / tiles;
+  auto len = [&](long want_chunks) {
+    if (want_chunks < 1) want_chunks = 1;
     long L = (Tn + want_chunks - 1) / want_chunks;
     return L < 64 ? 64L : L;
   };
   const long forced = scan_env_long("EKSB_SCAN_WARPS_PER_SM", 0);
-  if (forced > 0) return len(forced);
-  const long L12 = len(12);
-  return L12 >= 3500 ? L12 : len(8);
+  if (forced > 0) return len((148L * forced + tiles - 1) / tiles);
+  if (scan_v2_enabled()) {
+    long target = (long)pipe_vt_target_tiles(n, p, elem_size);
+    if (target <= 0) target = 148L * 4;
+    long nc = target / tiles;
+    const long nc_max = Tn / 2048;
+    if (nc > nc_max) nc = nc_max;
+    return len(nc);
+  }
+  const long L12 = len((148L * 12 + tiles - 1) / tiles);
+  return L12 >= 3500 ? L12 : len((148L * 8 + tiles - 1) / tiles);
 }
 
 // Workspace layout shared by the forward and the backward half (they may be launched by separate calls).
 template <typename T, int N> struct ScanWs {
   T *fsum, *bsum, *finit, *binit;
   long *fcut, *bcut;
-  int* alive;   // [0] forward, [1] backward: "the fold must run"
+  int* alive;   // [0] forward, [1] backward: "the fold must run"; [2] forward, [3] backward: "some chunk never forgot its
+                // start: the fallback kernels run instead of the virtual-tile kernels" (time-split scan)
   ScanWs(T* ws, long tiles, long nc) {
     constexpr int SG = Dim<N>::SIGMA;
     fsum = ws;
@@ -65,19 +76,33 @@ static int scan_run_fwd_off(const T* obs, const T* yoff, const T* m0, const T* S
                             long B, long Tn, long L, int first, T* ws, T* filt, int* status, cudaStream_t st) {
   const long tiles = num_tiles(B), nc = (Tn + L - 1) / L;
   ScanWs<T, N> w(ws, tiles, nc);
-  if (nc > 1 && cudaMemsetAsync(w.alive, 0, sizeof(int), st) != cudaSuccess) return check_launch("scan flags");
   const int early = scan_env_long("EKSB_SCAN_NO_EARLY", 0) ? 0 : 1;                 // A/B switch: old 2-read behaviour
   const int thr = kScanWarps * kLanes;
   const size_t smem_f = kScanWarps * ring_bytes_per_warp<T, 2 * P>();               // per-lane frame rings, one per warp
   cudaFuncSetAttribute(scan_fwd_summary_kernel<T, N, P, AM, OFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f);
   if (nc == 1) {
-    scan_fwd_rerun_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 0, 1, first, yoff, w.finit, nullptr, filt, status);
-  } else {
-    // chunk 0 (sequential from the prior) rides in the same launch as the summaries of chunks >= 1
-    scan_fwd_summary_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * nc), thr, smem_f, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, early, first, yoff, w.fsum, w.fcut, w.alive, filt, status);
-    scan_fwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(filt, w.fsum, B, Tn, L, nc, w.alive, w.finit, status);
-    scan_fwd_rerun_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 1, nc, first, yoff, w.finit, w.fcut, filt, status);
+    scan_fwd_rerun_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 0, 1, first, yoff, w.finit, nullptr, filt, status, nullptr);
+    return check_launch("scan forward kernels");
   }
+  if (cudaMemsetAsync(w.alive, 0, sizeof(int), st) != cudaSuccess || cudaMemsetAsync(w.alive + 2, 0, sizeof(int), st) != cudaSuccess)
+    return check_launch("scan flags");
+  const int* gate = nullptr;
+  if (scan_v2_enabled()) {
+    // time-split pipelined scan: K warm-up frames per chunk, then every (tile, chunk) is a tile of the TMA-fed kernel
+    gate = w.alive + 2;
+    scan_fwd_warm_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, w.fcut, w.alive + 2, filt);
+    int rc = check_launch("scan forward warm-up");
+    if (rc != EKSB_OK) return rc;
+    VTiles vt;
+    vt.L = L; vt.nc = nc; vt.cut = w.fcut; vt.gate = gate;
+    rc = kf_forward_pipe_vt<T>(obs, m0, S0, C, A, Q, mask, B, Tn, N, P, AM ? EKSB_A_DENSE : EKSB_A_DIAG, first, filt, status, yoff, vt, st);
+    if (rc != EKSB_OK) return rc;
+  }
+  // summary / fold / re-run: the whole pass when gate == nullptr, else only if some chunk never forgot its start
+  // (chunk 0, sequential from the prior, rides in the same launch as the summaries of chunks >= 1)
+  scan_fwd_summary_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * nc), thr, smem_f, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, early, first, yoff, w.fsum, w.fcut, w.alive, filt, status, gate);
+  scan_fwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(filt, w.fsum, B, Tn, L, nc, w.alive, w.finit, status, gate);
+  scan_fwd_rerun_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, m0, S0, C, A, Q, mask, B, Tn, L, nc, 1, nc, first, yoff, w.finit, w.fcut, filt, status, gate);
   return check_launch("scan forward kernels");
 }
 template <typename T, int N, int P, int AM>
@@ -94,19 +119,31 @@ static int scan_run_bwd(const T* filt, const T* C, const T* A, const T* Q, int m
   constexpr int SG = Dim<N>::SIGMA;
   const long tiles = num_tiles(B), nc = (Tn + L - 1) / L;
   ScanWs<T, N> w(ws, tiles, nc);
-  if (nc > 1 && cudaMemsetAsync(w.alive + 1, 0, sizeof(int), st) != cudaSuccess) return check_launch("scan flags");
   const int early = scan_env_long("EKSB_SCAN_NO_EARLY", 0) ? 0 : 1;
   const int thr = kScanWarps * kLanes;
   const size_t smem_b = kScanWarps * ring_bytes_per_warp<T, SG>();
   cudaFuncSetAttribute(scan_bwd_summary_kernel<T, N, P, AM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b);
   if (nc == 1) {
-    scan_bwd_rerun_kernel<T, N, P, AM><<<scan_blocks(tiles), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, nc - 1, nc, w.binit, nullptr, smth, ym, status);
-  } else {
-    // the terminal chunk (sequential from the end of the track) rides in the summary launch
-    scan_bwd_summary_kernel<T, N, P, AM><<<scan_blocks(tiles * nc), thr, smem_b, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, early, w.bsum, w.bcut, w.alive + 1, smth, ym, status);
-    scan_bwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(smth, w.bsum, B, Tn, L, nc, w.alive + 1, w.binit);
-    scan_bwd_rerun_kernel<T, N, P, AM><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, 0, nc - 1, w.binit, w.bcut, smth, ym, status);
+    scan_bwd_rerun_kernel<T, N, P, AM><<<scan_blocks(tiles), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, nc - 1, nc, w.binit, nullptr, smth, ym, status, nullptr);
+    return check_launch("scan backward kernels");
   }
+  if (cudaMemsetAsync(w.alive + 1, 0, sizeof(int), st) != cudaSuccess || cudaMemsetAsync(w.alive + 3, 0, sizeof(int), st) != cudaSuccess)
+    return check_launch("scan flags");
+  const int* gate = nullptr;
+  if (scan_v2_enabled()) {
+    gate = w.alive + 3;
+    scan_bwd_warm_kernel<T, N, P, AM><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, w.bcut, w.alive + 3, w.binit);
+    int rc = check_launch("scan backward warm-up");
+    if (rc != EKSB_OK) return rc;
+    VTiles vt;
+    vt.L = L; vt.nc = nc; vt.cut = w.bcut; vt.init = w.binit; vt.gate = gate;
+    rc = rts_backward_pipe_vt<T>(filt, C, A, Q, mask, B, Tn, N, P, AM ? EKSB_A_DENSE : EKSB_A_DIAG, smth, ym, status, vt, st);
+    if (rc != EKSB_OK) return rc;
+  }
+  // (the terminal chunk, sequential from the end of the track, rides in the summary launch)
+  scan_bwd_summary_kernel<T, N, P, AM><<<scan_blocks(tiles * nc), thr, smem_b, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, early, w.bsum, w.bcut, w.alive + 1, smth, ym, status, gate);
+  scan_bwd_fold_kernel<T, N><<<(unsigned)tiles, kLanes, 0, st>>>(smth, w.bsum, B, Tn, L, nc, w.alive + 1, w.binit, gate);
+  scan_bwd_rerun_kernel<T, N, P, AM><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, 0, nc - 1, w.binit, w.bcut, smth, ym, status, gate);
   return check_launch("scan backward kernels");
 }
 
@@ -171,8 +208,13 @@ inline bool route_scan(long B, long Tn, int n, int p, int elem_size) {
   if (e && e[0] == 's' && e[1] == 'c') return true;
   if (Tn < 4096) return false;
   const long tiles = num_tiles(B);
+  if (scan_v2_enabled()) {
+    // worth it when the timeline splits at least in two: fewer real tiles than half of what fills the GPU
+    const long L = scan_auto_chunk(B, Tn, n, elem_size, p);
+    return (Tn + L - 1) / L >= 2;
+  }
   if (tiles <= 96) return true;
-  return tiles <= 208 && scan_auto_chunk(B, Tn, n, elem_size) >= 2048;
+  return tiles <= 208 && scan_auto_chunk(B, Tn, n, elem_size, p) >= 2048;
 }
 
 // Sequential entry points of the other translation units (same shared library).
@@ -202,7 +244,7 @@ template <> struct SeqApi<float> {
 
 inline size_t route_workspace_bytes(long B, long Tn, int n, int p, int elem_size) {
   if (!route_scan(B, Tn, n, p, elem_size)) return 0;
-  return scan_workspace_elems(B, Tn, n, scan_auto_chunk(B, Tn, n, elem_size)) * (size_t)elem_size;
+  return scan_workspace_elems(B, Tn, n, scan_auto_chunk(B, Tn, n, elem_size, p)) * (size_t)elem_size;
 }
 
 template <typename T>
@@ -213,7 +255,7 @@ static int forward_ws_api(const T* obs, const T* yoff, const T* m0, const T* S0,
   if (need == 0 || ws_bytes < need || !obs || !m0 || !S0 || !C || !A || !Q ||
       (first != kPriorUpdate && first != kPriorOnly) || (a_mode != EKSB_A_DIAG && a_mode != EKSB_A_DENSE))
     return SeqApi<T>::fwd(obs, yoff, m0, S0, C, A, Q, mask, B, Tn, n, p, a_mode, first, filt, nll, status, stream);
-  return scan_dispatch<T>(1, obs, yoff, m0, S0, C, A, Q, mask, B, Tn, n, p, a_mode, scan_auto_chunk(B, Tn, n, (int)sizeof(T)),
+  return scan_dispatch<T>(1, obs, yoff, m0, S0, C, A, Q, mask, B, Tn, n, p, a_mode, scan_auto_chunk(B, Tn, n, (int)sizeof(T), p),
                           first, ws, filt, (T*)nullptr, (T*)nullptr, status, (cudaStream_t)stream);
 }
 
@@ -224,7 +266,7 @@ static int backward_ws_api(const T* filt, const T* C, const T* A, const T* Q, in
   if (need == 0 || ws_bytes < need || !filt || !smth || !C || !A || !Q || (a_mode != EKSB_A_DIAG && a_mode != EKSB_A_DENSE))
     return SeqApi<T>::bwd(filt, C, A, Q, mask, B, Tn, n, p, a_mode, smth, ym, yv, cv, status, stream);
   return scan_dispatch<T>(2, (const T*)nullptr, (const T*)nullptr, (const T*)nullptr, (const T*)nullptr, C, A, Q, mask, B, Tn, n, p,
-                          a_mode, scan_auto_chunk(B, Tn, n, (int)sizeof(T)), kPriorUpdate, ws, const_cast<T*>(filt), smth, ym,
+                          a_mode, scan_auto_chunk(B, Tn, n, (int)sizeof(T), p), kPriorUpdate, ws, const_cast<T*>(filt), smth, ym,
                           status, (cudaStream_t)stream);
 }
 

@@ -28,7 +28,7 @@ def test_non_compute_entry_points():
         assert lib.eksb_supported_dims(n, p) == 1
     # (n,p) outside that list, e.g. (5,4) or five cameras' (3,10), are served by the runtime-dimension kernels
     # eksb_kf_forward_generic / eksb_rts_backward_generic (tests/test_gpu_round2.py::test_shapes_without_a_template_instantiation)
-    assert lib.eksb_route_workspace_bytes(2048, 100000, 3, 4, 8) > 0 and lib.eksb_route_workspace_bytes(8192, 100000, 3, 4, 8) == 0
+    assert lib.eksb_route_workspace_bytes(2048, 100000, 3, 4, 8) > 0 and lib.eksb_route_workspace_bytes(16384, 100000, 3, 4, 8) == 0
     # argument validation happens before any CUDA call
     assert lib.eksb_ensemble_f64(None, 5, 10, 4, 0, None, None, None) == -2
     assert b"bad argument" in lib.eksb_last_error_string()

@@ -21,8 +21,8 @@ def make_obs(dt, tiles, T, p, d):
 def main():
     bits = int(os.environ.get("BITS", "64"))
     T = int(os.environ.get("FRAMES", "100000"))
-    tiles_list = [int(x) for x in os.environ.get("TILES", "32,64,96,128,148,171,192,256").split(",")]
-    wps = [int(x) for x in os.environ.get("WPS", "8,12").split(",")]
+    tiles_list = [int(x) for x in os.environ.get("TILES", "16,64,128,192,256,296").split(",")]
+    modes = os.environ.get("MODES", "v2,old12").split(",")      # v2 = time-split pipelined scan; oldN = summary/fold/re-run, N warps per SM
     dt = torch.float64 if bits == 64 else torch.float32
     d = torch.device("cuda", 0)
     p, n = 4, 3
@@ -40,6 +40,7 @@ def main():
         prm = dev.TrackParams.from_numpy(np.zeros(n), np.eye(n), C[:B], np.eye(n), 1e-3 * np.eye(n), dtype=dt, device=d)
         tf = B * T
         f = b = 0.0
+        os.environ["EKSB_ROUTE"] = "seq"
         for r in range(reps + 1):
             ev[0].record()
             dev.kf_forward(obs, prm, B, T, filt=filt)
@@ -49,10 +50,16 @@ def main():
             torch.cuda.synchronize()
             if r:
                 f += ev[0].elapsed_time(ev[1]) / reps; b += ev[1].elapsed_time(ev[2]) / reps
-        print(f"f{bits} tiles={tiles:4d} T={T} pipe  fwd {f:7.2f} bwd {b:7.2f} total {f+b:7.2f} ms -> {tf/(f+b)*1e-6:6.2f} G tf/s "
+        os.environ.pop("EKSB_ROUTE", None)
+        print(f"f{bits} tiles={tiles:4d} T={T} pipe   fwd {f:7.2f} bwd {b:7.2f} total {f+b:7.2f} ms -> {tf/(f+b)*1e-6:6.2f} G tf/s "
               f"({tf*(3*p+3*dev.sigma(n))*es/(f+b)*1e-6:6.0f} GB/s)", flush=True)
-        for w in wps:
-            os.environ["EKSB_SCAN_WARPS_PER_SM"] = str(w)
+        for mode in modes:
+            os.environ.pop("EKSB_SCAN_WARPS_PER_SM", None)
+            if mode == "v2":
+                os.environ["EKSB_SCAN_V2"] = "1"
+            else:
+                os.environ["EKSB_SCAN_V2"] = "0"
+                os.environ["EKSB_SCAN_WARPS_PER_SM"] = mode[3:]
             ws_bytes = dev.lib().eksb_scan_workspace_bytes(B, T, n, 0, es)
             ws = torch.empty(ws_bytes // es + 1, dtype=dt, device=d)
             f = tot = 0.0
@@ -65,9 +72,11 @@ def main():
                 torch.cuda.synchronize()
                 if r:
                     f += ev[0].elapsed_time(ev[1]) / reps; tot += ev[1].elapsed_time(ev[2]) / reps
-            print(f"f{bits} tiles={tiles:4d} T={T} scan{w:<2d} fwd {f:7.2f} bwd {tot-f:7.2f} total {tot:7.2f} ms -> {tf/tot*1e-6:6.2f} G tf/s "
+            assert int(out["status"].sum()) == 0
+            print(f"f{bits} tiles={tiles:4d} T={T} {mode:6s} fwd {f:7.2f} bwd {tot-f:7.2f} total {tot:7.2f} ms -> {tf/tot*1e-6:6.2f} G tf/s "
                   f"({tf*(3*p+3*dev.sigma(n))*es/tot*1e-6:6.0f} GB/s) chunk={out['chunk']}", flush=True)
             del ws
+        os.environ.pop("EKSB_SCAN_V2", None); os.environ.pop("EKSB_SCAN_WARPS_PER_SM", None)
     print("done")
 
 
