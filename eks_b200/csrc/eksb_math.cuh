@@ -1371,9 +1371,11 @@ EKSB_HD void bwd_summary_step(const T* rec, T* acc) {
 // RTS gains).  HBM traffic drops from (2 reads of the input + 1 write) to (1 + K/L reads + 1 write).
 // ---------------------------------------------------------------------------
 template <typename T> struct ScanCut;
-// state error after the cut <= ScanCut * |x_start|: below one ulp of the state for |x_start| up to ~1e6 (f64) / ~1e4 (f32)
-template <> struct ScanCut<double> { static constexpr double value = 1e-22; };
-template <> struct ScanCut<float> { static constexpr float value = 1e-11f; };
+// State error after the cut <= ScanCut * |x_start| (x_start = the unknown state before the chunk, of the same magnitude
+// as the states that follow it): a tenth of an ulp of the state in either type.  Round 1 used 1e-22 / 1e-11; every
+// decade costs ~20 warm-up frames per chunk on the shapes of BASELINE.json (K = 480 -> 370 in f64).
+template <> struct ScanCut<double> { static constexpr double value = 1e-17; };
+template <> struct ScanCut<float> { static constexpr float value = 1e-8f; };
 
 #if defined(__CUDA_ARCH__)
 #define EKSB_WARP_ALL(pred) __all_sync(0xffffffffu, (pred))

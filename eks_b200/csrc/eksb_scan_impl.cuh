@@ -195,11 +195,8 @@ static int scan_api(const T* obs, const T* m0, const T* S0, const T* C, const T*
 // eksb_rts_backward plus a caller-owned workspace.  The sequential warp-specialised kernels keep one chain warp per
 // track tile, so a batch with fewer tiles than the GPU has SMs (or an awkward count between one and two tiles per
 // SM) runs at one warp's pace no matter how few bytes it moves; such batches go through the two halves of the
-// parallel-in-time scan instead.  Measured, f64, 100 000 frames, sequential vs scan (tools/route_sweep.py):
-//   32 tiles 22.8 / 6.7 ms, 64 tiles 22.8 / 12.8, 96 tiles 23.3 / 18.3, 128 tiles 25.4 / 24.0, 171 tiles 36.2 / 31.8,
-//   192 tiles 38.4 / 35.0, 256 tiles 43.6 / 45.8 (f32: 64 tiles 16.7 / 7.1, 128 tiles 16.7 / 13.7, 256 tiles 24.3 / 27.0).
-// Policy: T >= 4096 and a scan instantiation; up to 96 tiles always, up to 208 tiles when the scan's chunks are
-// at least 2048 frames long.  EKSB_ROUTE=seq|scan forces a side (read per call).
+// parallel-in-time scan instead (policy and the measurements behind it: route_scan below).
+// EKSB_ROUTE=seq|scan forces a side (read per call).
 // ------------------------------------------------------------------------------------------------------------
 inline bool route_scan(long B, long Tn, int n, int p, int elem_size) {
   if (B <= 0 || Tn <= 0 || !scan_dims_ok(n, p)) return false;
@@ -209,7 +206,13 @@ inline bool route_scan(long B, long Tn, int n, int p, int elem_size) {
   if (Tn < 4096) return false;
   const long tiles = num_tiles(B);
   if (scan_v2_enabled()) {
-    // worth it when the timeline splits at least in two: fewer real tiles than half of what fills the GPU
+    // Worth it while the real tiles leave the pipelined kernels short of ~2 tiles per SM.  Measured (tools/route_sweep.py,
+    // f64, 100 000 frames, sequential vs time-split): 16 tiles 25.3 / 4.2 ms, 64 tiles 25.2 / 12.2, 128 tiles 26.7 / 22.7,
+    // 192 tiles 39.2 / 33.1, 256 tiles 44.0 / 44.2, 296 tiles 48.7 / 49.9 (f32: 64 tiles 17.5 / 6.1, 128 tiles 17.5 / 11.1,
+    // 256 tiles 24.8 / 24.1).  Hence: at least two chunks per tile and fewer than 0.43 x the tiles that fill the GPU.
+    long target = (long)pipe_vt_target_tiles(n, p, elem_size);
+    if (target <= 0) target = 148L * 4;
+    if (tiles * 100 > target * 43) return false;
     const long L = scan_auto_chunk(B, Tn, n, elem_size, p);
     return (Tn + L - 1) / L >= 2;
   }

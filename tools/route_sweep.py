@@ -22,7 +22,7 @@ def main():
     bits = int(os.environ.get("BITS", "64"))
     T = int(os.environ.get("FRAMES", "100000"))
     tiles_list = [int(x) for x in os.environ.get("TILES", "16,64,128,192,256,296").split(",")]
-    modes = os.environ.get("MODES", "v2,old12").split(",")      # v2 = time-split pipelined scan; oldN = summary/fold/re-run, N warps per SM
+    modes = [m for m in os.environ.get("MODES", "v2,old12").split(",") if m]      # v2 = time-split pipelined scan; oldN = summary/fold/re-run, N warps per SM
     dt = torch.float64 if bits == 64 else torch.float32
     d = torch.device("cuda", 0)
     p, n = 4, 3
