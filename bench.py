@@ -753,6 +753,7 @@ def gpu_main(a):
                "pcie": {"h2d_gbs_measured": pcie["h2d"], "d2h_gbs_measured": pcie["d2h"],
                         "h2d_gbs_in_run": h2d / step_s / 1e9, "d2h_gbs_in_run": d2h / step_s / 1e9,
                         "how": "1 GiB pinned <-> device copies, one direction at a time, this rank"},
+               "host_dma_gbs_all_gpus": (h2d + d2h) * world / step_s / 1e9,     # what the host moved per second for all ranks
                "pcie_frac": max(h2d / step_s / 1e9 / pcie["h2d"], d2h / step_s / 1e9 / pcie["d2h"]),
                "binding_direction": "h2d" if h2d / pcie["h2d"] >= d2h / pcie["d2h"] else "d2h"}
         launches += cnt["launches"]

@@ -209,10 +209,11 @@ inline bool route_scan(long B, long Tn, int n, int p, int elem_size) {
     // Worth it while the real tiles leave the pipelined kernels short of ~2 tiles per SM.  Measured (tools/route_sweep.py,
     // f64, 100 000 frames, sequential vs time-split): 16 tiles 25.3 / 4.2 ms, 64 tiles 25.2 / 12.2, 128 tiles 26.7 / 22.7,
     // 192 tiles 39.2 / 33.1, 256 tiles 44.0 / 44.2, 296 tiles 48.7 / 49.9 (f32: 64 tiles 17.5 / 6.1, 128 tiles 17.5 / 11.1,
-    // 256 tiles 24.8 / 24.1).  Hence: at least two chunks per tile and fewer than 0.43 x the tiles that fill the GPU.
+    // 256 tiles 24.8 / 24.1); in the bench's sustained, power-capped region 2 x 256 tiles take 89.7 / 88.0 ms.
+    // Hence: at least two chunks per tile and at most 0.45 x the tiles that fill the GPU (256 of 592).
     long target = (long)pipe_vt_target_tiles(n, p, elem_size);
     if (target <= 0) target = 148L * 4;
-    if (tiles * 100 > target * 43) return false;
+    if (tiles * 100 > target * 45) return false;
     const long L = scan_auto_chunk(B, Tn, n, elem_size, p);
     return (Tn + L - 1) / L >= 2;
   }
