@@ -277,15 +277,14 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def committed_traffic(dtype):
-    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture."""
+def committed_traffic(dtype, launch_tracks):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/traffic.json,
+    tools/collect_profiles_r2.py), if that capture is of launches of the same size."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        return t[dtype]["dram_bytes"]
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[dtype]
+        return t["dram_bytes"] if t.get("launch_tracks") == launch_tracks else None
     except Exception:
         return None
-
-
 
 
 def _es(dt_name):
@@ -556,9 +555,7 @@ def gpu_main(a):
              else ("mixed" if any_routed else "sequential warp-specialised kernels"))
     kname = {"kf_forward": ("eksb_kf_forward_ws -> " + ("scan_fwd_warm_kernel + kf_forward_pipe_kernel over virtual tiles" if all_routed else "kf_forward_pipe_kernel")),
              "rts_backward": ("eksb_rts_backward_ws -> " + ("scan_bwd_warm_kernel + rts_backward_pipe_kernel over virtual tiles" if all_routed else "rts_backward_pipe_kernel"))}
-    traffic = None if any_routed else committed_traffic(a.dtype)
-    if traffic is not None and Gmax != 8192:
-        traffic = None                                              # the committed capture is of an 8192-track launch
+    traffic = committed_traffic(a.dtype, Gmax) if (dom == "rts_backward" and T == 100_000) else None
     step_b = B * T * (3 * P_OBS + 3 * SIGMA) * es
     roof = {"bound": "hbm", "kernel": kname[dom], "achieved": kern[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
             "frac": kern[dom]["frac"], "traffic": traffic, "peak_source": peak_src,
