@@ -1,11 +1,15 @@
 """Randomised parity sweep (developer probe): many small (B, T, n, p, dtype, A-mode) cases through the C ABI,
-pipelined kernels vs the numpy oracle; extreme ensemble variances (1e-4 .. 1e3), ragged B and T, T in {1,2,3,..}."""
+pipelined kernels vs the numpy oracle; extreme ensemble variances (1e-4 .. 1e3), ragged B and T, T in {1,2,3,..}.
+Metric and bars are the tests' own (tests/conftest.py rel: per component, scaled by its largest magnitude over time;
+1e-3 in fp32 = north_star's bar, 1e-8 in fp64)."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import numpy as np, torch
 from eks_b200 import device as dev
 from oracle import restated as o
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from conftest import rel
 
 rng = np.random.default_rng(int(os.environ.get("SEED", "0")))
 d = torch.device("cuda", 0)
@@ -15,7 +19,7 @@ for it in range(int(os.environ.get("ITERS", "150"))):
     n, p = [(3, 4), (3, 6), (3, 8), (2, 4), (4, 6), (6, 8)][rng.integers(6)]
     B = int(rng.choice([1, 2, 31, 32, 33, 64, 70, 150]))
     T = int(rng.choice([1, 2, 3, 4, 5, 6, 7, 8, 9, 11, 12, 13, 17, 24, 25, 48, 49, 97, 200, 333]))
-    dt, tol = (torch.float64, 1e-8) if rng.random() < 0.6 else (torch.float32, 5e-3)
+    dt, tol = (torch.float64, 1e-8) if rng.random() < 0.5 else (torch.float32, 1e-3)
     a_diag = rng.random() < 0.7
     C = np.stack([np.linalg.qr(rng.normal(size=(p, n)))[0] for _ in range(B)])
     A = np.diag(rng.uniform(0.9, 1.0, n)) if a_diag else np.eye(n) * 0.95 + 0.02 * rng.normal(size=(n, n))
@@ -38,10 +42,8 @@ for it in range(int(os.environ.get("ITERS", "150"))):
     for b in {0, B - 1, B // 2}:
         mf, Vf, S = o.filtering_pass(yq[b], m0, S0, C[b], np.eye(p), A, Q, evq[b])
         ms, Vs, _ = o.smooth_backward(yq[b], mf, Vf, S, A, Q, C[b])
-        sc = max(1.0, np.abs(ms).max())
-        errs = dict(mf=np.abs(mfV[b][:, :n] - mf).max() / sc, Vf=np.abs(mfV[b][:, n:] - Vf[:, iu[0], iu[1]]).max() / max(1e-300, np.abs(Vf).max()),
-                    ms=np.abs(sm[b][:, :n] - ms).max() / sc, Vs=np.abs(sm[b][:, n:] - Vs[:, iu[0], iu[1]]).max() / max(1e-300, np.abs(Vs).max()),
-                    ym=np.abs(ym[b] - ms @ C[b].T).max() / sc)
+        errs = dict(mf=rel(mfV[b][:, :n], mf), Vf=rel(mfV[b][:, n:], Vf[:, iu[0], iu[1]]), ms=rel(sm[b][:, :n], ms),
+                    Vs=rel(sm[b][:, n:], Vs[:, iu[0], iu[1]]), ym=rel(ym[b], ms @ C[b].T))
         for k, e in errs.items():
             key = (str(dt)[6:], k)
             worst[key] = max(worst.get(key, 0.0), e)
