@@ -41,6 +41,11 @@ int kf_forward_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T*
 template <typename T>
 int rts_backward_pipe(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn, int n, int p,
                       int a_mode, T* smth, T* ym, T* yv, int* status, cudaStream_t st);
+// NLL only (no state records), n_scale candidates of q_scale * Q per launch, in the warp-specialised form
+// (eksb_nll_pipe.cuh); EKSB_EDIM for shapes it is not instantiated for (dense A is the caller's check).
+template <typename T>
+int kf_nll_pipe(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
+                int n, int p, int first, const T* q_scale, int n_scale, double* nll, int* status, const T* yoff, cudaStream_t st);
 // The same kernels over virtual tiles (vt.nc > 1); diagonal-R Kalman filter / RTS smoother only.
 template <typename T>
 int kf_forward_pipe_vt(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask, long B,

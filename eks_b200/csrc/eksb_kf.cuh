@@ -91,6 +91,11 @@ rts_backward_kernel(const T* filt, const T* __restrict__ C, const T* __restrict_
   if (b < B && status) set_status(status + b, ok, false);
 }
 
+inline bool use_nll_pipe() {
+  const char* e = getenv("EKSB_NLL_PIPE");                 // A/B switch, read per call: 0 = plain thread-per-track NLL kernel
+  return !(e && e[0] == '0');
+}
+
 template <typename T, int N, int P>
 static int launch_forward(const T* obs, const T* m0, const T* S0, const T* C, const T* A, const T* Q, int shared_mask,
                           long B, long Tn, int a_mode, int first, const T* q_scale, int n_scale, T* filt, double* nll,
@@ -106,6 +111,10 @@ static int launch_forward(const T* obs, const T* m0, const T* S0, const T* C, co
                               shared_mask, Bs, Tn, N, P, a_mode, first, filt + g0 * Tn * Dim<N>::SIGMA * kLanes,
                               status ? status + b0 : nullptr, yoff ? yoff + b0 * P : nullptr, st);
     }
+    if (rc != EKSB_EDIM) return rc;
+  }
+  if (nll && !filt && a_mode == EKSB_A_DIAG && use_pipe(B) && use_nll_pipe()) {   // NLL / grid search: pipelined form
+    const int rc = kf_nll_pipe<T>(obs, m0, S0, C, A, Q, shared_mask, B, Tn, N, P, first, q_scale, n_scale, nll, status, yoff, st);
     if (rc != EKSB_EDIM) return rc;
   }
   dim3 grid((unsigned)num_tiles(B), (unsigned)(q_scale ? n_scale : 1));

@@ -829,6 +829,103 @@ EKSB_HD void fwd_chain_scaled(const Params<T, N, P, 0>& prm, const T* rec, bool 
   fwd_mean_scaled<T, N, P>(prm, rec, do_predict, Nm, r, m, Vout);
 }
 
+// ---------------------------------------------------------------------------
+// NLL in the producer / consumer split (kf_nll_pipe_kernel, eksb_pipe.cuh; diagonal A, N <= 3 -- the scaled chain).
+// Per frame  log det Sig + nu^T Sig^-1 nu,  Sig = R + C S C^T (== update_state<NLL>), from
+//   log det Sig = log prod_j r_j + log det(Id + Lam S),    det(Id + Lam S) = det(Lt) / det(S)^(N-1) = 1 / (r det(S)^(N-2))
+//   nu^T Sig^-1 nu = quad - u^T V u,   quad = sum_j w_j nu_j^2 = yy - mp.(iv + u),   u = iv - Lam mp,   u^T V u = r u.(Nm u)
+// with Lam, iv from the info record, yy = sum_j w_j y_j^2 and ldr = log prod_j r_j two more values of it: nothing in the
+// record depends on Q, so ONE helper stream feeds the chains of every smoothing-parameter candidate.
+// ---------------------------------------------------------------------------
+template <int N> struct RecNll { static constexpr int FWD = Rec<N>::FWD + 2; };   // Lam | iv | yy | ldr
+
+template <typename T, int N, int P>
+EKSB_HD void fwd_prep_outer_nll(const T C[P][N], const T CC[P][Dim<N>::NS], const T* y, const T* r, T* rec) {
+  constexpr int NS = Dim<N>::NS;
+  EKSB_UNROLL
+  for (int k = 0; k < NS + N; ++k) rec[k] = T(0);
+  T yy = T(0), prod = T(1);
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) {
+    const T w = rcp_chain(r[j]);
+    const T wy = w * y[j];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) rec[NS + i] += C[j][i] * wy;
+    EKSB_UNROLL
+    for (int k = 0; k < NS; ++k) rec[k] += w * CC[j][k];
+    yy += wy * y[j];
+    prod *= r[j];
+  }
+  rec[NS + N] = yy;
+  rec[NS + N + 1] = (T)log((double)prod);
+}
+
+// the same record without the precomputed outer products (observation dims whose C_j C_j^T do not fit in registers)
+template <typename T, int N, int P>
+EKSB_HD void fwd_prep_nll(const T C[P][N], const T* y, const T* r, T* rec) {
+  constexpr int NS = Dim<N>::NS;
+  EKSB_UNROLL
+  for (int k = 0; k < NS + N; ++k) rec[k] = T(0);
+  T yy = T(0), prod = T(1);
+  EKSB_UNROLL
+  for (int j = 0; j < P; ++j) {
+    const T w = rcp_chain(r[j]);
+    const T wy = w * y[j];
+    T cw[N];
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) cw[i] = C[j][i] * w;
+    EKSB_UNROLL
+    for (int i = 0; i < N; ++i) {
+      rec[NS + i] += C[j][i] * wy;
+      EKSB_UNROLL
+      for (int k = i; k < N; ++k) rec[sym_idx<N>(i, k)] += cw[i] * C[j][k];
+    }
+    yy += wy * y[j];
+    prod *= r[j];
+  }
+  rec[NS + N] = yy;
+  rec[NS + N + 1] = (T)log((double)prod);
+}
+
+// One frame of an NLL chain: (m, Nm, r) carried like fwd_chain_scaled (V = Nm r), no normalised covariance formed.
+// xdet receives 1 / det(Id + Lam S) (in (0, 1]; the caller multiplies a few of them before taking a log),
+// returns yy - mp.(iv + u) - r u.(Nm u).
+template <typename T, int N, int P>
+EKSB_HD T fwd_nll_scaled(const Params<T, N, P, 0>& prm, const T* rec, bool do_predict, T* m, T* Nm, T& r, T& xdet, bool& ok) {
+  constexpr int NS = Dim<N>::NS;
+  T S[NS];
+  if (do_predict) {
+    EKSB_UNROLL
+    for (int k = 0; k < NS; ++k) S[k] = (prm.AA[k] * Nm[k]) * r + prm.Q[k];
+  } else {
+    EKSB_UNROLL
+    for (int k = 0; k < NS; ++k) S[k] = Nm[k] * r;
+  }
+  T adjS[NS], detS, Lt[NS], detL;
+  sym_adjugate<T, N>(S, adjS, detS);
+  EKSB_UNROLL
+  for (int k = 0; k < NS; ++k) Lt[k] = detS * rec[k] + adjS[k];
+  sym_adjugate<T, N>(Lt, Nm, detL);
+  ok = ok && !(detS <= T(0)) && !(detL <= T(0)) && !(S[0] <= T(0));
+  r = detS * rcp(detL);
+  xdet = (N == 3) ? r * detS : (N == 2 ? r : r * rcp(detS));
+  T mp[N], u[N], Nu[N];
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) mp[i] = do_predict ? prm.A[i] * m[i] : m[i];
+  sym_matvec<T, N>(rec, mp, u);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) u[i] = rec[NS + i] - u[i];
+  sym_matvec<T, N>(Nm, u, Nu);
+  T e = rec[NS + N], q = T(0);
+  EKSB_UNROLL
+  for (int i = 0; i < N; ++i) {
+    e -= mp[i] * (rec[NS + i] + u[i]);
+    q += u[i] * Nu[i];
+    m[i] = mp[i] + Nu[i] * r;
+  }
+  return e - r * q;
+}
+
 template <typename T, int N, int P, int AM>
 EKSB_HD void bwd_prep(const Params<T, N, P, AM>& prm, const T* m, const T* V, T* rec, bool& ok) {
   constexpr int NS = Dim<N>::NS;

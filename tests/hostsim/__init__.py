@@ -93,6 +93,24 @@ def kf_rts_split(y, ev, m0, S0, C, A, Q, dtype=np.float64, first=1):
     return dict(rc=rc, mf=filt[:, :n], Vf=sym_unpack(filt[:, n:], n), ms=smth[:, :n], Vs=sym_unpack(smth[:, n:], n))
 
 
+def nll_split(y, ev, m0, S0, C, A, Q, dtype=np.float64, first=1):
+    """Host build of the NLL in the prep / chain split (fwd_prep_outer_nll + fwd_nll_scaled); diagonal A, n <= 3.
+    Returns 0.5 * (sum of per-frame terms + T p log 2 pi), like the kernels."""
+    T, p = y.shape
+    n = m0.shape[0]
+    c = lambda a: np.ascontiguousarray(a, dtype=dtype)
+    assert a_mode(A) == 0
+    y, ev, m0, S0, C, A, Q = map(c, (y, ev, m0, S0, C, A, Q))
+    out = ctypes.c_double(0.0)
+    fn = lib().hs_nll_split_f64 if dtype == np.float64 else lib().hs_nll_split_f32
+    P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    rc = fn(ctypes.c_int(n), ctypes.c_int(p), ctypes.c_long(T), P(y), P(ev), P(m0), P(S0), P(C), P(A), P(Q),
+            ctypes.c_int(first), ctypes.byref(out))
+    if rc < 0:
+        raise ValueError(f"unsupported dims n={n} p={p}")
+    return dict(rc=rc, nll=0.5 * (out.value + T * p * np.log(2 * np.pi)))
+
+
 def btd(y, ev, m0, S0, C, A, Q, dtype=np.float64):
     """Host build of the block-tridiagonal solve (fwd_prep + btd_fwd_chain, btd_bwd_prep + bwd_chain)."""
     T, p = y.shape

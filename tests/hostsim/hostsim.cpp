@@ -54,6 +54,54 @@ extern "C" int hs_kf_rts_f32(int n, int p, int am, long Tn, const float* y, cons
   return dispatch<float>(n, p, am, Tn, y, ev, m0, S0, C, A, Q, first, filt, smth, ym, yv, cv, nll);
 }
 
+// ---- NLL in the split form (kf_nll_pipe_kernel): helper record with yy / ldr, scaled chain, one log per 4 frames ----
+template <typename T, int N, int P>
+static int run_nll_split(long Tn, const T* y, const T* ev, const T* m0, const T* S0, const T* C, const T* A, const T* Q,
+                         int first, double* nll_terms) {
+  constexpr int NS = Dim<N>::NS;
+  Params<T, N, P, 0> prm;
+  load_params<T, N, P, 0>(prm, C, A, Q);
+  T m[N], Nm[NS], rr = T(1);
+  for (int i = 0; i < N; ++i) m[i] = m0[i];
+  load_sym<T, N>(Nm, S0);
+  bool ok = true;
+  if (first == kPriorOnly) {
+    T Vi[NS];
+    sym_inv<T, N>(Nm, Vi, ok);
+    for (int i = 0; i < NS; ++i) Nm[i] = Vi[i];
+  }
+  T CC[P][NS];
+  make_outer<T, N, P>(prm.C, CC);
+  double acc = 0.0;
+  T xprod = T(1);
+  for (long t = 0; t < Tn; ++t) {
+    if (t == 0 && first == kPriorOnly) continue;
+    T rec[RecNll<N>::FWD], xdet;
+    fwd_prep_outer_nll<T, N, P>(prm.C, CC, y + t * P, ev + t * P, rec);
+    const T e = fwd_nll_scaled<T, N, P>(prm, rec, !(t == 0 && first == kPriorUpdate), m, Nm, rr, xdet, ok);
+    acc += (double)e + (double)rec[NS + N + 1];
+    xprod *= xdet;
+    if ((t & 3) == 3 || t == Tn - 1) { acc -= log((double)xprod); xprod = T(1); }
+  }
+  *nll_terms = acc;
+  return ok ? 0 : 1;
+}
+
+extern "C" int hs_nll_split_f64(int n, int p, long Tn, const double* y, const double* ev, const double* m0, const double* S0,
+                                const double* C, const double* A, const double* Q, int first, double* nll_terms) {
+#define X(N_, P_) if (n == N_ && p == P_) return run_nll_split<double, N_, P_>(Tn, y, ev, m0, S0, C, A, Q, first, nll_terms);
+  X(2, 4) X(3, 4) X(3, 6) X(3, 8)
+#undef X
+  return -1;
+}
+extern "C" int hs_nll_split_f32(int n, int p, long Tn, const float* y, const float* ev, const float* m0, const float* S0,
+                                const float* C, const float* A, const float* Q, int first, double* nll_terms) {
+#define X(N_, P_) if (n == N_ && p == P_) return run_nll_split<float, N_, P_>(Tn, y, ev, m0, S0, C, A, Q, first, nll_terms);
+  X(2, 4) X(3, 4) X(3, 6) X(3, 8)
+#undef X
+  return -1;
+}
+
 // ---- producer/consumer split form (what the warp-specialised kernels run) ----
 template <typename T, int N, int P, int AM>
 static int run_split(long Tn, const T* y, const T* ev, const T* m0, const T* S0, const T* C, const T* A, const T* Q,

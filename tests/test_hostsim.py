@@ -31,6 +31,17 @@ def test_kernel_math_vs_reference(name, dtype, tol):
         assert abs(got - want) < 1e-9 * abs(want)
 
 
+@pytest.mark.parametrize("name", ["p4", "p6", "p8", "n2p4", "T1", "T2"])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-11), (np.float32, 1e-4)])
+def test_nll_split_form_vs_oracle(name, dtype, tol):
+    """NLL from the helper record (Lam, iv, yy, log prod r) and the scaled chain == the oracle's Gaussian NLL."""
+    c = CORE[name]
+    T, p = c["y"].shape
+    want = o.nll(c["y"], c["m0"], c["S0"], c["C"], np.eye(p), c["A"], c["Q"], c["ev"])
+    r = hostsim.nll_split(c["y"], c["ev"], c["m0"], c["S0"], c["C"], c["A"], c["Q"], dtype=dtype)
+    assert r["rc"] == 0 and abs(r["nll"] - want) < tol * abs(want)
+
+
 def test_newton_first_frame_mode():
     c = CORE["p4"]
     S0i = np.linalg.inv(c["S0"])      # the kernel inverts S0 itself; the host build takes P0 directly

@@ -17,17 +17,25 @@ def run(dt, B, T, G, p=4, n=3):
     prm = dev.TrackParams.from_numpy(np.zeros(n), np.eye(n), C, np.eye(n), 1e-3 * np.eye(n), dtype=dt, device=d)
     grid = np.logspace(-2, 2, G)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    for r in range(3):
-        e0.record()
-        nll, st = sel.nll_grid(obs, prm, B, T, grid)
-        tot = sel.nll_sums(nll)
-        e1.record()
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1)
-        if r:
-            print(f"{str(dt):14s} B={B} T={T} grid={G}: NLL sweep {ms:8.2f} ms -> {B*T*G/ms*1e-6:7.2f} G track-frame-evaluations/s, "
-                  f"obs bytes read once = {B*T*2*p*obs.element_size()/ms*1e-6:7.1f} GB/s", flush=True)
-    filt, _, _ = dev.kf_forward(obs, prm, B, T)
+    tots = {}
+    for mode in ("1", "0"):                                  # pipelined NLL kernel / plain thread-per-track kernel
+        os.environ["EKSB_NLL_PIPE"] = mode
+        for r in range(3):
+            e0.record()
+            nll, st = sel.nll_grid(obs, prm, B, T, grid)
+            tot = sel.nll_sums(nll)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            if r:
+                print(f"{str(dt):14s} B={B} T={T} grid={G} {'pipe ' if mode == '1' else 'plain'}: NLL sweep {ms:8.2f} ms -> {B*T*G/ms*1e-6:7.2f} G track-frame-evaluations/s, "
+                      f"obs bytes read once = {B*T*2*p*obs.element_size()/ms*1e-6:7.1f} GB/s", flush=True)
+        tots[mode] = tot.cpu().numpy()
+    os.environ.pop("EKSB_NLL_PIPE", None)
+    print("   pipe vs plain: max rel diff of the grid sums", float(np.abs(tots["1"] - tots["0"]).max() / np.abs(tots["0"]).max()), flush=True)
+    e0.record(); filt, _, _ = dev.kf_forward(obs, prm, B, T); e1.record(); torch.cuda.synchronize()
+    e0.record(); filt, _, _ = dev.kf_forward(obs, prm, B, T, filt=filt); e1.record(); torch.cuda.synchronize()
+    print(f"{str(dt):14s} B={B} T={T} forward filter (records written) {e0.elapsed_time(e1):8.2f} ms", flush=True)
     out = dev.rts_backward(filt, prm, B, T, inplace=True)
     for r in range(3):
         e0.record()
