@@ -19,6 +19,10 @@ inline int check_launch(const char* what) {
   return EKSB_OK;
 }
 
+// Multiprocessors of the CURRENT device (148 on B200), queried once per device: every launch-shape decision
+// (tiles per CTA, virtual tiles of the time-split scan, grid caps) scales with it instead of a literal.
+int sm_count();
+
 __host__ __device__ inline long num_tiles(long B) { return (B + kLanes - 1) / kLanes; }
 __device__ __forceinline__ long num_tiles_dev(long B) { return (B + kLanes - 1) / kLanes; }
 

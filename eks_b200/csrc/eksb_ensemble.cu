@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(256) ensemble_tiled_kernel(const T* __restrict
 template <typename T, int M>
 static int launch_ensemble(const T* preds, long TK, int mode, T* avg, T* var, cudaStream_t st) {
   long blocks = (TK + 255) / 256;
-  const long cap = 148L * 64;   // a few waves of 148 SMs; grid-stride covers the rest
+  const long cap = (long)sm_count() * 64;   // a few waves over the SMs; grid-stride covers the rest
   if (blocks > cap) blocks = cap;
   ensemble_kernel<T, M><<<(unsigned)blocks, 256, 0, st>>>(preds, TK, mode, avg, var);
   return check_launch("ensemble_kernel");
@@ -177,7 +177,7 @@ static int ensemble_api(const T* preds, int M, long Tn, long K, int mode, T* avg
   }
   if (M < 1 || M > kMaxModels) { set_error("ensemble: M=%d outside 1..%d", M, kMaxModels); return EKSB_EDIM; }
   long blocks = (Tn * K + 255) / 256;
-  if (blocks > 148L * 64) blocks = 148L * 64;
+  if (blocks > (long)sm_count() * 64) blocks = (long)sm_count() * 64;
   ensemble_anym_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(preds, M, Tn * K, mode, avg, var);
   return check_launch("ensemble_anym_kernel");
 }

@@ -15,6 +15,17 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+int sm_count() {
+  static int cached[64];                                   // 0 = not queried yet; benign race: every thread writes the same value
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    cached[dev] = (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) ? n : 148;
+  }
+  return cached[dev];
+}
+
 bool use_pipe(long B) {
   const char* e = getenv("EKSB_PIPE");                    // read per call: tests switch kernel families in-process
   return !(e && e[0] == '0') && B > 0;

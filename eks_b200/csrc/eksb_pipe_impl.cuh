@@ -7,12 +7,12 @@ namespace eksb {
 
 constexpr size_t kCtaSmemBudget = 227 * 1024;   // one CTA may take the whole SM
 constexpr size_t kTileSmemBudget = 56 * 1024;   // four tiles per SM
-constexpr int kSMs = 148;                       // B200
 
 // Tiles per CTA for a launch over `tiles` track tiles.  A tile lives on one SM for the whole pass, so
-// the pass takes as long as the most loaded SM: aim for ceil(tiles/148) tiles on every busy SM, in ONE
+// the pass takes as long as the most loaded SM: aim for ceil(tiles / #SMs) tiles on every busy SM, in ONE
 // CTA (warp w runs on scheduler w % 4, so the chain warps 0..tpc-1 land on distinct schedulers).
 inline int pick_tpc(long tiles, int tpc_max, size_t tile_smem) {
+  const int kSMs = sm_count();
   long per_sm = (tiles + kSMs - 1) / kSMs;
   if (per_sm < 1) per_sm = 1;
   for (int c = 1; c <= 8; ++c) {                  // c co-resident CTAs per SM when one CTA cannot hold per_sm tiles
@@ -242,6 +242,7 @@ static int launch_fwd_pipe(const T* obs, const T* m0, const T* S0, const T* C, c
   using Shallow = AutoCfg<T, kFwdHelpers, 2 * P, Rec<N>::FWD, EKSB_FWD_F, EKSB_FWD_NST>;
   using Deep = AutoCfg<T, EKSB_FWD_DEEP_H, 2 * P, Rec<N>::FWD, 8, 4>;
   const long nvt = vtile_count(B, vt);
+  const int kSMs = sm_count();
   if constexpr (OP == 0 && AM == 0 && N <= 3 && Auto3<T, N, P, Fwd3Helpers<T>::value>::ok) {
     const long per_sm = (nvt + kSMs - 1) / kSMs;
     // Measured (f64, 100 000 frames, sustained): one tile per SM 16.2 -> 13.5 ms (the pass runs at the chain's
@@ -287,6 +288,7 @@ template <typename T, int N, int P, int AM, int OP, int OUT>
 static int launch_bwd_pipe_out(const T* filt, const T* C, const T* A, const T* Q, int shared_mask, long B, long Tn,
                                T* smth, T* ym, T* yv, int* status, cudaStream_t st, const VTiles& vt = VTiles()) {
   const long nvt = vtile_count(B, vt);
+  const int kSMs = sm_count();
   using Narrow = AutoCfg<T, kBwdHelpers, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_F, EKSB_BWD_NST>;
   using Wide = AutoCfg<T, EKSB_BWD_WIDE_H, Dim<N>::SIGMA, Rec<N>::BWD, EKSB_BWD_WIDE_F, EKSB_BWD_WIDE_NST>;
   // "Solo": an SM holds one tile, so the whole shared memory and all four schedulers serve it -- 4 helpers on
@@ -355,7 +357,7 @@ int kf_forward_pipe_vt(const T* obs, const T* m0, const T* S0, const T* C, const
 inline size_t pipe_vt_target_tiles_impl(int n, int p, int elem_size) {
 #define X(N_, P_)                                                                                              \
   if (n == N_ && p == P_)                                                                                      \
-    return (size_t)kSMs * (elem_size == 8 ? AutoCfg<double, kFwdHelpers, 2 * P_, Rec<N_>::FWD, EKSB_FWD_F, EKSB_FWD_NST>::TPC \
+    return (size_t)sm_count() * (elem_size == 8 ? AutoCfg<double, kFwdHelpers, 2 * P_, Rec<N_>::FWD, EKSB_FWD_F, EKSB_FWD_NST>::TPC \
                                           : AutoCfg<float, kFwdHelpers, 2 * P_, Rec<N_>::FWD, EKSB_FWD_F, EKSB_FWD_NST>::TPC);
   EKSB_FOR_EACH_PIPE_DIM(X)
 #undef X

@@ -37,17 +37,17 @@ inline long scan_auto_chunk(long B, long Tn, int n, int elem_size, int p = 4) {
     return L < 64 ? 64L : L;
   };
   const long forced = scan_env_long("EKSB_SCAN_WARPS_PER_SM", 0);
-  if (forced > 0) return len((148L * forced + tiles - 1) / tiles);
+  if (forced > 0) return len(((long)sm_count() * forced + tiles - 1) / tiles);
   if (scan_v2_enabled()) {
     long target = (long)pipe_vt_target_tiles(n, p, elem_size);
-    if (target <= 0) target = 148L * 4;
+    if (target <= 0) target = (long)sm_count() * 4;
     long nc = target / tiles;
     const long nc_max = Tn / 2048;
     if (nc > nc_max) nc = nc_max;
     return len(nc);
   }
-  const long L12 = len((148L * 12 + tiles - 1) / tiles);
-  return L12 >= 3500 ? L12 : len((148L * 8 + tiles - 1) / tiles);
+  const long L12 = len(((long)sm_count() * 12 + tiles - 1) / tiles);
+  return L12 >= 3500 ? L12 : len(((long)sm_count() * 8 + tiles - 1) / tiles);
 }
 
 // Workspace layout shared by the forward and the backward half (they may be launched by separate calls).
@@ -212,7 +212,7 @@ inline bool route_scan(long B, long Tn, int n, int p, int elem_size) {
     // 256 tiles 24.8 / 24.1); in the bench's sustained, power-capped region 2 x 256 tiles take 89.7 / 88.0 ms.
     // Hence: at least two chunks per tile and at most 0.45 x the tiles that fill the GPU (256 of 592).
     long target = (long)pipe_vt_target_tiles(n, p, elem_size);
-    if (target <= 0) target = 148L * 4;
+    if (target <= 0) target = (long)sm_count() * 4;
     if (tiles * 100 > target * 45) return false;
     const long L = scan_auto_chunk(B, Tn, n, elem_size, p);
     return (Tn + L - 1) / L >= 2;

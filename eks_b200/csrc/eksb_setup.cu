@@ -21,17 +21,16 @@
 namespace eksb {
 
 constexpr int kMomWarpsPerCta = 4;
-constexpr int kSetupSMs = 148;
 
 // time slices per tile: enough (tile, slice) work items to fill the GPU even for a few long tracks
 inline int select_slices(long tiles, long Tn) {      // one 8-warp CTA per (tile, slice)
-  long s = (kSetupSMs * 4 + tiles - 1) / tiles;
+  long s = ((long)sm_count() * 4 + tiles - 1) / tiles;
   const long cap = (Tn + 2047) / 2048;
   if (s > cap) s = cap;
   return (int)(s < 1 ? 1 : s);
 }
 inline int moment_slices(long tiles, long Tn) {      // one warp per (tile, slice)
-  long s = (kSetupSMs * 32 + tiles - 1) / tiles;
+  long s = ((long)sm_count() * 32 + tiles - 1) / tiles;
   if (s < 16) s = 16;
   const long cap = (Tn + 255) / 256;
   if (s > cap) s = cap;

@@ -14,4 +14,5 @@ timeout 900 python bench.py --dtype f32 --no-cpu > $O/bench_f32.json 2> $O/bench
 for S in 4096 2048; do
   timeout 600 python bench.py --tracks $S --no-cpu --no-e2e --no-c5 --no-setup --no-sustained > $O/bench_f64_shard$S.json 2> $O/bench_f64_shard$S.err; echo "bench shard $S rc=$?" | tee -a $O/rc2.txt
 done
+ITERS=200 timeout 600 python tools/stress_parity.py > $O/stress_parity.log 2>&1; echo "stress rc=$?" | tee -a $O/rc2.txt
 cat $O/rc2.txt
