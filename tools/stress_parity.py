@@ -14,6 +14,7 @@ from conftest import rel
 rng = np.random.default_rng(int(os.environ.get("SEED", "0")))
 d = torch.device("cuda", 0)
 worst = {}
+worst_n = {}
 nfail = 0
 for it in range(int(os.environ.get("ITERS", "150"))):
     n, p = [(3, 4), (3, 6), (3, 8), (2, 4), (4, 6), (6, 8)][rng.integers(6)]
@@ -47,8 +48,11 @@ for it in range(int(os.environ.get("ITERS", "150"))):
         for k, e in errs.items():
             key = (str(dt)[6:], k)
             worst[key] = max(worst.get(key, 0.0), e)
+            kn = (str(dt)[6:], f"n={n}", "Vs/Vf" if k in ("Vs", "Vf") else "means")
+            worst_n[kn] = max(worst_n.get(kn, 0.0), e)
             if not (e < tol):
                 nfail += 1
                 print("FAIL", dict(n=n, p=p, B=B, T=T, dt=str(dt), a_diag=a_diag, b=b), k, e, flush=True)
 print("worst relative errors:", {k: float(f"{v:.3g}") for k, v in sorted(worst.items())})
-print("failures:", nfail)
+print("worst by state dimension:", {" ".join(k): float(f"{v:.3g}") for k, v in sorted(worst_n.items())})
+print("failures (fp32 bar 1e-3, fp64 1e-8, per component):", nfail)
