@@ -38,9 +38,13 @@ inline int moment_slices(long tiles, long Tn) {      // one warp per (tile, slic
   return (int)(s < 1 ? 1 : s);
 }
 template <int P> constexpr int mom_rows() { return 2 + 4 * P + P * (P + 1); }
-constexpr int kCandCap = 1024;    // candidate slots per track after the full-length select passes
+constexpr int kCandCap = 8192;    // candidate slots per track after the full-length select pass(es)
+// Wide first digit of the select (round 2): sign + exponent + kWideMant mantissa bits, i.e. 8 bins per binade, in a
+// window of kWideBins bins centred on 1.0 (2^-32 .. 2^32); + one bin below and one above the window.
+constexpr int kMomGroups = 32;    // few tiles, long tracks: the moment slices are folded to this many before the finalize
+constexpr int kWideMant = 3, kWideBins = 512, kWideRows = kWideBins + 2, kWideHalfBinades = 32;
 struct SetupWs {                  // workspace layout in 8-byte words
-  size_t thr, state, ghist, part, cand, flag, mx, total;
+  size_t thr, state, ghist, ghist2, gwide, part2, part, cand, flag, mx, total;
 };
 inline SetupWs setup_layout(long B, long Tn, int p, int elem_size) {
   const size_t tiles = (size_t)num_tiles(B);
@@ -49,10 +53,13 @@ inline SetupWs setup_layout(long B, long Tn, int p, int elem_size) {
   w.thr = 0;
   w.state = w.thr + tiles * kLanes;
   w.ghist = w.state + tiles * 6 * kLanes;
-  w.part = w.ghist + (size_t)npass * tiles * 256 * kLanes / 2;
+  w.ghist2 = w.ghist + (size_t)npass * tiles * 256 * kLanes / 2;      // short passes of the wide-digit path
+  w.gwide = w.ghist2 + (size_t)npass * tiles * 256 * kLanes / 2;
+  w.part2 = w.gwide + tiles * (size_t)kWideRows * kLanes / 2;         // moment partials folded to kMomGroups per tile
+  w.part = w.part2 + tiles * (size_t)kMomGroups * (2 + 4 * p + p * (p + 1)) * kLanes;
   w.cand = w.part + tiles * (size_t)moment_slices((long)tiles, Tn) * (2 + 4 * p + p * (p + 1)) * kLanes;
   w.flag = w.cand + (tiles * (size_t)kCandCap * kLanes * elem_size + 7) / 8;
-  w.mx = w.flag + 1;
+  w.mx = w.flag + 2;                                 // ints: [0] candidate overflow, [1] fallback to the 8-bit passes, [2] deepen, [3] 1|2
   w.total = w.mx + (tiles * (size_t)Tn * kLanes * elem_size + 7) / 8;
   return w;
 }
@@ -126,27 +133,34 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 setup_hist_kernel(const T* __restrict__ mx, long Tn, const T* __restrict__ cand, const int* __restrict__ overflow,
                   int slices, int shift, const unsigned long long* __restrict__ state,
-                  unsigned int* __restrict__ ghist /* [tile][256][32], this pass */) {
+                  unsigned int* __restrict__ ghist /* [tile][256][32], this pass */, int match_shift,
+                  const int* __restrict__ gate, int gate_want, const int* __restrict__ deep = nullptr, int deep_match = 0) {
   using K = KeyOf<T>;
   using Key = typename K::type;
   __shared__ unsigned int hist[256][kLanes];
+  if (gate && (*gate != 0) != (gate_want != 0)) return;    // wide-digit path vs its 8-bit fallback
+  // after the extra full-length digit of the wide path the rank counts inside the longer prefix: match all of it
+  // (the same keys on the candidates; it matters when the remaining passes run at full length)
+  if (deep && *deep && deep_match < match_shift) match_shift = deep_match;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long g = blockIdx.x / slices;
   const int sl = (int)(blockIdx.x - g * slices);
   const bool use_c = cand && *overflow == 0;               // candidates collected: the short buffer holds every match
-  const long n = use_c ? kCandCap : Tn;
+  long n = Tn;
+  if (use_c)                                               // ... in its first max-over-the-tile NCAND slots
+    n = (long)__reduce_max_sync(0xffffffffu, (unsigned)state[(g * SelState::WORDS + SelState::NCAND) * kLanes + lane]);
   const long len = (n + slices - 1) / slices;
   const long t0 = sl * len, t1 = (t0 + len < n) ? t0 + len : n;
   if (t0 >= t1) return;
   for (int i = threadIdx.x; i < 256 * kLanes; i += blockDim.x) (&hist[0][0])[i] = 0;
   __syncthreads();
   const Key prefix = (Key)state[(g * SelState::WORDS + SelState::PREFIX) * kLanes + lane];
-  const bool top = (shift == K::kBits - 8);
+  const bool top = (match_shift >= K::kBits);              // no prefix yet: every key takes part
   const T* base = (use_c ? cand + g * kCandCap * kLanes : mx + g * Tn * kLanes) + lane;
   for (long t = t0 + warp; t < t1; t += 8) {
     const Key key = K::of(base[t * kLanes]);
     if (use_c && key == (Key) ~(Key)0) continue;          // empty candidate slot
-    if (top || (key >> ((shift + 8) & (K::kBits - 1))) == (prefix >> ((shift + 8) & (K::kBits - 1))))
+    if (top || (key >> (match_shift & (K::kBits - 1))) == (prefix >> (match_shift & (K::kBits - 1))))
       atomicAdd(&hist[(unsigned)(key >> shift) & 255u][lane], 1u);
   }
   __syncthreads();
@@ -162,9 +176,11 @@ setup_hist_kernel(const T* __restrict__ mx, long Tn, const T* __restrict__ cand,
 // then warp 0 (lane = track) walks its 256 bins there.
 template <typename T>
 __global__ void __launch_bounds__(256)
-setup_pick_kernel(const unsigned int* __restrict__ ghist, int shift, unsigned long long* __restrict__ state) {
+setup_pick_kernel(const unsigned int* __restrict__ ghist, int shift, unsigned long long* __restrict__ state,
+                  const int* __restrict__ gate, int gate_want) {
   using Key = typename KeyOf<T>::type;
   __shared__ unsigned int hist[256 * kLanes];
+  if (gate && (*gate != 0) != (gate_want != 0)) return;
   const long g = blockIdx.x;
   const uint4* src = reinterpret_cast<const uint4*>(ghist + g * 256 * kLanes);
   uint4* dst = reinterpret_cast<uint4*>(hist);
@@ -196,7 +212,8 @@ setup_tail_kernel(const T* __restrict__ mx, long Tn, const T* __restrict__ cand,
   const long g = blockIdx.x / slices;
   const int sl = (int)(blockIdx.x - g * slices);
   const bool use_c = cand && *overflow == 0;
-  const long n = use_c ? kCandCap : Tn;
+  long n = Tn;
+  if (use_c) n = (long)__reduce_max_sync(0xffffffffu, (unsigned)state[(g * SelState::WORDS + SelState::NCAND) * kLanes + lane]);
   const long len = (n + slices - 1) / slices;
   const long t0 = sl * len, t1 = (t0 + len < n) ? t0 + len : n;
   if (t0 >= t1) return;
@@ -227,10 +244,16 @@ setup_tail_kernel(const T* __restrict__ mx, long Tn, const T* __restrict__ cand,
 template <typename T>
 __global__ void __launch_bounds__(256)
 setup_collect_kernel(const T* __restrict__ mx, long Tn, int slices, int low_bit, unsigned long long* __restrict__ state,
-                     T* __restrict__ cand, int* __restrict__ overflow) {
+                     T* __restrict__ cand, int* __restrict__ overflow, const int* __restrict__ gate, int gate_want) {
   using K = KeyOf<T>;
   using Key = typename K::type;
+  // The wide-digit path collects ~T/25 keys per track: one global atomic per key on the track's counter was half of
+  // this kernel's time.  Each thread (one track, every 8th frame of the slice) stages its matches in a private strip
+  // of shared memory and reserves their slots with one atomic per kStage matches; no CTA-wide synchronisation.
+  constexpr int kStage = 8;
   __shared__ unsigned long long s_above[kLanes];
+  __shared__ T s_buf[8][kStage][kLanes];
+  if (gate && (*gate != 0) != (gate_want != 0)) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long g = blockIdx.x / slices;
   const int sl = (int)(blockIdx.x - g * slices);
@@ -244,21 +267,141 @@ setup_collect_kernel(const T* __restrict__ mx, long Tn, int slices, int low_bit,
   const T* base = mx + g * Tn * kLanes + lane;
   T* out = cand + g * kCandCap * kLanes + lane;
   unsigned long long above = ~0ull;
-  for (long t = t0 + warp; t < t1; t += 8) {
-    const T v = base[t * kLanes];
+  int cnt = 0;
+  auto flush = [&]() {
+    if (cnt == 0) return;
+    unsigned long long idx = atomicAdd(&st[SelState::NCAND * kLanes], (unsigned long long)cnt);
+    for (int i = 0; i < cnt; ++i, ++idx) {
+      if (idx < (unsigned long long)kCandCap) out[idx * kLanes] = s_buf[warp][i][lane];
+      else atomicExch(overflow, 1);
+    }
+    cnt = 0;
+  };
+  auto take = [&](T v) {
     const Key key = K::of(v);
     const Key kp = key >> low_bit;
     if (kp == pp) {
-      const unsigned long long idx = atomicAdd(&st[SelState::NCAND * kLanes], 1ull);
-      if (idx < (unsigned long long)kCandCap) out[idx * kLanes] = v;
-      else atomicExch(overflow, 1);
+      s_buf[warp][cnt++][lane] = v;
     } else if (kp > pp && (unsigned long long)key < above) {
       above = key;
     }
+  };
+  long t = t0 + warp;
+  for (; t + 24 < t1; t += 32) {                           // four lines in flight per warp
+    const T v0 = base[t * kLanes], v1 = base[(t + 8) * kLanes], v2 = base[(t + 16) * kLanes], v3 = base[(t + 24) * kLanes];
+    if (cnt > kStage - 4) flush();
+    take(v0); take(v1); take(v2); take(v3);
   }
+  for (; t < t1; t += 8) {
+    if (cnt >= kStage) flush();
+    take(base[t * kLanes]);
+  }
+  flush();
   if (above != ~0ull) atomicMin(&s_above[lane], above);
   __syncthreads();
   if (warp == 0 && s_above[lane] != ~0ull) atomicMin(&st[SelState::NEXT * kLanes], s_above[lane]);
+}
+
+// ---- wide first digit (round 2): ONE full-length pass instead of three ------------------------------------------
+// The top byte of a positive float is almost all exponent: ensemble variances of a session span a few binades, so the
+// first 8-bit pass fills 3 bins and the select needs three full-length passes before a handful of keys are left.  Here
+// the first digit is sign + exponent + 3 mantissa bits inside a window of 64 binades around 1.0: one pass leaves
+// ~T/50 keys per track (one eighth of a binade), which are collected at once; the remaining bits are resolved on the
+// candidates.  Off the common case, decided on the device behind flags (the other side's kernels exit at once):
+//   * the bin holds more keys than candidate slots (the pick kernel has the count): one more full-length 8-bit digit
+//     below the wide one, then collect -- four full-length reads, what round 1 always paid;
+//   * still more than the slots (tied keys): the remaining passes run at full length, as in round 1;
+//   * the rank falls below / above the window (zero or absurd variances): the round-1 8-bit passes from the top.
+template <typename T> struct WideOf;
+template <> struct WideOf<double> { static constexpr int shift = 52 - kWideMant; static constexpr long base = (long)(1023 - kWideHalfBinades) << kWideMant; };
+template <> struct WideOf<float> { static constexpr int shift = 23 - kWideMant; static constexpr long base = (long)(127 - kWideHalfBinades) << kWideMant; };
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+setup_wide_kernel(const T* __restrict__ mx, long Tn, int slices, unsigned int* __restrict__ gwide /* [tile][kWideRows][32] */) {
+  using K = KeyOf<T>;
+  using Key = typename K::type;
+  extern __shared__ unsigned int whist[];                  // [kWideRows][32]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long g = blockIdx.x / slices;
+  const int sl = (int)(blockIdx.x - g * slices);
+  const long len = (Tn + slices - 1) / slices;
+  const long t0 = sl * len, t1 = (t0 + len < Tn) ? t0 + len : Tn;
+  if (t0 >= t1) return;
+  for (int i = threadIdx.x; i < kWideRows * kLanes; i += blockDim.x) whist[i] = 0;
+  __syncthreads();
+  const T* base = mx + g * Tn * kLanes + lane;
+  auto bin_of = [](Key key) {
+    const long d = (long)(key >> WideOf<T>::shift) - WideOf<T>::base;
+    return d < 0 ? kWideBins : (d >= kWideBins ? kWideBins + 1 : (int)d);
+  };
+  long t = t0 + warp;
+  for (; t + 24 < t1; t += 32) {                           // four lines in flight per warp
+    const Key k0 = K::of(base[t * kLanes]), k1 = K::of(base[(t + 8) * kLanes]), k2 = K::of(base[(t + 16) * kLanes]),
+              k3 = K::of(base[(t + 24) * kLanes]);
+    atomicAdd(&whist[bin_of(k0) * kLanes + lane], 1u);
+    atomicAdd(&whist[bin_of(k1) * kLanes + lane], 1u);
+    atomicAdd(&whist[bin_of(k2) * kLanes + lane], 1u);
+    atomicAdd(&whist[bin_of(k3) * kLanes + lane], 1u);
+  }
+  for (; t < t1; t += 8) atomicAdd(&whist[bin_of(K::of(base[t * kLanes])) * kLanes + lane], 1u);
+  __syncthreads();
+  unsigned int* gh = gwide + g * kWideRows * kLanes;
+  for (int i = threadIdx.x; i < kWideRows * kLanes; i += blockDim.x) {
+    const unsigned int c = whist[i];
+    if (c) atomicAdd(&gh[i], c);
+  }
+}
+
+// one CTA per tile: walk the wide histogram to the bin holding rank k; below / above the window -> fallback
+template <typename T>
+__global__ void __launch_bounds__(256)
+setup_wide_pick_kernel(const unsigned int* __restrict__ gwide, unsigned long long* __restrict__ state, long B,
+                       int* __restrict__ fallback, int* __restrict__ deep, int* __restrict__ skip_collect) {
+  using Key = typename KeyOf<T>::type;
+  extern __shared__ unsigned int whist[];
+  const long g = blockIdx.x;
+  const uint4* src = reinterpret_cast<const uint4*>(gwide + g * kWideRows * kLanes);
+  uint4* dst = reinterpret_cast<uint4*>(whist);
+  for (int i = threadIdx.x; i < kWideRows * kLanes / 4; i += blockDim.x) dst[i] = src[i];
+  __syncthreads();
+  if (threadIdx.x >= kLanes) return;
+  const int lane = threadIdx.x;
+  if (g * kLanes + lane >= B) return;                      // padding lanes of the last tile (all-zero records) do not vote
+  unsigned long long* st = state + g * SelState::WORDS * kLanes + lane;
+  long k = (long)st[SelState::RANK * kLanes];
+  const long under = whist[kWideBins * kLanes + lane];
+  if (k < under) { atomicExch(fallback, 1); atomicExch(skip_collect, 1); return; }
+  k -= under;
+  int d = 0;
+  for (; d < kWideBins; ++d) {
+    const unsigned c = whist[d * kLanes + lane];
+    if (k < (long)c) break;
+    k -= c;
+  }
+  if (d == kWideBins) { atomicExch(fallback, 1); atomicExch(skip_collect, 1); return; }
+  // more keys in the bin than candidate slots (long or narrowly distributed tracks): one more full-length digit first
+  if (whist[d * kLanes + lane] > (unsigned)kCandCap) { atomicExch(deep, 1); atomicExch(skip_collect, 1); }
+  st[SelState::RANK * kLanes] = (unsigned long long)k;
+  st[SelState::PREFIX * kLanes] = (unsigned long long)((Key)(WideOf<T>::base + d) << WideOf<T>::shift);
+}
+
+// fallback only: bring the select state and the candidate buffer back to their initial values
+template <typename T>
+__global__ void __launch_bounds__(256)
+setup_fallback_reset_kernel(unsigned long long* __restrict__ state, long tiles, long lo, T* __restrict__ cand,
+                            const int* __restrict__ fallback, int* __restrict__ overflow) {
+  if (*fallback == 0) return;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *overflow = 0;
+  const long nthr = (long)gridDim.x * blockDim.x, i0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (long i = i0; i < tiles * kLanes; i += nthr) {
+    unsigned long long* st = state + (i / kLanes) * SelState::WORDS * kLanes + (i % kLanes);
+    st[SelState::PREFIX * kLanes] = 0; st[SelState::RANK * kLanes] = (unsigned long long)lo; st[SelState::CNT_LE * kLanes] = 0;
+    st[SelState::NEXT * kLanes] = ~0ull; st[SelState::NCAND * kLanes] = 0; st[SelState::RANK_C * kLanes] = 0;
+  }
+  using Key = typename KeyOf<T>::type;
+  Key* c = reinterpret_cast<Key*>(cand);
+  for (long i = i0; i < tiles * (long)kCandCap * kLanes; i += nthr) c[i] = (Key) ~(Key)0;
 }
 
 __global__ void setup_init_state_kernel(unsigned long long* __restrict__ state, long lo) {
@@ -445,6 +588,58 @@ template <int P> __device__ __noinline__ void jacobi_eig(double* a, double* d, d
   }
 }
 
+// Few tiles and long tracks leave thousands of moment slices per tile (one warp each, to fill the GPU); the finalize
+// kernel walks them in frame order, one thread per track (6 ms at 64 tracks x 2M frames).  One warp per (tile, group)
+// folds a run of consecutive slices into one partial of the same layout first; the finalize then walks kMomGroups.
+template <int P>
+__global__ void __launch_bounds__(256)
+setup_reduce_kernel(const double* __restrict__ part, long tiles, int slices, int groups, double* __restrict__ part2) {
+  using MR = MomRows<P>;
+  constexpr int PS = MR::PS;
+  const int lane = threadIdx.x & 31;
+  const long w = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const long g = w / groups;
+  const int grp = (int)(w - g * groups);
+  if (g >= tiles) return;
+  const int per = (slices + groups - 1) / groups, s0 = grp * per, s1 = (s0 + per < slices) ? s0 + per : slices;
+  double n0 = 0, nd = 0, sy[P], syy[PS], sd[P], sdd[PS], first[P], last[P];
+  for (int j = 0; j < P; ++j) sy[j] = sd[j] = first[j] = last[j] = 0;
+  for (int j = 0; j < PS; ++j) syy[j] = sdd[j] = 0;
+  bool have = false;
+  for (int sl = s0; sl < s1; ++sl) {
+    const double* r = part + ((g * slices + sl) * MR::ROWS) * kLanes + lane;
+    const double n_s = r[MR::N0 * kLanes];
+    if (n_s == 0) continue;
+    if (have) {                                 // stitch, as in the finalize kernel
+      double d[P];
+      for (int j = 0; j < P; ++j) { d[j] = r[(MR::FIRST + j) * kLanes] - last[j]; sd[j] += d[j]; }
+      int k = 0;
+      for (int i = 0; i < P; ++i)
+        for (int j = i; j < P; ++j) sdd[k++] += d[i] * d[j];
+      nd += 1;
+    } else {
+      for (int j = 0; j < P; ++j) first[j] = r[(MR::FIRST + j) * kLanes];
+    }
+    have = true;
+    n0 += n_s;
+    nd += r[MR::ND * kLanes];
+    for (int j = 0; j < P; ++j) {
+      sy[j] += r[(MR::SY + j) * kLanes];
+      sd[j] += r[(MR::SD + j) * kLanes];
+      last[j] = r[(MR::LAST + j) * kLanes];
+    }
+    for (int j = 0; j < PS; ++j) { syy[j] += r[(MR::SYY + j) * kLanes]; sdd[j] += r[(MR::SDD + j) * kLanes]; }
+  }
+  double* o = part2 + ((g * groups + grp) * MR::ROWS) * kLanes + lane;
+  o[MR::N0 * kLanes] = n0;
+  o[MR::ND * kLanes] = nd;
+  for (int j = 0; j < P; ++j) {
+    o[(MR::SY + j) * kLanes] = sy[j]; o[(MR::SD + j) * kLanes] = sd[j];
+    o[(MR::FIRST + j) * kLanes] = first[j]; o[(MR::LAST + j) * kLanes] = last[j];
+  }
+  for (int j = 0; j < PS; ++j) { o[(MR::SYY + j) * kLanes] = syy[j]; o[(MR::SDD + j) * kLanes] = sdd[j]; }
+}
+
 template <typename T, int P, int N>
 __global__ void setup_finalize_kernel(const T* __restrict__ obs, const double* __restrict__ part, long B, long Tn,
                                       int slices, double smooth_param, T* __restrict__ means, T* __restrict__ Cout,
@@ -577,36 +772,83 @@ static int setup_run(T* obs, long B, long Tn, int n, double q, double s, int cen
   T* cand = reinterpret_cast<T*>(ws + L.cand);
   int* overflow = reinterpret_cast<int*>(ws + L.flag);
   const int npass = (int)sizeof(Key), ssl = select_slices(tiles, Tn), msl = moment_slices(tiles, Tn);
+  unsigned int* ghist2 = reinterpret_cast<unsigned int*>(ws + L.ghist2);
+  unsigned int* gwide = reinterpret_cast<unsigned int*>(ws + L.gwide);
+  int* fallback = overflow + 1;
   // full-length passes before the candidates are collected (EKSB_SETUP_NO_COLLECT=1: never, every pass full length)
   const char* nc = getenv("EKSB_SETUP_NO_COLLECT");
   const int collect_after = (nc && nc[0] == '1') ? npass : (sizeof(T) == 8 ? 3 : 2);
+  const char* nw = getenv("EKSB_SETUP_NO_WIDE");          // A/B switch: 1 = 8-bit passes only (round 1)
   // state: prefix 0, rank = lo, cnt_le 0, next = ~0 ; histograms 0
   long lo;
   double gamma;
   percentile_position(Tn, q, lo, gamma);
-  cudaMemsetAsync(ghist, 0, (size_t)npass * tiles * 256 * kLanes * sizeof(unsigned int), st);
-  cudaMemsetAsync(state, 0, (size_t)tiles * SelState::WORDS * kLanes * 8, st);
-  cudaMemsetAsync(overflow, 0, 8, st);
   const bool collect = collect_after < npass;
+  const bool wide = collect && !(nw && nw[0] == '1');
+  cudaMemsetAsync(ghist, 0, (size_t)npass * tiles * 256 * kLanes * sizeof(unsigned int), st);
+  if (wide) {
+    cudaMemsetAsync(ghist2, 0, (size_t)npass * tiles * 256 * kLanes * sizeof(unsigned int), st);
+    cudaMemsetAsync(gwide, 0, (size_t)tiles * kWideRows * kLanes * sizeof(unsigned int), st);
+  }
+  cudaMemsetAsync(state, 0, (size_t)tiles * SelState::WORDS * kLanes * 8, st);
+  cudaMemsetAsync(overflow, 0, 16, st);                                                          // overflow, fallback, deepen
   if (collect) cudaMemsetAsync(cand, 0xFF, (size_t)tiles * kCandCap * kLanes * sizeof(T), st);   // all-ones key = empty slot
   setup_init_state_kernel<<<(unsigned)tiles, kLanes, 0, st>>>(state, lo);
   if (!mx_ready)     // else the ensemble kernel wrote max_vars into the workspace already (eksb_ensemble_tiled_mx)
     setup_mx_kernel<T, P><<<(unsigned)((tiles * Tn + 7) / 8), 256, 0, st>>>(obs, tiles, Tn, mx);
+  const int* gate = nullptr;
+  if (wide) {
+    // one full-length pass with a wide first digit, the candidates of its bin, the remaining bits on the candidates
+    constexpr int kWideSmem = kWideRows * kLanes * (int)sizeof(unsigned int);
+    cudaFuncSetAttribute(setup_wide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideSmem);
+    cudaFuncSetAttribute(setup_wide_pick_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideSmem);
+    setup_wide_kernel<T><<<(unsigned)(tiles * ssl), 256, kWideSmem, st>>>(mx, Tn, ssl, gwide);
+    int* deep = overflow + 2;
+    int* skip_collect = overflow + 3;                       // fallback or deepen
+    setup_wide_pick_kernel<T><<<(unsigned)tiles, 256, kWideSmem, st>>>(gwide, state, B, fallback, deep, skip_collect);
+    setup_collect_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, ssl, WideOf<T>::shift, state, cand, overflow, skip_collect, 0);
+    // a bin with more keys than candidate slots (the pick kernel knows the count): one more full-length 8-bit digit
+    // below the wide one, then collect -- four full-length reads, what round 1 always paid
+    constexpr int dshift = WideOf<T>::shift - 8;
+    {
+      unsigned int* gh = ghist2 + (size_t)(npass - 1) * tiles * 256 * kLanes;
+      setup_hist_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, nullptr, overflow, ssl, dshift, state, gh, WideOf<T>::shift, deep, 1);
+      setup_pick_kernel<T><<<(unsigned)tiles, 256, 0, st>>>(gh, dshift, state, deep, 1);
+      setup_collect_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, ssl, dshift, state, cand, overflow, deep, 1);
+    }
+    int pass = 0;
+    for (int shift = ((WideOf<T>::shift - 1) / 8) * 8; shift >= 0; shift -= 8, ++pass) {
+      unsigned int* gh = ghist2 + (size_t)pass * tiles * 256 * kLanes;
+      const int match = shift + 8 < WideOf<T>::shift ? shift + 8 : WideOf<T>::shift;
+      setup_hist_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, cand, overflow, ssl, shift, state, gh, match, fallback, 0, deep, dshift);
+      setup_pick_kernel<T><<<(unsigned)tiles, 256, 0, st>>>(gh, shift, state, fallback, 0);
+    }
+    setup_fallback_reset_kernel<T><<<(unsigned)(4 * sm_count()), 256, 0, st>>>(state, tiles, lo, cand, fallback, overflow);
+    gate = fallback;                                        // the 8-bit passes below run only if the flag is up
+  }
   for (int pass = 0; pass < npass; ++pass) {
     const int shift = 8 * (npass - 1 - pass);
     unsigned int* gh = ghist + (size_t)pass * tiles * 256 * kLanes;
     if (pass == collect_after)
-      setup_collect_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, ssl, shift + 8, state, cand, overflow);
+      setup_collect_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, ssl, shift + 8, state, cand, overflow, gate, 1);
     setup_hist_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, pass >= collect_after ? cand : nullptr, overflow,
-                                                                  ssl, shift, state, gh);
-    setup_pick_kernel<T><<<(unsigned)tiles, 256, 0, st>>>(gh, shift, state);
+                                                                  ssl, shift, state, gh, shift + 8, gate, 1);
+    setup_pick_kernel<T><<<(unsigned)tiles, 256, 0, st>>>(gh, shift, state, gate, 1);
   }
   setup_tail_kernel<T><<<(unsigned)(tiles * ssl), 256, 0, st>>>(mx, Tn, collect ? cand : nullptr, overflow, ssl, state);
   setup_thr_kernel<T><<<(unsigned)((B + 127) / 128), 128, 0, st>>>(state, overflow, collect ? 1 : 0, B, Tn, q, thr);
   const long warps = tiles * msl;
   setup_moments_kernel<T, P><<<(unsigned)((warps + kMomWarpsPerCta - 1) / kMomWarpsPerCta), kMomWarpsPerCta * kLanes, 0, st>>>(
       obs, mx, B, Tn, msl, thr, part);
-  setup_finalize_kernel<T, P, 3><<<(unsigned)((B + 63) / 64), 64, 0, st>>>(obs, part, B, Tn, msl, s, means, C, S0, Q, status);
+  const double* fpart = part;
+  int fsl = msl;
+  if (msl > 2 * kMomGroups) {                   // few tiles, long tracks: fold the slices first (see setup_reduce_kernel)
+    double* part2 = ws + L.part2;
+    setup_reduce_kernel<P><<<(unsigned)((tiles * kMomGroups + 7) / 8), 256, 0, st>>>(part, tiles, msl, kMomGroups, part2);
+    fpart = part2;
+    fsl = kMomGroups;
+  }
+  setup_finalize_kernel<T, P, 3><<<(unsigned)((B + 63) / 64), 64, 0, st>>>(obs, fpart, B, Tn, fsl, s, means, C, S0, Q, status);
   if (center) {
     const long warps_c = tiles * ((Tn + kCenterFrames - 1) / kCenterFrames);
     center_rows_kernel<T, P><<<(unsigned)((warps_c + 7) / 8), 256, 0, st>>>(obs, means, B, Tn, 2 * P);

@@ -85,10 +85,11 @@ def _synthetic_session(B, T, p, M=5, seed=0):
     return (clean[None] + sd[None] * rng.normal(size=(M, B, T, p))).transpose(0, 2, 1, 3)   # (M,T,B,p)
 
 
-@pytest.mark.parametrize("B,T,p,q", [(5, 700, 4, 25), (37, 333, 6, 50), (3, 1500, 8, 90), (2, 64, 4, 100)])
+@pytest.mark.parametrize("B,T,p,q", [(5, 700, 4, 25), (37, 333, 6, 50), (3, 1500, 8, 90), (2, 64, 4, 100), (3, 40000, 4, 25)])
 def test_device_parameter_setup_matches_oracle(B, T, p, q):
     """K8: percentile threshold / good-frame means / PCA / S0 / Q computed on the device equal the oracle's
-    restatement of multiview_pca_smoother.py:684-731 (numpy percentile + sklearn PCA) per track."""
+    restatement of multiview_pca_smoother.py:684-731 (numpy percentile + sklearn PCA) per track.  (3 tracks x 40 000
+    frames: 157 moment slices per tile, folded to 32 by setup_reduce_kernel before the finalize.)"""
     import torch
     from eks_b200 import device as dev
     from oracle import restated_smoothers as osm
@@ -112,40 +113,52 @@ def test_device_parameter_setup_matches_oracle(B, T, p, q):
 
 
 @pytest.mark.parametrize("dtname,rtol", [("float64", 1e-10), ("float32", 2e-5)])
-@pytest.mark.parametrize("ties", [False, True])
-def test_percentile_select_candidate_buffer_and_overflow_fallback(dtname, rtol, ties, monkeypatch):
-    """The exact percentile is a radix select; after the first full-length passes the few keys still matching the
-    prefix are collected into a short buffer and the remaining passes run on it.  Same parameters, bit for bit,
-    as with every pass at full length (EKSB_SETUP_NO_COLLECT=1), also when thousands of tied keys overflow the
-    buffer and the kernels fall back to the full-length passes; good-frame means equal the numpy percentile mask."""
+@pytest.mark.parametrize("case", ["plain", "ties", "many_ties", "one_bin", "tiny"])
+def test_percentile_select_candidate_buffer_and_overflow_fallback(dtname, rtol, case, monkeypatch):
+    """The exact percentile is a radix select.  Default: ONE full-length pass with a wide first digit (sign + exponent +
+    3 mantissa bits), the keys of its bin collected into a short buffer, the remaining bits resolved there.  Same
+    parameters, bit for bit, as the round-1 path (three 8-bit passes, then collect: EKSB_SETUP_NO_WIDE=1) and as every
+    pass at full length (EKSB_SETUP_NO_COLLECT=1) -- also off the common case: more keys in the bin than candidate slots
+    ("one_bin": 30 000 variances in [1, 1.05] > 8192 slots -> one more full-length 8-bit digit, then collect again),
+    more TIED keys than slots ("many_ties": 10 000 copies -> the second collect overflows too, remaining passes at full
+    length), or a quantile among variances below the wide digit's window ("tiny": a third of the frames at 1e-30 ->
+    the 8-bit passes).  Good-frame means equal the numpy percentile mask."""
     import torch
     from eks_b200 import device as dev
     from oracle import restated_smoothers as osm
     dt = getattr(torch, dtname)
-    B, T, p = 40, 6000, 4
-    rng = np.random.default_rng(11 + ties)
+    B, p = 40, 4
+    T = 30000 if case in ("many_ties", "one_bin") else 6000
+    rng = np.random.default_rng(11 + len(case))
     y = np.cumsum(rng.normal(size=(B, T, p)) * 0.3, axis=1) + rng.uniform(50, 400, size=(B, 1, p))
     ev = np.exp(rng.normal(np.log(0.05), 1.6, size=(B, T, p)))
-    if ties:                                                          # 3 distinct max_vars, ~2000 copies of each
+    if case in ("ties", "many_ties"):                                 # 3 distinct max_vars, T/3 copies of each
         ev = np.array([0.01, 0.1, 1.0])[rng.integers(0, 3, size=(B, T, 1))] * np.ones(p)
+    if case == "one_bin":
+        ev = 1.0 + 0.05 * rng.random((B, T, p))
+    if case == "tiny":
+        ev = np.where(rng.random((B, T, 1)) < 0.34, 1e-30 * (1 + rng.random((B, T, p))), ev)
     d = torch.device("cuda", 0)
     yt, evt = torch.as_tensor(y, dtype=dt), torch.as_tensor(ev, dtype=dt)
     obs = dev.pack_obs(yt.to(d), evt.to(d))
     for q in (25, 60):
         res = {}
-        for mode in ("collect", "full"):
+        for mode in ("wide", "narrow", "full"):
+            monkeypatch.delenv("EKSB_SETUP_NO_COLLECT", raising=False)
+            monkeypatch.delenv("EKSB_SETUP_NO_WIDE", raising=False)
             if mode == "full":
                 monkeypatch.setenv("EKSB_SETUP_NO_COLLECT", "1")
-            else:
-                monkeypatch.delenv("EKSB_SETUP_NO_COLLECT", raising=False)
+            if mode == "narrow":
+                monkeypatch.setenv("EKSB_SETUP_NO_WIDE", "1")
             prm, means, status = dev.pca_setup(obs.clone(), B, T, p, q, 0.01, center=False)
             assert int(status.sum()) == 0
             res[mode] = (means, prm.C, prm.S0, prm.Q)
-        for a, b in zip(res["collect"], res["full"]):
-            assert torch.equal(a, b)
+        for mode in ("wide", "narrow"):
+            for a, b in zip(res[mode], res["full"]):
+                assert torch.equal(a, b), (mode, q, float((a.double() - b.double()).abs().max()))
         for b in (0, 17, B - 1):
             good = osm.good_frame_mask(evt[b].double().numpy(), q)
-            np.testing.assert_allclose(res["collect"][0][b].cpu().double().numpy(), yt[b].double().numpy()[good].mean(axis=0), rtol=rtol)
+            np.testing.assert_allclose(res["wide"][0][b].cpu().double().numpy(), yt[b].double().numpy()[good].mean(axis=0), rtol=rtol)
 
 
 @pytest.mark.parametrize("dtname", ["float64", "float32"])
