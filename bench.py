@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--group", type=int, default=0, help="tracks per group (default: the largest whose buffers fit)")
     ap.add_argument("--frames", type=int, default=100_000)
     ap.add_argument("--e2e-tracks", type=int, default=4096, help="TOTAL tracks of the end-to-end run, sharded over the GPUs")
-    ap.add_argument("--e2e-block", type=int, default=512)
+    ap.add_argument("--e2e-block", type=int, default=0, help="tracks per streamed block of the e2e run (0 = the API's default sizing)")
     ap.add_argument("--c5-tracks", type=int, default=64)
     ap.add_argument("--c5-frames", type=int, default=10_000_000)
     ap.add_argument("--no-c5", action="store_true", help="skip configs[4] (64 x 10 M)")
@@ -724,7 +724,7 @@ def gpu_main(a):
         outs = batched.alloc_outputs(Be, T, N_LAT, P_OBS, dt, pin=True, outputs=("ym",))
         cnt = {}
         call = lambda c=None: batched.smooth_tracks(y_h, ev_h, pe["m0"], pe["S0"], pe["C"], pe["A"], pe["Q"], dtype=dt,
-                                                    device=d, block_tracks=a.e2e_block, out=outs, outputs=("ym",), counters=c)
+                                                    device=d, block_tracks=a.e2e_block or None, out=outs, outputs=("ym",), counters=c)
         call()                                                  # warm-up (allocator, first-touch)
         e2e_steps = max(1, min(a.steps, 5))
         if world > 1:
@@ -745,7 +745,7 @@ def gpu_main(a):
                "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
                "tracks": a.e2e_tracks, "tracks_per_gpu": Be, "frames": T, "steps": e2e_steps, "numa_node": numa_node,
                "outputs": "ym = C ms (what every reference smoother consumes, multiview_pca_smoother.py:745,761-762)",
-               "api": f"eks_b200.batched.smooth_tracks (pinned host in/out, {a.e2e_block}-track blocks, 3 streams per GPU)",
+               "api": f"eks_b200.batched.smooth_tracks (pinned host in/out, {a.e2e_block or 'default-sized (~0.8 GB of input)'} track blocks, 3 streams per GPU)",
                "ms_per_step": 1e3 * step_s,
                "pcie": {"h2d_gbs_measured": pcie["h2d"], "d2h_gbs_measured": pcie["d2h"],
                         "h2d_gbs_in_run": h2d / step_s / 1e9, "d2h_gbs_in_run": d2h / step_s / 1e9,

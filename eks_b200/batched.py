@@ -87,7 +87,7 @@ class _DeviceLane:
         return dev.TrackParams(*sl, a_mode=self.a_mode)
 
 
-def smooth_tracks(y, ev, m0, S0, C, A, Q, *, dtype=torch.float64, device=None, devices=None, block_tracks=1024,
+def smooth_tracks(y, ev, m0, S0, C, A, Q, *, dtype=torch.float64, device=None, devices=None, block_tracks=None,
                   out=None, outputs=("ym",), counters=None, scan=None):
     """Kalman filter + RTS smoother for B independent tracks (A2 + A4 + A5 of SURVEY section 8a).
 
@@ -102,7 +102,9 @@ def smooth_tracks(y, ev, m0, S0, C, A, Q, *, dtype=torch.float64, device=None, d
     reference's LinAlgError].  Tracks with a non-positive ensemble variance are re-run through the literal
     p x p LU kernel (the information-form fast path divides by every variance; the reference does not).
     devices: list of CUDA device indices; the blocks of the batch are dealt out over them (contiguous shard per GPU),
-    all driven from this process.  scan: None = the library's routing (parallel-in-time kernels when a block has
+    all driven from this process.  block_tracks: tracks per streamed block; None = about 0.8 GB of input per block
+    (128 tracks at 100 000 frames, p = 4, f64: measured best on B200, the exposed head and tail of the copy pipeline
+    shrink with the block while the time-split kernels keep few-tile blocks on the roofline), at most 1024.  scan: None = the library's routing (parallel-in-time kernels when a block has
     too few tiles for the sequential ones), True / False = force.
     """
     if not torch.cuda.is_available():
@@ -141,6 +143,8 @@ def smooth_tracks(y, ev, m0, S0, C, A, Q, *, dtype=torch.float64, device=None, d
     dlist = dlist[:ndev]
     per_dev = (B + ndev - 1) // ndev
     per_dev = (per_dev + 31) // 32 * 32                       # shard boundaries on tile boundaries
+    if block_tracks is None:
+        block_tracks = min(1024, max(32, int(round(0.8e9 / (T * 2 * p * y.element_size()) / 32)) * 32))
     blk = max(32, (min(block_tracks, per_dev) + 31) // 32 * 32)
     want_yv = "yv" in outputs
     # forcing: scan=True routes through the library's workspace API with EKSB_ROUTE honoured there; scan=False = no workspace

@@ -357,7 +357,14 @@ template <typename T, int N, int P, int AM, bool OFF>
 __global__ void __launch_bounds__(kScanWarps* kLanes)
 scan_fwd_warm_kernel(const T* __restrict__ obs, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
                      int shared_mask, long B, long Tn, long L, long nc, const T* __restrict__ yoff,
-                     long* __restrict__ fcut, int* __restrict__ gate, T* __restrict__ filt) {
+                     long* __restrict__ fcut, int* __restrict__ gate, T* __restrict__ filt,
+                     const T* __restrict__ q_scale, T* __restrict__ finit, long kcap) {
+  // The time-split NLL sweep (eksb_nll_pipe.cuh) launches this with grid.y = candidate scales: Q is scaled by
+  // q_scale[blockIdx.y], cuts and gate are per candidate, and the start states go to finit[scale][tile][chunk]
+  // (there are no filtered records to put them in).  There kcap > 0 lets the warm-up run on past the chunk's end,
+  // up to kcap frames (a slowly forgetting candidate: K > L is fine, the chunk's own sum just starts later); a chunk
+  // that reaches the end of the track first gets K = "to the end" (it has nothing to sum) and only kcap frames
+  // without forgetting raise the gate.  The scan passes q_scale = finit = nullptr, kcap = 0, grid.y = 1.
   constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P;
   const int lane = threadIdx.x & 31;
   const long tiles = num_tiles_dev(B);
@@ -365,10 +372,20 @@ scan_fwd_warm_kernel(const T* __restrict__ obs, const T* __restrict__ C, const T
   if (w >= tiles * (nc - 1)) return;
   const long g = w / (nc - 1), c = w - g * (nc - 1) + 1;
   const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
+  const long sidx = blockIdx.y;
+  fcut += sidx * tiles * nc;
+  gate += sidx;
   Params<T, N, P, AM> prm;
   load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
+  if (q_scale) {
+    const T qs = q_scale[sidx];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) prm.Q[i] *= qs;
+  }
   const T* mu = OFF ? yoff + bp * P : nullptr;
-  const long t0 = c * L, n = ((c + 1) * L < Tn ? (c + 1) * L : Tn) - t0;
+  const long t0 = c * L;
+  long n = ((c + 1) * L < Tn ? (c + 1) * L : Tn) - t0;
+  if (kcap > 0) n = (Tn - t0 < kcap ? Tn - t0 : kcap) + 1;   // (+1: the loop below stops one frame short of n)
   const T* o = obs + ((g * Tn + t0) * R2) * kLanes + lane;
   T Phi[N][N], bb[N], Cc[NS];
 #pragma unroll
@@ -388,8 +405,10 @@ scan_fwd_warm_kernel(const T* __restrict__ obs, const T* __restrict__ C, const T
     T cur[R2], rec[Rec<N>::FWD];
 #pragma unroll
     for (int r = 0; r < R2; ++r) cur[r] = nxt[r];
+    if (t0 + t + 1 < Tn) {
 #pragma unroll
-    for (int r = 0; r < R2; ++r) nxt[r] = o[((t + 1) * R2 + r) * kLanes];
+      for (int r = 0; r < R2; ++r) nxt[r] = o[((t + 1) * R2 + r) * kLanes];
+    }
     if (OFF) {
 #pragma unroll
       for (int j = 0; j < P; ++j) cur[j] -= mu[j];
@@ -408,15 +427,22 @@ scan_fwd_warm_kernel(const T* __restrict__ obs, const T* __restrict__ C, const T
     }
   }
   if (dead) {                                               // (bb, Cc) is the exact filtered state of frame t0 + t - 1
-    T* f = filt + ((g * Tn + t0 + t - 1) * SG) * kLanes + lane;
+    T* f = finit ? finit + (((sidx * tiles + g) * nc + c) * SG) * kLanes + lane
+                 : filt + ((g * Tn + t0 + t - 1) * SG) * kLanes + lane;
 #pragma unroll
     for (int i = 0; i < N; ++i) f[i * kLanes] = bb[i];
 #pragma unroll
     for (int i = 0; i < NS; ++i) f[(N + i) * kLanes] = Cc[i];
   }
   if (lane == 0) {
-    fcut[g * nc + c] = dead ? t : n;
-    if (!dead) atomicOr(gate, 1);
+    if (kcap > 0) {
+      const bool ran_out = !dead && (t0 + t >= Tn);        // the track ended first: nothing left for this chunk to sum
+      fcut[g * nc + c] = dead ? t : Tn - t0;
+      if (!dead && !ran_out) atomicOr(gate, 1);
+    } else {
+      fcut[g * nc + c] = dead ? t : n;
+      if (!dead) atomicOr(gate, 1);
+    }
   }
 }
 

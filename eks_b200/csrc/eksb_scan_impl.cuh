@@ -90,7 +90,7 @@ static int scan_run_fwd_off(const T* obs, const T* yoff, const T* m0, const T* S
   if (scan_v2_enabled()) {
     // time-split pipelined scan: K warm-up frames per chunk, then every (tile, chunk) is a tile of the TMA-fed kernel
     gate = w.alive + 2;
-    scan_fwd_warm_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, w.fcut, w.alive + 2, filt);
+    scan_fwd_warm_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, w.fcut, w.alive + 2, filt, (const T*)nullptr, (T*)nullptr, 0L);
     int rc = check_launch("scan forward warm-up");
     if (rc != EKSB_OK) return rc;
     VTiles vt;

@@ -313,6 +313,40 @@ def kf_forward(obs, prm: TrackParams, B, T, first=_lib.FIRST_PRIOR_UPDATE, q_sca
     return filt, nll, status
 
 
+def nll_workspace(B, T, n, p, n_scale, dtype, device):
+    """Workspace tensor for kf_nll (None when the plain launch is the route for this shape)."""
+    nbytes = lib().eksb_nll_workspace_bytes(B, T, n, p, int(n_scale), torch.empty(0, dtype=dtype).element_size())
+    return torch.empty(nbytes, dtype=torch.uint8, device=device) if nbytes else None
+
+
+def kf_nll(obs, prm: TrackParams, B, T, q_scale=None, first=_lib.FIRST_PRIOR_UPDATE, y_offset=None, status=None,
+           workspace="auto"):
+    """A8: innovation NLL of the forward filter per track and per candidate q_scale[g] * Q -> (nll (max(G,1), B)
+    float64, status (B,) int32).  No state records.  workspace: "auto" allocates what eksb_nll_workspace_bytes asks
+    for (few tiles + long tracks run time-split, include/eksb.h), a nll_workspace(...) tensor reuses one across calls
+    (an optimiser's loop), None forces the plain launch."""
+    _need_cuda(obs, "obs")
+    dev, dt = obs.device, obs.dtype
+    if prm.dtype != dt:
+        raise TypeError("obs and params dtypes differ")
+    n_scale = 0 if q_scale is None else int(q_scale.numel())
+    if q_scale is not None and (q_scale.dtype != dt or not q_scale.is_contiguous()):
+        raise ValueError("q_scale must be a contiguous tensor of the obs dtype")
+    if y_offset is not None and (y_offset.dtype != dt or tuple(y_offset.shape) != (B, prm.p) or not y_offset.is_contiguous()):
+        raise ValueError("y_offset must be a contiguous (B,p) tensor of the obs dtype")
+    nll = torch.empty((max(n_scale, 1), B), dtype=torch.float64, device=dev)
+    if status is None:
+        status = torch.zeros(B, dtype=torch.int32, device=dev)
+    if isinstance(workspace, str):
+        workspace = nll_workspace(B, T, prm.n, prm.p, n_scale, dt, dev)
+    fn = getattr(lib(), f"eksb_kf_nll_ws_{_sfx(dt)}")
+    check(fn(_ptr(obs), _ptr(y_offset), _ptr(prm.m0), _ptr(prm.S0), _ptr(prm.C), _ptr(prm.A), _ptr(prm.Q),
+             prm.shared_mask, B, T, prm.n, prm.p, prm.a_mode, first, _ptr(q_scale), n_scale, _ptr(nll), _ptr(status),
+             _ptr(workspace), 0 if workspace is None else workspace.numel() * workspace.element_size(), _stream(dev)),
+          "eksb_kf_nll_ws")
+    return nll, status
+
+
 def kf_forward_generic(obs, prm: TrackParams, B, T, R=None, first=_lib.FIRST_PRIOR_UPDATE, status=None):
     """Literal-arithmetic forward filter (dense R (p,p)/(B,p,p), any n<=8, p<=16).  Returns (filt, status)."""
     _need_cuda(obs, "obs")

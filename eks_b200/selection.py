@@ -36,7 +36,7 @@ def allreduce_sum_(vec):
 def nll_grid(obs, prm, B, T, s_grid):
     """(n_grid,B) float64 NLL of every local track for Q = s*prm.Q, one launch (grid.y = n_grid)."""
     q = torch.as_tensor(np.asarray(s_grid, dtype=np.float64), dtype=obs.dtype).to(obs.device)
-    _, nll, status = dev.kf_forward(obs, prm, B, T, q_scale=q, want_filt=False, want_nll=True)
+    nll, status = dev.kf_nll(obs, prm, B, T, q_scale=q)     # time-split when the batch has few tiles and long tracks
     return nll, status
 
 

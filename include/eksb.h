@@ -347,6 +347,27 @@ EKSB_API int eksb_rts_backward_ws_f32(const float* filt, const float* C, const f
                           long B, long T, int n, int p, int a_mode, float* smth, float* ym, float* yv, float* cv,
                           int* status, float* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- A8: NLL sweep with a workspace (time-split for few tiles and long tracks) ------------------------------
+ * The innovation NLL of filtering_pass (eks/ensemble_kalman.py:98-112) per trial smoothing parameter: the objective
+ * of the grid search / an optimiser over `s` that replaces the hand-set CLI flag of
+ * scripts/multicam_example.py:38-43 (the reference itself has no such search).  Same contract as the nll output of eksb_kf_forward (q_scale / n_scale candidates
+ * of q_scale[g]*Q, y_offset optional, first-frame mode), no state records.  With a caller-owned workspace of
+ * eksb_nll_workspace_bytes(...) bytes (0: the plain launch is the route, workspace may be NULL) a batch that leaves the
+ * plain kernel with fewer CTAs than ~2 per SM is cut in time as in eksb_kf_rts_scan: a warm-up kernel per candidate
+ * finds where each chunk has forgotten its start, CTA (tile, chunk) sums the terms of its frames, the chunks are
+ * added in order (deterministic).  One keypoint x 100 000 frames: one chain warp for the whole track otherwise.
+ * Candidates whose filter never forgets inside a chunk (tiny process noise) are evaluated whole by a second launch
+ * behind a device flag.  Same values up to rounding (tests: 1e-10).  Dense A / other shapes: the sequential kernels. */
+EKSB_API size_t eksb_nll_workspace_bytes(long B, long T, int n, int p, int n_scale, int elem_size);
+EKSB_API int eksb_kf_nll_ws_f64(const double* obs, const double* y_offset, const double* m0, const double* S0,
+                        const double* C, const double* A, const double* Q, int shared_mask, long B, long T, int n, int p,
+                        int a_mode, int first, const double* q_scale, int n_scale, double* nll, int* status,
+                        void* workspace, size_t workspace_bytes, void* stream);
+EKSB_API int eksb_kf_nll_ws_f32(const float* obs, const float* y_offset, const float* m0, const float* S0,
+                        const float* C, const float* A, const float* Q, int shared_mask, long B, long T, int n, int p,
+                        int a_mode, int first, const float* q_scale, int n_scale, double* nll, int* status,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- no-allocation variant of the parallel-in-time scan -------------------------------------------------------
  * No counterpart in the reference: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs
