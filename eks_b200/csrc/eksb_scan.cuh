@@ -396,34 +396,45 @@ scan_fwd_warm_kernel(const T* __restrict__ obs, const T* __restrict__ C, const T
   }
 #pragma unroll
   for (int i = 0; i < NS; ++i) Cc[i] = T(0);
-  T nxt[R2];
+  // One warp per chunk and a dependent recursion: the frames come through a register ring PF deep (a single frame of
+  // look-ahead left most of a global-load latency exposed in every step: ~1 us per frame).
+  constexpr int PF = (R2 * (int)sizeof(T) <= 64) ? 4 : 2;
+  T ring[PF][R2];
 #pragma unroll
-  for (int r = 0; r < R2; ++r) nxt[r] = o[r * kLanes];
+  for (int u = 0; u < PF; ++u)
+    if (t0 + u < Tn) {
+#pragma unroll
+      for (int r = 0; r < R2; ++r) ring[u][r] = o[(u * R2 + r) * kLanes];
+    }
   bool ok = true, dead = false;
   long t = 0;
-  while (t < n - 1) {                                       // the cut must leave the chunk at least one frame
-    T cur[R2], rec[Rec<N>::FWD];
+  while (t < n - 1 && !dead) {                              // the cut must leave the chunk at least one frame
 #pragma unroll
-    for (int r = 0; r < R2; ++r) cur[r] = nxt[r];
-    if (t0 + t + 1 < Tn) {
+    for (int u = 0; u < PF; ++u) {
+      if (t >= n - 1 || dead) break;
+      T cur[R2], rec[Rec<N>::FWD];
 #pragma unroll
-      for (int r = 0; r < R2; ++r) nxt[r] = o[((t + 1) * R2 + r) * kLanes];
-    }
-    if (OFF) {
+      for (int r = 0; r < R2; ++r) cur[r] = ring[u][r];
+      if (t0 + t + PF < Tn) {
 #pragma unroll
-      for (int j = 0; j < P; ++j) cur[j] -= mu[j];
-    }
-    fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
-    fwd_phi_step<T, N, P, AM>(prm, rec, Phi, bb, Cc, ok);
-    ++t;
-    if ((t & 15) == 0) {
-      T mx = T(0);
-#pragma unroll
-      for (int i = 0; i < N; ++i) {
-#pragma unroll
-        for (int j = 0; j < N; ++j) mx = fmax(mx, fabs(Phi[i][j]));
+        for (int r = 0; r < R2; ++r) ring[u][r] = o[((t + PF) * R2 + r) * kLanes];
       }
-      if (__all_sync(0xffffffffu, mx < ScanCut<T>::value)) { dead = true; break; }
+      if (OFF) {
+#pragma unroll
+        for (int j = 0; j < P; ++j) cur[j] -= mu[j];
+      }
+      fwd_prep<T, N, P, AM>(prm, cur, cur + P, rec);
+      fwd_phi_step<T, N, P, AM>(prm, rec, Phi, bb, Cc, ok);
+      ++t;
+      if ((t & 15) == 0) {
+        T mx = T(0);
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+#pragma unroll
+          for (int j = 0; j < N; ++j) mx = fmax(mx, fabs(Phi[i][j]));
+        }
+        if (__all_sync(0xffffffffu, mx < ScanCut<T>::value)) dead = true;
+      }
     }
   }
   if (dead) {                                               // (bb, Cc) is the exact filtered state of frame t0 + t - 1
@@ -466,26 +477,37 @@ scan_bwd_warm_kernel(const T* __restrict__ filt, const T* __restrict__ C, const 
   for (int i = 0; i < SR; ++i) acc[i] = T(0);
 #pragma unroll
   for (int i = 0; i < N; ++i) acc[i * N + i] = T(1);
-  T nxt[SG];
+  constexpr int PF = (SG * (int)sizeof(T) <= 72) ? 4 : 2;    // register ring of records, as in the forward warm-up
+  T ring[PF][SG];
 #pragma unroll
-  for (int r = 0; r < SG; ++r) nxt[r] = f[((L - 1) * SG + r) * kLanes];
+  for (int u = 0; u < PF; ++u)
+    if (L - 1 - u >= 0) {
+#pragma unroll
+      for (int r = 0; r < SG; ++r) ring[u][r] = f[((L - 1 - u) * SG + r) * kLanes];
+    }
   bool ok = true, dead = false;
   long done = 0;
-  while (done < L - 2) {                                     // leave the virtual tile below at least one frame of its own
-    T cur[SG], rec[Rec<N>::BWD];
+  while (done < L - 2 && !dead) {                            // leave the virtual tile below at least one frame of its own
 #pragma unroll
-    for (int r = 0; r < SG; ++r) cur[r] = nxt[r];
-    const long tn = L - 2 - done;                            // next frame down (>= 0 inside the loop)
+    for (int u = 0; u < PF; ++u) {
+      if (done >= L - 2 || dead) break;
+      T cur[SG], rec[Rec<N>::BWD];
 #pragma unroll
-    for (int r = 0; r < SG; ++r) nxt[r] = f[(tn * SG + r) * kLanes];
-    bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
-    bwd_summary_step<T, N>(rec, acc);
-    ++done;
-    if ((done & 15) == 0) {
-      T mx = T(0);
+      for (int r = 0; r < SG; ++r) cur[r] = ring[u][r];     // frame L - 1 - done
+      const long tn = L - 1 - done - PF;                     // the frame that takes its slot
+      if (tn >= 0) {
 #pragma unroll
-      for (int i = 0; i < N * N; ++i) mx = fmax(mx, fabs(acc[i]));
-      if (__all_sync(0xffffffffu, mx < ScanCut<T>::value)) { dead = true; break; }
+        for (int r = 0; r < SG; ++r) ring[u][r] = f[(tn * SG + r) * kLanes];
+      }
+      bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
+      bwd_summary_step<T, N>(rec, acc);
+      ++done;
+      if ((done & 15) == 0) {
+        T mx = T(0);
+#pragma unroll
+        for (int i = 0; i < N * N; ++i) mx = fmax(mx, fabs(acc[i]));
+        if (__all_sync(0xffffffffu, mx < ScanCut<T>::value)) dead = true;
+      }
     }
   }
   if (dead) {                                               // (g, L) of the element = smoothed (ms, Vs) of frame (c+1) L - done
