@@ -458,6 +458,13 @@ def gpu_main(a):
                  "tracks": Bs_setup, "ms": sms, "keypoint_frames_per_s": tfs / (sms * 1e-3),
                  "achieved_gbs": tfs * sb / (sms * 1e-3) / 1e9, "frac": tfs * sb / (sms * 1e-3) / 1e9 / peak,
                  "failed_tracks": int(st_setup.sum())}
+        try:                                                       # committed ncu capture of one call of this shape (tools/gpu_ncu_r2.sh)
+            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("pca_setup_" + a.dtype)
+            if tr and tr["algorithmic"] == tfs * sb:
+                setup["dram_bytes_ncu"] = tr["core_dram_bytes"]
+                setup["dram_bytes_over_algorithmic"] = tr["core_dram_bytes"] / (tfs * sb)
+        except Exception:
+            pass
         launches += 48
         del prm_s, ws_setup, mx_all
         torch.cuda.empty_cache()

@@ -45,6 +45,53 @@ traffic = {"_source": f"profiles/{tag}_dram_bytes_full_size.csv: ncu --metrics d
                                               "read": int(mean("fwd", "dram__bytes_read.sum")), "write": int(mean("fwd", "dram__bytes_write.sum")),
                                               "algorithmic": tf * 136, "ncu_duration_ms": mean("fwd", "gpu__time_duration.sum") / 1e6}}}
 
+# ---- (2b) f32: one launch per pass covers the whole 16 384-track batch
+f32_csv = os.path.join(G, "dram_full_f32.csv")
+if os.path.exists(f32_csv):
+    shutil.copy(f32_csv, os.path.join(P, f"{tag}_dram_bytes_full_size_f32.csv"))
+    try:
+        b32 = json.loads(open(os.path.join(P, f"{tag}_bench_f32.json")).read().strip().splitlines()[-1])
+        G32 = b32["config"]["group_tracks"]
+    except Exception:
+        G32 = 16384
+    h, rows = table(f32_csv)
+    kn, mn, mv = h.index("Kernel Name"), h.index("Metric Name"), h.index("Metric Value")
+    acc = collections.defaultdict(lambda: collections.defaultdict(list))
+    for r in rows:
+        if len(r) > mv:
+            acc["fwd" if "kf_forward" in r[kn] else "bwd"][r[mn]].append(float(r[mv].replace(",", "")))
+    tf32 = G32 * T
+    traffic["f32"] = {"_source": f"profiles/{tag}_dram_bytes_full_size_f32.csv (same command with --dtype f32, {G32}-track launches)",
+                      "kernel": "rts_backward_pipe_kernel", "launch_tracks": G32,
+                      "dram_bytes": int(mean("bwd", "dram__bytes_read.sum") + mean("bwd", "dram__bytes_write.sum")),
+                      "read": int(mean("bwd", "dram__bytes_read.sum")), "write": int(mean("bwd", "dram__bytes_write.sum")),
+                      "algorithmic": tf32 * 88, "ncu_duration_ms": mean("bwd", "gpu__time_duration.sum") / 1e6,
+                      "kf_forward_pipe_kernel": {"dram_bytes": int(mean("fwd", "dram__bytes_read.sum") + mean("fwd", "dram__bytes_write.sum")),
+                                                 "algorithmic": tf32 * 68, "ncu_duration_ms": mean("fwd", "gpu__time_duration.sum") / 1e6}}
+
+# ---- (2c) pca_setup: every kernel of one call (wide-digit select, the default), tools/setup_time.py bench
+setup_csv = os.path.join(G, "dram_setup.csv")
+if os.path.exists(setup_csv):
+    shutil.copy(setup_csv, os.path.join(P, f"{tag}_dram_bytes_setup.csv"))
+    h, rows = table(setup_csv)
+    kn, mn, mv, idc = h.index("Kernel Name"), h.index("Metric Name"), h.index("Metric Value"), h.index("ID")
+    per = collections.OrderedDict()
+    for r in rows:
+        if len(r) > mv:
+            per.setdefault(r[idc], {"name": short(r[kn])})[r[mn]] = float(r[mv].replace(",", ""))
+    ls = list(per.values())
+    starts = [i for i, l in enumerate(ls) if l["name"].startswith("setup_init_state_kernel")]
+    call = ls[starts[2]:starts[3]]                          # third call of the wide path (the first two warm up)
+    core = [l for l in call if not l["name"].startswith(("setup_mx_kernel", "center_rows_kernel"))]
+    byt = lambda l: l.get("dram__bytes_read.sum", 0) + l.get("dram__bytes_write.sum", 0)
+    traffic["pca_setup_f64"] = {"_source": f"profiles/{tag}_dram_bytes_setup.csv: one eksb_pca_setup call, 8192 tracks x 100000 frames (tools/setup_time.py bench); "
+                                           "'core' = without setup_mx_kernel / center_rows_kernel, which the bench's pipeline does not run (max_vars from the ensemble "
+                                           "kernel, centring fused into the forward filter)",
+                                "core_dram_bytes": int(sum(byt(l) for l in core)), "core_ms": sum(l.get("gpu__time_duration.sum", 0) for l in core) / 1e6,
+                                "algorithmic": 8192 * 100000 * 40,
+                                "kernels": [{"kernel": l["name"][:50], "ms": l.get("gpu__time_duration.sum", 0) / 1e6, "dram_bytes": int(byt(l))}
+                                            for l in call if l.get("gpu__time_duration.sum", 0) > 50e3]}
+
 # ---- (3) configs[4]: all kernels of one routed forward + backward call (the LAST complete call in the capture)
 h, rows = table(os.path.join(G, "dram_c5.csv"))
 kn, mn, mv, idc = h.index("Kernel Name"), h.index("Metric Name"), h.index("Metric Value"), h.index("ID")
