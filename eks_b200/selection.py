@@ -58,6 +58,40 @@ def select_smooth_param(obs, prm, B, T, s_grid):
     return float(np.asarray(s_grid)[int(np.argmin(tot_h))]), tot_h
 
 
+def refine_smooth_param(obs, prm, B, T, lo, hi, iters=24, candidates=2):
+    """Golden-section search of the summed NLL over log s in [lo, hi] (the same objective and the same one
+    all-reduce per evaluation as select_smooth_param; every rank takes the same steps).  Each step evaluates
+    `candidates` = 2 interior points in one launch, through eksb_kf_nll_ws with ONE workspace kept for the whole
+    search: for a few keypoints x a long video an evaluation is time-split (include/eksb.h) -- 1.3 ms instead of
+    20.7 ms for one keypoint x 100 000 frames.  Returns (best_s, evaluations [(s, nll)], ...)."""
+    assert candidates == 2
+    phi = (np.sqrt(5.0) - 1.0) / 2.0
+    a, b = np.log(lo), np.log(hi)
+    ws = dev.nll_workspace(B, T, prm.n, prm.p, 2, obs.dtype, obs.device)
+    hist = []
+
+    def both(x1, x2):
+        q = torch.as_tensor(np.exp([x1, x2]), dtype=obs.dtype).to(obs.device)
+        nll, _ = dev.kf_nll(obs, prm, B, T, q_scale=q, workspace=ws)
+        tot = allreduce_sum_(nll_sums(nll)).cpu().numpy()
+        hist.extend([(float(np.exp(x1)), float(tot[0])), (float(np.exp(x2)), float(tot[1]))])
+        return float(tot[0]), float(tot[1])
+
+    x1, x2 = b - phi * (b - a), a + phi * (b - a)
+    f1, f2 = both(x1, x2)
+    for _ in range(iters):
+        if f1 <= f2:
+            b, x2, f2 = x2, x1, f1
+            x1 = b - phi * (b - a)
+        else:
+            a, x1, f1 = x1, x2, f2
+            x2 = a + phi * (b - a)
+        # (one of the two is a re-evaluation: it keeps the launch shape -- and the workspace -- fixed)
+        f1, f2 = both(x1, x2)
+    best = min(hist, key=lambda e: e[1])
+    return best[0], hist
+
+
 def zscore(obs, smth, prm, B, T, add_ev=True):
     """p-row records of z = (y - C ms)/sqrt(diag(C Vs C^T) [+ ev])."""
     z = dev.alloc_records(B, T, prm.p, obs.dtype, obs.device)
