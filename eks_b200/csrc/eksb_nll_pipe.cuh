@@ -358,13 +358,26 @@ static int launch_nll_split(const T* obs, const T* m0, const T* S0, const T* C, 
   cudaMemsetAsync(gate, 0, (size_t)ns * sizeof(int), st);
   cudaMemsetAsync(sp.part, 0, (size_t)ns * tiles * nc * kLanes * sizeof(double), st);   // (a chunk with nothing to sum writes nothing)
   const long kcap = 4 * L;                                 // warm-up frames before a candidate is given up (evaluated whole)
-  dim3 wgrid((unsigned)((tiles * (nc - 1) + kScanWarps - 1) / kScanWarps), (unsigned)ns);
-  if (yoff)
-    scan_fwd_warm_kernel<T, N, P, 0, true><<<wgrid, kScanWarps * kLanes, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, fcut, gate,
-                                                                                  (T*)nullptr, q_scale, finit, kcap);
-  else
-    scan_fwd_warm_kernel<T, N, P, 0, false><<<wgrid, kScanWarps * kLanes, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, fcut, gate,
-                                                                                   (T*)nullptr, q_scale, finit, kcap);
+  const char* w1 = getenv("EKSB_SCAN_WARM1");              // A/B switch: the one-warp warm-up kernel
+  if ((w1 && w1[0] == '1') || sizeof(T) != 8) {            // (float: see scan_run_fwd_off)
+    dim3 wgrid((unsigned)((tiles * (nc - 1) + kScanWarps - 1) / kScanWarps), (unsigned)ns);
+    if (yoff)
+      scan_fwd_warm_kernel<T, N, P, 0, true><<<wgrid, kScanWarps * kLanes, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, fcut, gate,
+                                                                                    (T*)nullptr, q_scale, finit, kcap);
+    else
+      scan_fwd_warm_kernel<T, N, P, 0, false><<<wgrid, kScanWarps * kLanes, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, fcut, gate,
+                                                                                     (T*)nullptr, q_scale, finit, kcap);
+  } else {
+    dim3 wgrid((unsigned)(tiles * (nc - 1)), (unsigned)ns);  // three-role warm-up: one CTA per (tile, chunk) and candidate
+    constexpr size_t wsm = Warm3Smem<T, N>::kTotal;
+    if (yoff) {
+      cudaFuncSetAttribute(scan_fwd_warm3_kernel<T, N, P, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm);
+      scan_fwd_warm3_kernel<T, N, P, true><<<wgrid, 3 * kLanes, wsm, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, fcut, gate, (T*)nullptr, q_scale, finit, kcap);
+    } else {
+      cudaFuncSetAttribute(scan_fwd_warm3_kernel<T, N, P, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm);
+      scan_fwd_warm3_kernel<T, N, P, false><<<wgrid, 3 * kLanes, wsm, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, fcut, gate, (T*)nullptr, q_scale, finit, kcap);
+    }
+  }
   int rc = launch_nll_pipe<T, N, P>(obs, m0, S0, C, A, Q, mask, B, Tn, first, q_scale, n_scale, nll, status, yoff, st, sp);
   if (rc != EKSB_OK) return rc;
   const long items = (long)ns * B;

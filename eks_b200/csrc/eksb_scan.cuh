@@ -457,6 +457,209 @@ scan_fwd_warm_kernel(const T* __restrict__ obs, const T* __restrict__ C, const T
   }
 }
 
+// The forward warm-up in three roles (diagonal A, N <= 3: the scaled chain of eksb_math.cuh).  A warp's FP64 instruction
+// takes its scheduler's pipe for ~4 cycles, so the one-warp kernel above runs at its instruction count: ~200 per frame,
+// 0.8 us -- 1.6 ms for the K ~ 2 000 frames of a bench chunk, with most of the GPU idle.  Here one CTA owns a chunk and
+// three warps on three schedulers split the frame: the helper turns obs frames into the state-independent record
+// (Lam, iv) (~52), the chain warp runs the filter recursion in its scaled form (~90) and publishes (Nm, adj S,
+// 1 / det Lt), from which the third warp forms the gain G = Nm adj(S) / det(Lt) and the sensitivity product
+// Phi <- G A Phi (~72) and tests it.  Batches of kWarmF frames, double-buffered in shared memory, one CTA barrier per
+// batch: helper on batch i, chain on i - 1, phi on i - 2.  Same contract (fcut, gate, record of frame c L + K - 1,
+// q_scale / finit / kcap of the NLL sweep); K is a multiple of kWarmF instead of 16.
+constexpr int kWarmF = 4;
+template <typename T, int N> struct Warm3Smem {
+  static constexpr size_t kTotal = sizeof(T) * kLanes * (2 * kWarmF * (Rec<N>::FWD + 2 * Dim<N>::NS + 1) + 2 * Dim<N>::SIGMA);
+};
+template <typename T, int N, int P, bool OFF>
+__global__ void __launch_bounds__(3 * kLanes)
+scan_fwd_warm3_kernel(const T* __restrict__ obs, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
+                      int shared_mask, long B, long Tn, long L, long nc, const T* __restrict__ yoff,
+                      long* __restrict__ fcut, int* __restrict__ gate, T* __restrict__ filt,
+                      const T* __restrict__ q_scale, T* __restrict__ finit, long kcap) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, R2 = 2 * P, REC = Rec<N>::FWD, F = kWarmF, GR = 2 * NS + 1;
+  extern __shared__ __align__(16) unsigned char warm_smem[];       // Warm3Smem<T, N>::kTotal bytes (50 KB for f64, n = 3)
+  typedef T (*RecB)[F][REC][kLanes];
+  typedef T (*GBuf)[F][GR][kLanes];
+  typedef T (*SBuf)[SG][kLanes];
+  RecB recb = reinterpret_cast<RecB>(warm_smem);
+  GBuf gbuf = reinterpret_cast<GBuf>(warm_smem + sizeof(T) * 2 * F * REC * kLanes);
+  SBuf sbuf = reinterpret_cast<SBuf>(warm_smem + sizeof(T) * 2 * F * (REC + GR) * kLanes);
+  __shared__ int stop;
+  const int lane = threadIdx.x & 31, role = threadIdx.x >> 5;      // 0 helper, 1 chain, 2 phi
+  const long tiles = num_tiles_dev(B);
+  const long w = blockIdx.x;                                        // (tile, chunk >= 1)
+  const long g = w / (nc - 1), c = w - g * (nc - 1) + 1;
+  const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
+  const long sidx = blockIdx.y;
+  fcut += sidx * tiles * nc;
+  gate += sidx;
+  Params<T, N, P, 0> prm;
+  load_track_params<T, N, P, 0>(prm, C, A, Q, shared_mask, bp);
+  if (q_scale) {
+    const T qs = q_scale[sidx];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) prm.Q[i] *= qs;
+  }
+  const long t0 = c * L;
+  const long clen = ((c + 1) * L < Tn ? (c + 1) * L : Tn) - t0;
+  const long steps = kcap > 0 ? (Tn - t0 < kcap ? Tn - t0 : kcap) : clen - 1;   // frames the recursion may take
+  const long nb = (steps + F - 1) / F;
+  if (threadIdx.x == 0) stop = 0;
+  // helper state
+  const T* o = obs + ((g * Tn + t0) * R2) * kLanes + lane;
+  constexpr bool kOuter = (P * NS <= 36);
+  T CC[kOuter ? P : 1][NS];
+  T mu[P];
+  T raw[F][R2];
+  if (role == 0) {
+    if constexpr (kOuter) make_outer<T, N, P>(prm.C, CC);
+#pragma unroll
+    for (int j = 0; j < P; ++j) mu[j] = OFF ? yoff[bp * P + j] : T(0);
+#pragma unroll
+    for (int j = 0; j < F; ++j)
+      if (j < steps) {
+#pragma unroll
+        for (int r = 0; r < R2; ++r) raw[j][r] = o[(j * R2 + r) * kLanes];
+      }
+  }
+  // chain state: (m, V = Nm r) started at (0, 0)
+  T m[N], Nm[NS], rr = T(1);
+#pragma unroll
+  for (int i = 0; i < N; ++i) m[i] = T(0);
+#pragma unroll
+  for (int i = 0; i < NS; ++i) Nm[i] = T(0);
+  // phi state
+  T Phi[N][N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) Phi[i][j] = (i == j) ? T(1) : T(0);
+  }
+  bool dead = false;
+  for (long i = 0; i < nb + 2; ++i) {
+    __syncthreads();
+    if (stop) break;
+    if (role == 0) {
+      if (i < nb) {
+#pragma unroll
+        for (int j = 0; j < F; ++j) {
+          if (i * F + j < steps) {
+            T cur[R2], rec[REC];
+#pragma unroll
+            for (int r = 0; r < R2; ++r) cur[r] = raw[j][r];
+            if (OFF) {
+#pragma unroll
+              for (int q = 0; q < P; ++q) cur[q] -= mu[q];
+            }
+            if constexpr (kOuter) fwd_prep_outer<T, N, P>(prm.C, CC, cur, cur + P, rec);
+            else fwd_prep<T, N, P, 0>(prm, cur, cur + P, rec);
+#pragma unroll
+            for (int r = 0; r < REC; ++r) recb[i & 1][j][r][lane] = rec[r];
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < F; ++j) {                       // the next batch's frames: in flight across the barrier
+          const long t = (i + 1) * F + j;
+          if (t < steps) {
+#pragma unroll
+            for (int r = 0; r < R2; ++r) raw[j][r] = o[(t * R2 + r) * kLanes];
+          }
+        }
+      }
+    } else if (role == 1) {
+      if (i >= 1 && i <= nb) {
+        const long k = i - 1;
+#pragma unroll
+        for (int j = 0; j < F; ++j) {
+          if (k * F + j < steps) {
+            T rec[REC], S[NS], adjS[NS], Lt[NS], detS, detL, Vout[NS];
+#pragma unroll
+            for (int r = 0; r < REC; ++r) rec[r] = recb[k & 1][j][r][lane];
+#pragma unroll
+            for (int q = 0; q < NS; ++q) S[q] = (prm.AA[q] * Nm[q]) * rr + prm.Q[q];
+            sym_adjugate<T, N>(S, adjS, detS);
+#pragma unroll
+            for (int q = 0; q < NS; ++q) Lt[q] = detS * rec[q] + adjS[q];
+            sym_adjugate<T, N>(Lt, Nm, detL);
+            const T rcpL = rcp_chain(detL);
+            rr = detS * rcpL;
+            fwd_mean_scaled<T, N, P>(prm, rec, true, Nm, rr, m, Vout);
+#pragma unroll
+            for (int q = 0; q < NS; ++q) { gbuf[k & 1][j][q][lane] = Nm[q]; gbuf[k & 1][j][NS + q][lane] = adjS[q]; }
+            gbuf[k & 1][j][2 * NS][lane] = rcpL;
+            if (j == F - 1 || k * F + j == steps - 1) {      // the batch's last frame: the state a cut here would record
+#pragma unroll
+              for (int q = 0; q < N; ++q) sbuf[k & 1][q][lane] = m[q];
+#pragma unroll
+              for (int q = 0; q < NS; ++q) sbuf[k & 1][N + q][lane] = Vout[q];
+            }
+          }
+        }
+      }
+    } else {
+      if (i >= 2) {
+        const long k = i - 2;
+#pragma unroll
+        for (int j = 0; j < F; ++j) {
+          if (k * F + j < steps) {
+            T nm[NS], aS[NS], T1[N][N];
+#pragma unroll
+            for (int q = 0; q < NS; ++q) { nm[q] = gbuf[k & 1][j][q][lane]; aS[q] = gbuf[k & 1][j][NS + q][lane]; }
+            const T rcpL = gbuf[k & 1][j][2 * NS][lane];
+#pragma unroll
+            for (int a = 0; a < N; ++a) {
+#pragma unroll
+              for (int d = 0; d < N; ++d) {
+                T acc = T(0);
+#pragma unroll
+                for (int q = 0; q < N; ++q) acc += aS[sym_idx<N>(a, q)] * (prm.A[q] * Phi[q][d]);
+                T1[a][d] = acc;
+              }
+            }
+#pragma unroll
+            for (int a = 0; a < N; ++a) {
+#pragma unroll
+              for (int d = 0; d < N; ++d) {
+                T acc = T(0);
+#pragma unroll
+                for (int q = 0; q < N; ++q) acc += nm[sym_idx<N>(a, q)] * T1[q][d];
+                Phi[a][d] = acc * rcpL;
+              }
+            }
+          }
+        }
+        T mx = T(0);
+#pragma unroll
+        for (int a = 0; a < N; ++a) {
+#pragma unroll
+          for (int d = 0; d < N; ++d) mx = fmax(mx, fabs(Phi[a][d]));
+        }
+        const long done = (k + 1) * F < steps ? (k + 1) * F : steps;      // frames the recursion has taken
+        // (a cut needs a frame of the chunk left for the tile that starts there: done <= clen - 1 when kcap == 0 by
+        // the choice of `steps`; with kcap the chunk's own sum may be empty)
+        if (__all_sync(0xffffffffu, mx < ScanCut<T>::value)) {
+          dead = true;
+          T* f = finit ? finit + (((sidx * tiles + g) * nc + c) * SG) * kLanes + lane
+                       : filt + ((g * Tn + t0 + done - 1) * SG) * kLanes + lane;
+#pragma unroll
+          for (int q = 0; q < SG; ++q) f[q * kLanes] = sbuf[k & 1][q][lane];
+          if (lane == 0) { fcut[g * nc + c] = done; stop = 1; }
+        }
+      }
+    }
+  }
+  if (role == 2 && !dead && lane == 0) {
+    if (kcap > 0) {
+      const bool ran_out = (t0 + steps >= Tn);               // the track ended first: nothing left for this chunk to sum
+      fcut[g * nc + c] = Tn - t0;
+      if (!ran_out) atomicOr(gate, 1);
+    } else {
+      fcut[g * nc + c] = clen;
+      atomicOr(gate, 1);
+    }
+  }
+}
+
 template <typename T, int N, int P, int AM>
 __global__ void __launch_bounds__(kScanWarps* kLanes)
 scan_bwd_warm_kernel(const T* __restrict__ filt, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,

@@ -90,7 +90,18 @@ static int scan_run_fwd_off(const T* obs, const T* yoff, const T* m0, const T* S
   if (scan_v2_enabled()) {
     // time-split pipelined scan: K warm-up frames per chunk, then every (tile, chunk) is a tile of the TMA-fed kernel
     gate = w.alive + 2;
-    scan_fwd_warm_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, w.fcut, w.alive + 2, filt, (const T*)nullptr, (T*)nullptr, 0L);
+    // three-role warm-up: double only (its scaled chain forms det(adj S + det S Lam) ~ (var)^6: below the float range
+    // for process noise ~1e-7 -- the main kernels' chain has the same limit, but a warm-up has no fallback of its own)
+    if constexpr (AM == 0 && N <= 3 && sizeof(T) == 8) {
+      if (scan_env_long("EKSB_SCAN_WARM1", 0))             // A/B switch: the one-warp warm-up kernel
+        scan_fwd_warm_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, w.fcut, w.alive + 2, filt, (const T*)nullptr, (T*)nullptr, 0L);
+      else {
+        cudaFuncSetAttribute(scan_fwd_warm3_kernel<T, N, P, OFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Warm3Smem<T, N>::kTotal);
+        scan_fwd_warm3_kernel<T, N, P, OFF><<<(unsigned)(tiles * (nc - 1)), 3 * kLanes, Warm3Smem<T, N>::kTotal, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, w.fcut, w.alive + 2, filt, (const T*)nullptr, (T*)nullptr, 0L);
+      }
+    } else {
+      scan_fwd_warm_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, w.fcut, w.alive + 2, filt, (const T*)nullptr, (T*)nullptr, 0L);
+    }
     int rc = check_launch("scan forward warm-up");
     if (rc != EKSB_OK) return rc;
     VTiles vt;
