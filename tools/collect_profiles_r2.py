@@ -103,7 +103,7 @@ launches = list(per_id.values())
 # a call = warm-up, pipe, 3 gated fallback kernels, forward then backward: take the last 10 launches that form one
 names = [l["name"] for l in launches]
 last_b = max(i for i, n in enumerate(names) if n.startswith("rts_backward_pipe_kernel<double, 3, 4, 0, 0, 1"))   # with the ym write
-first_f = max(i for i, n in enumerate(names[:last_b]) if n.startswith("scan_fwd_warm_kernel"))
+first_f = max(i for i, n in enumerate(names[:last_b]) if n.startswith("scan_fwd_warm"))
 call = launches[first_f:last_b + 4]
 c5_bytes = sum(l.get("dram__bytes_read.sum", 0) + l.get("dram__bytes_write.sum", 0) for l in call)
 c5_ms = sum(l.get("gpu__time_duration.sum", 0) for l in call) / 1e6
