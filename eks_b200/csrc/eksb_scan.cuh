@@ -484,7 +484,9 @@ scan_fwd_warm3_kernel(const T* __restrict__ obs, const T* __restrict__ C, const 
   RecB recb = reinterpret_cast<RecB>(warm_smem);
   GBuf gbuf = reinterpret_cast<GBuf>(warm_smem + sizeof(T) * 2 * F * REC * kLanes);
   SBuf sbuf = reinterpret_cast<SBuf>(warm_smem + sizeof(T) * 2 * F * (REC + GR) * kLanes);
-  __shared__ int stop;
+  // iteration at whose start everybody leaves; written once, by the phi warp, DURING the iteration before it (a plain
+  // flag could be seen by a thread still entering the iteration it was raised in, and not by its neighbours)
+  __shared__ long stop_at;
   const int lane = threadIdx.x & 31, role = threadIdx.x >> 5;      // 0 helper, 1 chain, 2 phi
   const long tiles = num_tiles_dev(B);
   const long w = blockIdx.x;                                        // (tile, chunk >= 1)
@@ -504,7 +506,7 @@ scan_fwd_warm3_kernel(const T* __restrict__ obs, const T* __restrict__ C, const 
   const long clen = ((c + 1) * L < Tn ? (c + 1) * L : Tn) - t0;
   const long steps = kcap > 0 ? (Tn - t0 < kcap ? Tn - t0 : kcap) : clen - 1;   // frames the recursion may take
   const long nb = (steps + F - 1) / F;
-  if (threadIdx.x == 0) stop = 0;
+  if (threadIdx.x == 0) stop_at = nb + 8;
   // helper state
   const T* o = obs + ((g * Tn + t0) * R2) * kLanes + lane;
   constexpr bool kOuter = (P * NS <= 36);
@@ -538,7 +540,7 @@ scan_fwd_warm3_kernel(const T* __restrict__ obs, const T* __restrict__ C, const 
   bool dead = false;
   for (long i = 0; i < nb + 2; ++i) {
     __syncthreads();
-    if (stop) break;
+    if (i >= stop_at) break;
     if (role == 0) {
       if (i < nb) {
 #pragma unroll
@@ -643,7 +645,7 @@ scan_fwd_warm3_kernel(const T* __restrict__ obs, const T* __restrict__ C, const 
                        : filt + ((g * Tn + t0 + done - 1) * SG) * kLanes + lane;
 #pragma unroll
           for (int q = 0; q < SG; ++q) f[q * kLanes] = sbuf[k & 1][q][lane];
-          if (lane == 0) { fcut[g * nc + c] = done; stop = 1; }
+          if (lane == 0) { fcut[g * nc + c] = done; stop_at = i + 1; }
         }
       }
     }
