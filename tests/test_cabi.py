@@ -29,6 +29,12 @@ def test_non_compute_entry_points():
     # (n,p) outside that list, e.g. (5,4) or five cameras' (3,10), are served by the runtime-dimension kernels
     # eksb_kf_forward_generic / eksb_rts_backward_generic (tests/test_gpu_round2.py::test_shapes_without_a_template_instantiation)
     assert lib.eksb_route_workspace_bytes(2048, 100000, 3, 4, 8) > 0 and lib.eksb_route_workspace_bytes(16384, 100000, 3, 4, 8) == 0
+    # time-split NLL sweep: few tiles x long tracks are routed, a batch that already fills the GPU with 8-chain CTAs is not,
+    # short tracks are not, shapes without the pipelined NLL kernel are not
+    assert lib.eksb_nll_workspace_bytes(32, 100000, 3, 4, 16, 8) > 0 and lib.eksb_nll_workspace_bytes(8192, 20000, 3, 4, 0, 8) > 0
+    assert lib.eksb_nll_workspace_bytes(8192, 20000, 3, 4, 16, 8) == 0 and lib.eksb_nll_workspace_bytes(32, 4000, 3, 4, 16, 8) == 0
+    assert lib.eksb_nll_workspace_bytes(32, 100000, 4, 6, 16, 8) == 0 and lib.eksb_nll_workspace_bytes(32, 100000, 3, 4, 16, 3) == 0
+    assert lib.eksb_kf_nll_ws_f64(None, None, None, None, None, None, None, 31, 4, 100, 3, 4, 0, 0, None, 0, None, None, None, 0, None) == -2
     # argument validation happens before any CUDA call
     assert lib.eksb_ensemble_f64(None, 5, 10, 4, 0, None, None, None) == -2
     assert b"bad argument" in lib.eksb_last_error_string()
