@@ -359,7 +359,7 @@ static int launch_nll_split(const T* obs, const T* m0, const T* S0, const T* C, 
   cudaMemsetAsync(sp.part, 0, (size_t)ns * tiles * nc * kLanes * sizeof(double), st);   // (a chunk with nothing to sum writes nothing)
   const long kcap = 4 * L;                                 // warm-up frames before a candidate is given up (evaluated whole)
   const char* w1 = getenv("EKSB_SCAN_WARM1");              // A/B switch: the one-warp warm-up kernel
-  if ((w1 && w1[0] == '1') || sizeof(T) != 8) {            // (float: see scan_run_fwd_off)
+  if ((w1 && w1[0] == '1') || sizeof(T) != 8 || tiles * (nc - 1) * ns > 3L * sm_count()) {   // (float, many chunks: see scan_run_fwd_off)
     dim3 wgrid((unsigned)((tiles * (nc - 1) + kScanWarps - 1) / kScanWarps), (unsigned)ns);
     if (yoff)
       scan_fwd_warm_kernel<T, N, P, 0, true><<<wgrid, kScanWarps * kLanes, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, fcut, gate,

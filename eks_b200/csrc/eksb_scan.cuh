@@ -728,4 +728,104 @@ scan_bwd_warm_kernel(const T* __restrict__ filt, const T* __restrict__ C, const 
   }
 }
 
+// The backward warm-up in two roles (any shape and type: nothing here is the scaled chain).  bwd_prep -- S = A Vf A^T + Q,
+// its inverse, the RTS gain J and the frame's (L, g) -- depends on the filtered record alone, so a helper warp forms the
+// records of batch i while the chain warp composes batch i - 1 onto the chunk's (E, L, g) element and tests |E|; the two
+// sit on different schedulers and each carries about half of the one-warp kernel's FP64 instructions.  Same contract as
+// scan_bwd_warm_kernel; K is a multiple of kWarmF instead of 16.
+template <typename T, int N> struct Warm2Smem {
+  static constexpr size_t kTotal = sizeof(T) * kLanes * 2 * kWarmF * Rec<N>::BWD;
+};
+template <typename T, int N, int P, int AM>
+__global__ void __launch_bounds__(2 * kLanes)
+scan_bwd_warm2_kernel(const T* __restrict__ filt, const T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ Q,
+                      int shared_mask, long B, long Tn, long L, long nc, long* __restrict__ bcut, int* __restrict__ gate,
+                      T* __restrict__ binit) {
+  constexpr int NS = Dim<N>::NS, SG = Dim<N>::SIGMA, SR = ScanRec<N>::BWD, REC = Rec<N>::BWD, F = kWarmF;
+  extern __shared__ __align__(16) unsigned char warm_smem[];
+  typedef T (*RecB)[F][REC][kLanes];
+  RecB recb = reinterpret_cast<RecB>(warm_smem);
+  __shared__ long stop_at;                                   // as in scan_fwd_warm3_kernel
+  const int lane = threadIdx.x & 31, role = threadIdx.x >> 5;   // 0 helper, 1 chain
+  const long w = blockIdx.x;
+  const long g = w / (nc - 1), c = w - g * (nc - 1);         // chunks [0, nc-1): the last one starts at the track's end
+  const long b = g * kLanes + lane, bp = b < B ? b : B - 1;
+  Params<T, N, P, AM> prm;
+  load_track_params<T, N, P, AM>(prm, C, A, Q, shared_mask, bp);
+  const T* f = filt + ((g * Tn + c * L) * SG) * kLanes + lane;   // chunk c is full length (c < nc - 1)
+  const long steps = L - 2 > 0 ? L - 2 : 0;                  // leave the virtual tile below at least one frame of its own
+  const long nb = (steps + F - 1) / F;
+  if (threadIdx.x == 0) stop_at = nb + 8;
+  T raw[F][SG];
+  if (role == 0) {
+#pragma unroll
+    for (int j = 0; j < F; ++j)
+      if (j < steps) {
+#pragma unroll
+        for (int r = 0; r < SG; ++r) raw[j][r] = f[((L - 1 - j) * SG + r) * kLanes];
+      }
+  }
+  T acc[SR];
+#pragma unroll
+  for (int i = 0; i < SR; ++i) acc[i] = T(0);
+#pragma unroll
+  for (int i = 0; i < N; ++i) acc[i * N + i] = T(1);
+  bool ok = true, dead = false;
+  for (long i = 0; i < nb + 1; ++i) {
+    __syncthreads();
+    if (i >= stop_at) break;
+    if (role == 0) {
+      if (i < nb) {
+#pragma unroll
+        for (int j = 0; j < F; ++j) {
+          if (i * F + j < steps) {
+            T cur[SG], rec[REC];
+#pragma unroll
+            for (int r = 0; r < SG; ++r) cur[r] = raw[j][r];
+            bwd_prep<T, N, P, AM>(prm, cur, cur + N, rec, ok);
+#pragma unroll
+            for (int r = 0; r < REC; ++r) recb[i & 1][j][r][lane] = rec[r];
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < F; ++j) {                       // the next batch's records: in flight across the barrier
+          const long t = (i + 1) * F + j;
+          if (t < steps) {
+#pragma unroll
+            for (int r = 0; r < SG; ++r) raw[j][r] = f[((L - 1 - t) * SG + r) * kLanes];
+          }
+        }
+      }
+    } else if (i >= 1) {
+      const long k = i - 1;
+#pragma unroll
+      for (int j = 0; j < F; ++j) {
+        if (k * F + j < steps) {
+          T rec[REC];
+#pragma unroll
+          for (int r = 0; r < REC; ++r) rec[r] = recb[k & 1][j][r][lane];
+          bwd_summary_step<T, N>(rec, acc);
+        }
+      }
+      T mx = T(0);
+#pragma unroll
+      for (int q = 0; q < N * N; ++q) mx = fmax(mx, fabs(acc[q]));
+      const long done = (k + 1) * F < steps ? (k + 1) * F : steps;
+      if (__all_sync(0xffffffffu, mx < ScanCut<T>::value)) {   // (g, L) of the element = smoothed (ms, Vs) of frame (c+1) L - done
+        dead = true;
+        T* o = binit + ((g * nc + c) * SG) * kLanes + lane;
+#pragma unroll
+        for (int q = 0; q < N; ++q) o[q * kLanes] = acc[N * N + NS + q];
+#pragma unroll
+        for (int q = 0; q < NS; ++q) o[(N + q) * kLanes] = acc[N * N + q];
+        if (lane == 0) { bcut[g * nc + c] = done; stop_at = i + 1; }
+      }
+    }
+  }
+  if (role == 1 && !dead && lane == 0) {
+    bcut[g * nc + c] = L;
+    atomicOr(gate, 1);
+  }
+}
+
 }  // namespace eksb

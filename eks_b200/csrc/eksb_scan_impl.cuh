@@ -93,7 +93,9 @@ static int scan_run_fwd_off(const T* obs, const T* yoff, const T* m0, const T* S
     // three-role warm-up: double only (its scaled chain forms det(adj S + det S Lam) ~ (var)^6: below the float range
     // for process noise ~1e-7 -- the main kernels' chain has the same limit, but a warm-up has no fallback of its own)
     if constexpr (AM == 0 && N <= 3 && sizeof(T) == 8) {
-      if (scan_env_long("EKSB_SCAN_WARM1", 0))             // A/B switch: the one-warp warm-up kernel
+      // ... and only while its three warps per chunk find schedulers of their own: measured (ncu, f64) 256 chunks 0.216 ->
+      // 0.140 ms, 368 (NLL sweep) 5.6 -> 4.6 ms per sweep, 512 chunks 0.22 -> 0.26 ms
+      if (scan_env_long("EKSB_SCAN_WARM1", 0) || tiles * (nc - 1) > 3L * sm_count())   // EKSB_SCAN_WARM1=1: A/B switch
         scan_fwd_warm_kernel<T, N, P, AM, OFF><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(obs, C, A, Q, mask, B, Tn, L, nc, yoff, w.fcut, w.alive + 2, filt, (const T*)nullptr, (T*)nullptr, 0L);
       else {
         cudaFuncSetAttribute(scan_fwd_warm3_kernel<T, N, P, OFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Warm3Smem<T, N>::kTotal);
@@ -143,7 +145,12 @@ static int scan_run_bwd(const T* filt, const T* C, const T* A, const T* Q, int m
   const int* gate = nullptr;
   if (scan_v2_enabled()) {
     gate = w.alive + 3;
-    scan_bwd_warm_kernel<T, N, P, AM><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, w.bcut, w.alive + 3, w.binit);
+    if (scan_env_long("EKSB_SCAN_WARM1", 0)) {               // A/B switch: the one-warp warm-up kernel
+      scan_bwd_warm_kernel<T, N, P, AM><<<scan_blocks(tiles * (nc - 1)), thr, 0, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, w.bcut, w.alive + 3, w.binit);
+    } else {
+      cudaFuncSetAttribute(scan_bwd_warm2_kernel<T, N, P, AM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Warm2Smem<T, N>::kTotal);
+      scan_bwd_warm2_kernel<T, N, P, AM><<<(unsigned)(tiles * (nc - 1)), 2 * kLanes, Warm2Smem<T, N>::kTotal, st>>>(filt, C, A, Q, mask, B, Tn, L, nc, w.bcut, w.alive + 3, w.binit);
+    }
     int rc = check_launch("scan backward warm-up");
     if (rc != EKSB_OK) return rc;
     VTiles vt;
